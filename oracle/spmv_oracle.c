@@ -1,0 +1,371 @@
+/*
+ * spmv_oracle.c -- CPU restatement of the reference algorithms on the SpMV hot path.
+ *
+ * TEST INFRASTRUCTURE ONLY.  Nothing under oracle/ is part of the product: only tests/,
+ * __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load
+ * this library, and there only as the checker or as the timed CPU baseline.
+ *
+ * Parity status: PINNED.  Every function below is checked in tests/test_oracle_pin.py
+ * against the reference's own code compiled from /root/reference into oracle/_ref/
+ * (see oracle/Makefile) and against the committed fixtures in tests/golden/ that were
+ * produced by those reference builds (tests/golden/make_golden.py).
+ *
+ * Reference paths are relative to /root/reference.  K/ = benchmark_code/BENCH/src/spmv_kernels/.
+ */
+#define _GNU_SOURCE
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+#include <math.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+/* ---------------------------------------------------------------------------------------
+ * A2. serial CSR kernel -- K/csr.cpp:334-350 (subkernel_csr_scalar)
+ * one running nnz index across rows, one accumulator, ascending j, every row stored.
+ * ------------------------------------------------------------------------------------- */
+void oracle_csr_spmv_scalar(const int32_t *row_ptr, const int32_t *col_ind, const double *val,
+                            const double *x, double *y, int64_t i_s, int64_t i_e)
+{
+	int64_t j = row_ptr[i_s];
+	for (int64_t i = i_s; i < i_e; i++) {
+		int64_t j_e = row_ptr[i + 1];
+		double sum = 0;
+		for (; j < j_e; j++)
+			sum += val[j] * x[col_ind[j]];
+		y[i] = sum;
+	}
+}
+
+/* The north-star per-row parity bound: bound[i] = sum_j |a_ij * x_j|  (BASELINE.md section 2). */
+void oracle_row_abs_bound(const int32_t *row_ptr, const int32_t *col_ind, const double *val,
+                          const double *x, double *bound, int64_t m)
+{
+	#pragma omp parallel for schedule(static)
+	for (int64_t i = 0; i < m; i++) {
+		double s = 0;
+		for (int64_t j = row_ptr[i]; j < row_ptr[i + 1]; j++)
+			s += fabs(val[j] * x[col_ind[j]]);
+		bound[i] = s;
+	}
+}
+
+/* ---------------------------------------------------------------------------------------
+ * A1. nnz-balanced partitioner -- lib/parallel_util.h:156-184
+ *     (loop_partitioner_balance_prefix_sums) + lib/macros/macrolib.h:506-581
+ *     (macros_binary_search with the default comparator and distance).
+ * Sums[N] is never read.  Ties in distance go to the upper index; equal values resolve
+ * to the leftmost index holding the value.
+ * ------------------------------------------------------------------------------------- */
+static int64_t closest_index(const int32_t *A, int64_t lo, int64_t hi, int64_t target)
+{
+	int64_t s = lo, e = hi, mid;
+	if (target < A[s])
+		return s;
+	if (target > A[e])
+		return e;
+	for (;;) {
+		mid = (s + e) / 2;
+		if (mid == s || mid == e)
+			break;
+		if (target > A[mid])
+			s = mid;
+		else
+			e = mid;
+	}
+	if (target == A[s])
+		return s;
+	if (target == A[e])
+		return e;
+	int64_t ds = llabs(target - (int64_t)A[s]);
+	int64_t de = llabs(target - (int64_t)A[e]);
+	return (ds < de) ? s : e;
+}
+
+void oracle_partition_prefix_sums(int64_t num_workers, int64_t worker_pos, const int32_t *sums,
+                                  int64_t N, int64_t total, int64_t *start, int64_t *end)
+{
+	int64_t target = sums[0] + (total * worker_pos) / num_workers;
+	int64_t target_next = sums[0] + (total * (worker_pos + 1)) / num_workers;
+	*start = (worker_pos == 0) ? 0 : closest_index(sums, 0, N - 1, target);
+	*end = (worker_pos == num_workers - 1) ? N : closest_index(sums, 0, N - 1, target_next);
+}
+
+/* CPU baseline "port": OpenMP CSR, rows split per thread by nnz exactly as the reference does
+ * (K/csr.cpp:140 partition in the ctor, K/csr.cpp:381-404 compute_csr).  bounds has 2*T slots
+ * and is filled on first use when bounds[1] < 0. */
+void oracle_csr_spmv_omp(const int32_t *row_ptr, const int32_t *col_ind, const double *val,
+                         const double *x, double *y, int64_t m, int64_t nnz,
+                         int64_t *bounds, int num_threads)
+{
+	if (bounds[1] < 0) {
+		for (int t = 0; t < num_threads; t++)
+			oracle_partition_prefix_sums(num_threads, t, row_ptr, m, nnz, &bounds[2 * t], &bounds[2 * t + 1]);
+	}
+	#pragma omp parallel num_threads(num_threads)
+	{
+		#ifdef _OPENMP
+		int t = omp_get_thread_num();
+		#else
+		int t = 0;
+		#endif
+		oracle_csr_spmv_scalar(row_ptr, col_ind, val, x, y, bounds[2 * t], bounds[2 * t + 1]);
+	}
+}
+
+int oracle_max_threads(void)
+{
+	#ifdef _OPENMP
+	return omp_get_max_threads();
+	#else
+	return 1;
+	#endif
+}
+
+/* ---------------------------------------------------------------------------------------
+ * A6. merge-path diagonal search -- K/merge.cpp:230-251 (MergePathSearch); list A is
+ * row_end = row_ptr + 1 (length m), list B is the counting sequence 0..nnz-1.
+ * ------------------------------------------------------------------------------------- */
+void oracle_merge_path_search(int64_t diagonal, const int32_t *row_end, int64_t m, int64_t nnz,
+                              int64_t *out_row, int64_t *out_nz)
+{
+	int64_t x_min = diagonal - nnz > 0 ? diagonal - nnz : 0;
+	int64_t x_max = diagonal < m ? diagonal : m;
+	while (x_min < x_max) {
+		int64_t pivot = (x_min + x_max) >> 1;
+		if (row_end[pivot] <= diagonal - pivot - 1)
+			x_min = pivot + 1;
+		else
+			x_max = pivot;
+	}
+	*out_row = x_min < m ? x_min : m;
+	*out_nz = diagonal - x_min;
+}
+
+/* Merge-based CsrMV with T workers -- K/merge.cpp:256-318 (OmpMergeCsrmv): items per worker
+ * = ceil((m+nnz)/T), whole rows then the partial last row, serial carry-out fix-up.
+ * coords (2*(T+1) int64) receives the (row, nz) start coordinate of every worker + the end. */
+void oracle_merge_csrmv(int64_t T, const int32_t *row_ptr, const int32_t *col_ind, const double *val,
+                        const double *x, double *y, int64_t m, int64_t nnz, int64_t *coords)
+{
+	const int32_t *row_end = row_ptr + 1;
+	int64_t items = m + nnz;
+	int64_t per = (items + T - 1) / T;
+	int64_t *carry_row = (int64_t *)malloc(T * sizeof(int64_t));
+	double *carry_val = (double *)malloc(T * sizeof(double));
+	for (int64_t t = 0; t < T; t++) {
+		int64_t d0 = per * t < items ? per * t : items;
+		int64_t d1 = d0 + per < items ? d0 + per : items;
+		int64_t r, z, r1, z1;
+		oracle_merge_path_search(d0, row_end, m, nnz, &r, &z);
+		oracle_merge_path_search(d1, row_end, m, nnz, &r1, &z1);
+		if (coords) {
+			coords[2 * t] = r;
+			coords[2 * t + 1] = z;
+			if (t == T - 1) {
+				coords[2 * T] = r1;
+				coords[2 * T + 1] = z1;
+			}
+		}
+		for (; r < r1; ++r) {
+			double tot = 0.0;
+			for (; z < row_end[r]; ++z)
+				tot += val[z] * x[col_ind[z]];
+			y[r] = tot;
+		}
+		double tot = 0.0;
+		for (; z < z1; ++z)
+			tot += val[z] * x[col_ind[z]];
+		carry_row[t] = r1;
+		carry_val[t] = tot;
+	}
+	for (int64_t t = 0; t < T - 1; ++t)
+		if (carry_row[t] < m)
+			y[carry_row[t]] += carry_val[t];
+	free(carry_row);
+	free(carry_val);
+}
+
+/* ---------------------------------------------------------------------------------------
+ * A3 + A4. SELL-C-sigma conversion -- K/sell-C-s/RISC-V/radix_sort.c:36-122,
+ * sellcs_utils.c:36-48, sellcs_format.c:137-200 (csr_to_sellcs).
+ * The reference's LSD radix passes amount to a STABLE sort by DESCENDING row length inside
+ * each sigma window (ties keep ascending original row index); restated here as a stable
+ * counting sort over the window's length range.  Outputs use 64-bit slice pointers
+ * (the reference's -DINDEX64 build; its int32 build agrees after widening while it fits).
+ * Caller allocates col_out / val_out with slice_ptr[nslices] entries after a sizing call
+ * (col_out == NULL -> only row_order / slice_width / slice_ptr are produced).
+ * ------------------------------------------------------------------------------------- */
+int64_t oracle_sellcs_convert(const int32_t *row_ptr, const int32_t *col_ind, const double *val,
+                              int64_t m, int64_t C, int64_t sigma,
+                              int32_t *row_order, int32_t *slice_width, int64_t *slice_ptr,
+                              int32_t *col_out, double *val_out)
+{
+	int64_t nslices = (m + C - 1) / C;
+	int64_t *len_sorted = (int64_t *)malloc((m > 0 ? m : 1) * sizeof(int64_t));
+	for (int64_t k = 0; k < m; k += sigma) {
+		int64_t k_end = k + sigma > m ? m : k + sigma;
+		int64_t maxlen = 0;
+		for (int64_t i = k; i < k_end; i++) {
+			int64_t l = row_ptr[i + 1] - row_ptr[i];
+			if (l > maxlen)
+				maxlen = l;
+		}
+		int64_t *cnt = (int64_t *)calloc(maxlen + 2, sizeof(int64_t));
+		for (int64_t i = k; i < k_end; i++)
+			cnt[row_ptr[i + 1] - row_ptr[i]]++;
+		/* descending: position of first element of length l = number of rows longer than l */
+		int64_t run = 0;
+		for (int64_t l = maxlen; l >= 0; l--) {
+			int64_t c = cnt[l];
+			cnt[l] = run;
+			run += c;
+		}
+		for (int64_t i = k; i < k_end; i++) {
+			int64_t l = row_ptr[i + 1] - row_ptr[i];
+			int64_t pos = k + cnt[l]++;
+			row_order[pos] = (int32_t)i;
+			len_sorted[pos] = l;
+		}
+		free(cnt);
+	}
+	int64_t total = 0;
+	for (int64_t s = 0; s < nslices; s++) {
+		int64_t w = len_sorted[s * C];
+		slice_ptr[s] = total;
+		slice_width[s] = (int32_t)w;
+		total += w * C;
+	}
+	slice_ptr[nslices] = total;
+	free(len_sorted);
+	if (col_out == NULL)
+		return total;
+	memset(col_out, 0, total * sizeof(int32_t));
+	memset(val_out, 0, total * sizeof(double));
+	for (int64_t r = 0; r < m; r++) {
+		int64_t w = slice_ptr[r / C] + (r % C);
+		int64_t orig = row_order[r];
+		for (int64_t j = row_ptr[orig]; j < row_ptr[orig + 1]; j++) {
+			val_out[w] = val[j];
+			col_out[w] = col_ind[j];
+			w += C;
+		}
+	}
+	return total;
+}
+
+/* a7. SELL-C-sigma SpMV semantics -- K/sell-C-s/RISC-V/sellcs_mv_kernels_epi.c:178-257:
+ * per slice, lane-wise fused multiply-accumulate down the slice width, then scatter through
+ * row_order; the ragged last slice uses min(C, m - s*C) lanes.  (The reference kernel is
+ * RISC-V vector intrinsics; vfmacc is a fused multiply-add, hence fma() here.) */
+void oracle_sellcs_spmv(int64_t m, int64_t C, const int32_t *row_order, const int32_t *slice_width,
+                        const int64_t *slice_ptr, const int32_t *col, const double *val,
+                        const double *x, double *y)
+{
+	int64_t nslices = (m + C - 1) / C;
+	#pragma omp parallel for schedule(static)
+	for (int64_t s = 0; s < nslices; s++) {
+		int64_t row0 = s * C;
+		int64_t lanes = row0 + C > m ? m - row0 : C;
+		for (int64_t l = 0; l < lanes; l++) {
+			double acc = 0.0;
+			int64_t p = slice_ptr[s] + l;
+			for (int64_t k = 0; k < slice_width[s]; k++, p += C)
+				acc = fma(x[col[p]], val[p], acc);
+			y[row_order[row0 + l]] = acc;
+		}
+	}
+}
+
+/* ---------------------------------------------------------------------------------------
+ * a11. gold vector + pass criterion -- benchmark_code/BENCH/src/bench_spmv.cpp:108-235
+ * (check_accuracy): per-row Kahan sum in _Float128; max relative difference over rows with
+ * y_gold > eps (signed test, as in the reference); plus mae / max_ae / mse.
+ * out[0]=maxRelDiff out[1]=mae out[2]=max_ae out[3]=mse ; gold (may be NULL) gets (double)y_gold.
+ * ------------------------------------------------------------------------------------- */
+void oracle_check_accuracy(const int32_t *row_ptr, const int32_t *col_ind, const double *val,
+                           const double *x, const double *y, int64_t m, double eps,
+                           double *gold, double *out)
+{
+	_Float128 *yg = (_Float128 *)malloc((m > 0 ? m : 1) * sizeof(_Float128));
+	#pragma omp parallel for schedule(static)
+	for (int64_t i = 0; i < m; i++) {
+		_Float128 sum = 0, comp = 0, v, tmp;
+		for (int64_t j = row_ptr[i]; j < row_ptr[i + 1]; j++) {
+			v = (_Float128)val[j] * (_Float128)x[col_ind[j]] - comp;
+			tmp = sum + v;
+			comp = (tmp - sum) - v;
+			sum = tmp;
+		}
+		yg[i] = sum;
+	}
+	_Float128 maxrel = 0, sae = 0, sse = 0, maxae = 0;
+	for (int64_t i = 0; i < m; i++) {
+		_Float128 d = yg[i] - (_Float128)y[i];
+		if (d < 0)
+			d = -d;
+		sae += d;
+		sse += d * d;
+		if (d > maxae)
+			maxae = d;
+		if (yg[i] > (_Float128)eps) {
+			_Float128 r = d / yg[i];
+			if (r > maxrel)
+				maxrel = r;
+		}
+		if (gold)
+			gold[i] = (double)yg[i];
+	}
+	out[0] = (double)maxrel;
+	out[1] = m ? (double)(sae / m) : 0;
+	out[2] = (double)maxae;
+	out[3] = m ? (double)(sse / m) : 0;
+	free(yg);
+}
+
+/* ---------------------------------------------------------------------------------------
+ * a10. CSR-Adaptive greedy row blocking (behavioural reference for nnz-tiled binning) --
+ * K/GPU_clean/csr_adaptive_cuda.cu:46-79: blocks of consecutive rows holding at most
+ * block_nnz non-zeros, a lone over-long row gets a block of its own, list padded with m to a
+ * multiple of multiblock and terminated with m.  row_blocks needs m + multiblock + 1 slots.
+ * ------------------------------------------------------------------------------------- */
+int64_t oracle_adaptive_rowblocks(const int32_t *row_ptr, int64_t m, int64_t block_nnz,
+                                  int64_t multiblock, int32_t *row_blocks)
+{
+	int64_t cnt = 1, sum = 0, last_i = 0;
+	row_blocks[0] = 0;
+	for (int64_t i = 1; i < m; i++) {
+		sum += row_ptr[i] - row_ptr[i - 1];
+		if (sum == block_nnz) {
+			last_i = i;
+			row_blocks[cnt++] = (int32_t)i;
+			sum = 0;
+		} else if (sum > block_nnz) {
+			if (i - last_i > 1) {
+				row_blocks[cnt++] = (int32_t)(i - 1);
+				i--;
+			} else if (i - last_i == 1) {
+				row_blocks[cnt++] = (int32_t)i;
+			}
+			last_i = i;
+			sum = 0;
+		}
+	}
+	while (cnt % multiblock != 0)
+		row_blocks[cnt++] = (int32_t)m;
+	row_blocks[cnt++] = (int32_t)m;
+	return cnt;
+}
+
+/* FNV-1a-64 over raw bytes: the fingerprint used for the generator pins in SURVEY.md App. C. */
+uint64_t oracle_fnv1a64(const void *data, int64_t nbytes)
+{
+	const unsigned char *p = (const unsigned char *)data;
+	uint64_t h = 0xcbf29ce484222325ULL;
+	for (int64_t i = 0; i < nbytes; i++) {
+		h ^= p[i];
+		h *= 0x100000001b3ULL;
+	}
+	return h;
+}
