@@ -1,0 +1,146 @@
+/*
+ * b200spmv.h -- C-ABI of the B200-native fp64 SpMV engine (libb200spmv.so, sm_100a only).
+ *
+ * Drop-in boundary.  These entry points are what a format plugin of the reference harness
+ * binds (reference paths relative to /root/reference, K/ = benchmark_code/BENCH/src/spmv_kernels/):
+ *
+ *   b200spmv_create()        <- csr_to_format(INT_T* row_ptr, INT_T* col_ind, ValueTypeReference* values,
+ *                                             long m, long n, long nnz, long symmetric, long symmetry_expanded)
+ *                               K/spmv_kernel.h:28 ; CSR ctor K/csr.cpp:58-167,221-240 ;
+ *                               SELL-C-sigma ctor K/sell_c_s.cpp:58-75 -> K/sell-C-s/RISC-V/sellcs_format.c:137-224
+ *   b200spmv_spmv_host()     <- Matrix_Format::spmv(ValueType* x, ValueType* y)   K/spmv_kernel.h:16
+ *                               (reference GPU-plugin convention: K/GPU_clean/cuda_csr.cu:353-430)
+ *   b200spmv_spmv_device()   <- the same product with x / y already resident in HBM (iterated SpMV;
+ *                               nearest reference caller benchmark_code/BENCH/src/bench_cg.cpp:93-292)
+ *   b200spmv_partition*()    <- loop_partitioner_balance_prefix_sums()            lib/parallel_util.h:156-184
+ *   b200spmv_merge_coords()  <- MergePathSearch()                                 K/merge.cpp:230-251
+ *   b200spmv_export()        <- read-back of the converted layout for bit-exact tests
+ *                               (sellcs_matrix_t fields, K/sell-C-s/RISC-V/sellcs-spmv.h:28-47)
+ *   b200spmv_last_error()    <- error() / gpuCudaErrorCheck print-and-exit        lib/debug.h:135, lib/cuda/cuda_util.h:5-14
+ *
+ * Conventions: plain pointers and sizes, no C++ / torch types; every function returns 0 on
+ * success and non-zero on failure (message via b200spmv_last_error()); nothing throws.  A handle
+ * is not thread-safe (the reference calls csr_to_format / spmv from one thread).  There is no CPU
+ * fallback: without a CUDA device every compute entry point fails.
+ * INT_T = int32_t, ValueType = double (the reference's `_d` build, make.sh:166,212-213).
+ */
+#ifndef B200SPMV_H
+#define B200SPMV_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct b200spmv b200spmv_t;
+
+enum {
+	B200SPMV_CSR_ADAPTIVE = 0,   /* nnz-tiled adaptive CSR (thread / sub-warp / warp / block per row) */
+	B200SPMV_SELL_C_SIGMA = 1    /* SELL-C-sigma, converted on the GPU                               */
+};
+
+/* b200spmv_spmv_host_ex flags */
+enum {
+	B200SPMV_SKIP_X_UPLOAD   = 1,   /* x already uploaded by an earlier call (reference convention)  */
+	B200SPMV_SKIP_Y_DOWNLOAD = 2    /* leave y in HBM                                                  */
+};
+
+/* b200spmv_export selectors */
+enum {
+	B200SPMV_X_ROW_ORDER   = 1,    /* int32[m]            sellcs row_order                            */
+	B200SPMV_X_SLICE_WIDTH = 2,    /* int32[nslices]      sellcs slice_widths                         */
+	B200SPMV_X_SLICE_PTR   = 3,    /* int64[nslices+1]    sellcs slice_pointers                       */
+	B200SPMV_X_SELL_COL    = 4,    /* int32[padded]       sellcs column_indices                       */
+	B200SPMV_X_SELL_VAL    = 5,    /* double[padded]      sellcs values                               */
+	B200SPMV_X_TILE_ROW    = 6,    /* int32[ntiles+1]     first row owned by each CSR tile            */
+	B200SPMV_X_SPLIT_ROW   = 7,    /* int32[nsplit]       rows finished by the fix-up kernel          */
+	B200SPMV_X_SPLIT_TILE  = 8     /* int32[nsplit]       owner tile of each split row                */
+};
+
+typedef struct b200spmv_opts {
+	int32_t format;           /* B200SPMV_CSR_ADAPTIVE | B200SPMV_SELL_C_SIGMA                          */
+	int32_t device;           /* CUDA device ordinal, -1 = current                                      */
+	int32_t sell_C;           /* slice height: power of two in [2, 256]; default 32                     */
+	int32_t sell_sigma;       /* sort window, multiple of sell_C; default 16384 (K/sell_c_s.cpp:59)     */
+	int32_t csr_nnz_per_thread; /* 8 | 16 | 32 non-zeros per thread of a 256-thread tile; 0 = auto      */
+	int32_t csr_ext;          /* tail-extension capacity in nnz (multiple of 8); 0 = auto               */
+	int32_t x_hint;           /* 0: L2 evict_last hint on x gathers (default), 1: plain loads           */
+	int32_t reserved[9];
+} b200spmv_opts;
+
+/* extra outputs / inputs of one device-resident product (all pointers are DEVICE pointers) */
+typedef struct b200spmv_launch {
+	const double * scale;     /* optional scalar s: y = s * (A x)        (power iteration, A(s x) = s A x) */
+	double * norm2;           /* optional: receives sum_i y_i^2 of this handle's rows                    */
+	double * y_peer[8];       /* optional extra destinations written like y (peer GPUs' next-x buffers)  */
+	int32_t n_peer;
+	int32_t pad_;
+} b200spmv_launch;
+
+void b200spmv_default_opts(b200spmv_opts * opts);
+
+/* Deep-copies / uploads the CSR arrays (HOST pointers, borrowed for the call only) and builds the format. */
+int b200spmv_create(b200spmv_t ** out, const int32_t * row_ptr, const int32_t * col_ind, const double * values,
+                    int64_t m, int64_t n, int64_t nnz, const b200spmv_opts * opts);
+
+/* Same, from DEVICE pointers (copied device-to-device).  row_ptr may start at a non-zero offset
+ * (a row shard of a larger matrix): it is rebased; col_ind / values point at the shard's first entry. */
+int b200spmv_create_device(b200spmv_t ** out, const int32_t * d_row_ptr, const int32_t * d_col_ind, const double * d_values,
+                           int64_t m, int64_t n, int64_t nnz, const b200spmv_opts * opts);
+
+void b200spmv_destroy(b200spmv_t * h);
+
+/* y = A x with HOST vectors: H2D of x, kernel(s), D2H of y, stream synchronised on return. */
+int b200spmv_spmv_host(b200spmv_t * h, const double * x, double * y);
+int b200spmv_spmv_host_ex(b200spmv_t * h, const double * x, double * y, int32_t flags);
+
+/* y = A x with DEVICE vectors on `stream` (a cudaStream_t, NULL = the handle's own stream); asynchronous. */
+int b200spmv_spmv_device(b200spmv_t * h, const double * dx, double * dy, void * stream);
+int b200spmv_spmv_device_ex(b200spmv_t * h, const double * dx, double * dy, void * stream, const b200spmv_launch * launch);
+
+/* Number of kernel launches one b200spmv_spmv_device call issues for this handle (1 or 2). */
+int32_t b200spmv_launches_per_spmv(const b200spmv_t * h);
+
+/* Format statistics: out[0]=mem_footprint bytes, [1]=ntiles or nslices, [2]=nsplit rows,
+ * [3]=padded entries (SELL) or nnz, [4]=tile nnz (CSR) or C (SELL), [5]=ext capacity or sigma, [6]=convert ms. */
+int b200spmv_stats(const b200spmv_t * h, double * out, int32_t n_out);
+
+int b200spmv_export(const b200spmv_t * h, int32_t what, void * dst_host, int64_t capacity_bytes, int64_t * count_out);
+
+/* Reference partitioner on the GPU: bounds_out[2p], bounds_out[2p+1] = [i_s, i_e) of worker p of W.
+ * sums has N+1 entries of which sums[N] is never read (as in the reference); total = sums[N]-sums[0]. */
+int b200spmv_partition_device(const int32_t * d_sums, int64_t N, int64_t total, int32_t W, int64_t * bounds_out_host);
+int b200spmv_partition(const int32_t * sums_host, int64_t N, int64_t total, int32_t W, int64_t * bounds_out_host);
+
+/* Merge-path coordinates on the GPU for W workers: coords_out[2t], [2t+1] = (row, nz) where worker t
+ * starts, t = 0..W (W+1 pairs), items per worker = ceil((m+nnz)/W) as K/merge.cpp:277-283. */
+int b200spmv_merge_coords(const b200spmv_t * h, int32_t W, int64_t * coords_out_host);
+
+/* Device memory helpers so that a host program needs no CUDA runtime of its own. */
+int b200spmv_device_count(int32_t * count);
+int b200spmv_set_device(int32_t device);
+int b200spmv_malloc(void ** dptr, int64_t bytes);
+int b200spmv_free(void * dptr);
+int b200spmv_memcpy_h2d(void * dst, const void * src, int64_t bytes);
+int b200spmv_memcpy_d2h(void * dst, const void * src, int64_t bytes);
+int b200spmv_malloc_host(void ** hptr, int64_t bytes);      /* pinned */
+int b200spmv_free_host(void * hptr);
+int b200spmv_synchronize(void);
+/* CUDA IPC: export a device allocation to / import one from another process of the same box. */
+int b200spmv_ipc_export(void * dptr, unsigned char handle_out[64]);
+int b200spmv_ipc_import(const unsigned char handle[64], void ** dptr_out);
+int b200spmv_ipc_close(void * dptr);
+
+/* Device timing of `iters` back-to-back products (CUDA events on the handle's stream); when
+ * flush_bytes > 0 a scratch buffer of that size is rewritten before every product (outside the
+ * per-product event pair) so that nothing of the matrix survives in L2.  ms_out[iters]. */
+int b200spmv_time_device(b200spmv_t * h, const double * dx, double * dy, int32_t iters, int64_t flush_bytes, float * ms_out);
+
+const char * b200spmv_last_error(void);
+const char * b200spmv_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200SPMV_H */

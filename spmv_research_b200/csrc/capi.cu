@@ -1,0 +1,250 @@
+// capi.cu -- the extern "C" boundary of libb200spmv (see include/b200spmv.h for the contract).
+#include "common.cuh"
+
+thread_local char g_b200_err[512] = "";
+
+extern "C" const char * b200spmv_last_error(void) { return g_b200_err; }
+extern "C" const char * b200spmv_version(void) { return "b200spmv 0.1 (sm_100a)"; }
+
+extern "C" void b200spmv_default_opts(b200spmv_opts * o)
+{
+	memset(o, 0, sizeof(*o));
+	o->format = B200SPMV_CSR_ADAPTIVE;
+	o->device = -1;
+	o->sell_C = 32;
+	o->sell_sigma = 16384;
+}
+
+static int check_device(int device)
+{
+	int ndev = 0;
+	cudaError_t e = cudaGetDeviceCount(&ndev);
+	if (e != cudaSuccess || ndev < 1)
+		B200_FAIL("no CUDA device: libb200spmv has no CPU fallback (%s)", cudaGetErrorString(e));
+	if (device >= ndev)
+		B200_FAIL("device %d out of range (%d devices)", device, ndev);
+	if (device >= 0)
+		CU(cudaSetDevice(device));
+	int cur = 0, major = 0;
+	CU(cudaGetDevice(&cur));
+	CU(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, cur));
+	if (major != 10)
+		B200_FAIL("device %d has compute capability %d.x; this library carries sm_100a code only", cur, major);
+	return 0;
+}
+
+static bool is_pow2(int64_t v) { return v > 0 && (v & (v - 1)) == 0; }
+
+static int validate_opts(const b200spmv_opts * in, b200spmv_opts * o, int64_t m, int64_t n, int64_t nnz)
+{
+	if (in)
+		*o = *in;
+	else
+		b200spmv_default_opts(o);
+	if (m < 0 || n < 0 || nnz < 0)
+		B200_FAIL("negative dimension");
+	if (m >= 0x7fffffffLL || n > 0x7fffffffLL || nnz > 0x7fffffffLL)
+		B200_FAIL("m, n and nnz must fit int32 indices (INT_T = int32_t)");
+	if (o->format != B200SPMV_CSR_ADAPTIVE && o->format != B200SPMV_SELL_C_SIGMA)
+		B200_FAIL("unknown format %d", o->format);
+	if (o->sell_C == 0)
+		o->sell_C = 32;
+	if (o->sell_sigma == 0)
+		o->sell_sigma = 16384;
+	if (!is_pow2(o->sell_C) || o->sell_C < 2 || o->sell_C > 256)
+		B200_FAIL("sell_C must be a power of two in [2, 256]");
+	if (o->sell_sigma < o->sell_C || o->sell_sigma % o->sell_C)
+		B200_FAIL("sell_sigma must be a positive multiple of sell_C");
+	if (o->csr_nnz_per_thread == 0) {
+		// auto: larger windows for longer rows keep the tail extension a small fraction of the window
+		const double avg = m > 0 ? (double) nnz / (double) m : 0.0;
+		o->csr_nnz_per_thread = (avg > 96.0) ? 16 : 8;
+	}
+	if (o->csr_nnz_per_thread != 8 && o->csr_nnz_per_thread != 16 && o->csr_nnz_per_thread != 32)
+		B200_FAIL("csr_nnz_per_thread must be 8, 16 or 32");
+	if (o->csr_ext == 0)
+		o->csr_ext = (o->csr_nnz_per_thread == 8) ? 1024 : 2048;
+	if (o->csr_ext < 64 || o->csr_ext % 64 || o->csr_ext > 8192)
+		B200_FAIL("csr_ext must be a multiple of 64 in [64, 8192]");
+	return 0;
+}
+
+__global__ void rebase_row_ptr_kernel(const int32_t * __restrict__ in, int32_t * __restrict__ out, int64_t m1)
+{
+	const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < m1)
+		out[i] = in[i] - in[0];
+}
+
+static void free_handle(b200spmv * h)
+{
+	if (!h)
+		return;
+	void * ptrs[] = { h->d_row_ptr, h->d_col, h->d_val, h->d_tile_row, h->d_split_row, h->d_split_tile, h->d_tile_head, h->d_tile_tail,
+	                  h->d_row_order, h->d_slice_width, h->d_slice_ptr, h->d_scol, h->d_sval, h->d_x, h->d_y, h->d_norm_partial };
+	for (void * p : ptrs)
+		if (p)
+			cudaFree(p);
+	if (h->stream)
+		cudaStreamDestroy(h->stream);
+	free(h);
+}
+
+// Builds a handle from CSR arrays; `kind` says where the inputs live.
+static int create_common(b200spmv ** out, const int32_t * row_ptr, const int32_t * col_ind, const double * values,
+                         int64_t m, int64_t n, int64_t nnz, const b200spmv_opts * opts_in, cudaMemcpyKind kind)
+{
+	if (!out)
+		B200_FAIL("out is NULL");
+	*out = nullptr;
+	if (!row_ptr || (nnz > 0 && (!col_ind || !values)))
+		B200_FAIL("NULL CSR array");
+	b200spmv_opts o;
+	if (validate_opts(opts_in, &o, m, n, nnz))
+		return 1;
+	if (check_device(o.device))
+		return 1;
+	b200spmv * h = (b200spmv *) calloc(1, sizeof(b200spmv));
+	if (!h)
+		B200_FAIL("out of host memory");
+	h->format = o.format;
+	CU(cudaGetDevice(&h->device));
+	h->m = m;
+	h->n = n;
+	h->nnz = nnz;
+	h->x_hint = o.x_hint;
+	h->npt = o.csr_nnz_per_thread;
+	h->tile_nnz = CSR_THREADS * h->npt;
+	h->ext = o.csr_ext;
+	h->C = o.sell_C;
+	h->sigma = o.sell_sigma;
+	int rc = 1;
+	cudaEvent_t e0 = nullptr, e1 = nullptr;
+	do {
+		if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess)
+			break;
+		cudaEventCreate(&e0);
+		cudaEventCreate(&e1);
+		cudaEventRecord(e0, h->stream);
+		// CSR arrays, zero-padded so that whole windows (+ extension) can be loaded unconditionally
+		const int64_t tiles = (nnz + h->tile_nnz - 1) / h->tile_nnz;
+		const int64_t padded = (tiles > 0 ? tiles : 1) * h->tile_nnz + h->ext + 64;
+		if (cudaMalloc(&h->d_row_ptr, (m + 1) * sizeof(int32_t)) != cudaSuccess) break;
+		if (cudaMalloc(&h->d_col, padded * sizeof(int32_t)) != cudaSuccess) break;
+		if (cudaMalloc(&h->d_val, padded * sizeof(double)) != cudaSuccess) break;
+		cudaMemsetAsync(h->d_col + nnz, 0, (padded - nnz) * sizeof(int32_t), h->stream);
+		cudaMemsetAsync(h->d_val + nnz, 0, (padded - nnz) * sizeof(double), h->stream);
+		if (kind == cudaMemcpyHostToDevice) {
+			if (cudaMemcpyAsync(h->d_row_ptr, row_ptr, (m + 1) * sizeof(int32_t), kind, h->stream) != cudaSuccess) break;
+			if (m >= 0 && row_ptr[0] != 0) {
+				snprintf(g_b200_err, sizeof(g_b200_err), "row_ptr[0] must be 0 for host input");
+				goto fail;
+			}
+		} else {
+			rebase_row_ptr_kernel<<<(unsigned) ((m + 1 + 255) / 256), 256, 0, h->stream>>>(row_ptr, h->d_row_ptr, m + 1);
+		}
+		if (nnz > 0) {
+			if (cudaMemcpyAsync(h->d_col, col_ind, nnz * sizeof(int32_t), kind, h->stream) != cudaSuccess) break;
+			if (cudaMemcpyAsync(h->d_val, values, nnz * sizeof(double), kind, h->stream) != cudaSuccess) break;
+		}
+		if (cudaStreamSynchronize(h->stream) != cudaSuccess) break;
+		int64_t norm_slots;
+		if (h->format == B200SPMV_CSR_ADAPTIVE) {
+			if (csr_plan_tiles(h)) goto fail;
+			norm_slots = h->ntiles + h->nsplit;
+		} else {
+			if (sell_convert(h)) goto fail;
+			// the CSR copies of col / val are not needed any more
+			cudaFree(h->d_col);
+			cudaFree(h->d_val);
+			h->d_col = nullptr;
+			h->d_val = nullptr;
+			norm_slots = (m + SELL_ROWS_PER_CTA - 1) / SELL_ROWS_PER_CTA;
+		}
+		h->norm_slots = norm_slots > 0 ? norm_slots : 1;
+		if (cudaMalloc(&h->d_norm_partial, h->norm_slots * sizeof(double)) != cudaSuccess) break;
+		cudaEventRecord(e1, h->stream);
+		if (cudaStreamSynchronize(h->stream) != cudaSuccess) break;
+		cudaEventElapsedTime(&h->convert_ms, e0, e1);
+		rc = 0;
+	} while (0);
+	if (rc) {
+		snprintf(g_b200_err, sizeof(g_b200_err), "b200spmv_create: CUDA failure: %s", cudaGetErrorString(cudaGetLastError()));
+fail:
+		if (e0) cudaEventDestroy(e0);
+		if (e1) cudaEventDestroy(e1);
+		free_handle(h);
+		return 1;
+	}
+	cudaEventDestroy(e0);
+	cudaEventDestroy(e1);
+	*out = h;
+	return 0;
+}
+
+extern "C" int b200spmv_create(b200spmv_t ** out, const int32_t * row_ptr, const int32_t * col_ind, const double * values,
+                               int64_t m, int64_t n, int64_t nnz, const b200spmv_opts * opts)
+{
+	return create_common(out, row_ptr, col_ind, values, m, n, nnz, opts, cudaMemcpyHostToDevice);
+}
+
+extern "C" int b200spmv_create_device(b200spmv_t ** out, const int32_t * d_row_ptr, const int32_t * d_col_ind, const double * d_values,
+                                      int64_t m, int64_t n, int64_t nnz, const b200spmv_opts * opts)
+{
+	return create_common(out, d_row_ptr, d_col_ind, d_values, m, n, nnz, opts, cudaMemcpyDeviceToDevice);
+}
+
+extern "C" void b200spmv_destroy(b200spmv_t * h)
+{
+	if (h) {
+		cudaSetDevice(h->device);
+		free_handle(h);
+	}
+}
+
+extern "C" int32_t b200spmv_launches_per_spmv(const b200spmv_t * h)
+{
+	if (!h)
+		return 0;
+	return (h->format == B200SPMV_CSR_ADAPTIVE && h->nsplit > 0) ? 2 : 1;
+}
+
+extern "C" int b200spmv_spmv_device_ex(b200spmv_t * h, const double * dx, double * dy, void * stream, const b200spmv_launch * launch)
+{
+	if (!h || !dx || !dy)
+		B200_FAIL("NULL argument");
+	cudaStream_t st = stream ? (cudaStream_t) stream : h->stream;
+	if (h->format == B200SPMV_CSR_ADAPTIVE)
+		return launch_csr_spmv(h, dx, dy, st, launch);
+	return launch_sell_spmv(h, dx, dy, st, launch);
+}
+
+extern "C" int b200spmv_spmv_device(b200spmv_t * h, const double * dx, double * dy, void * stream)
+{
+	return b200spmv_spmv_device_ex(h, dx, dy, stream, nullptr);
+}
+
+extern "C" int b200spmv_spmv_host_ex(b200spmv_t * h, const double * x, double * y, int32_t flags)
+{
+	if (!h || !x || !y)
+		B200_FAIL("NULL argument");
+	CU(cudaSetDevice(h->device));
+	if (!h->d_x) {
+		CU(cudaMalloc(&h->d_x, (h->n > 0 ? h->n : 1) * sizeof(double)));
+		CU(cudaMalloc(&h->d_y, (h->m > 0 ? h->m : 1) * sizeof(double)));
+		flags &= ~B200SPMV_SKIP_X_UPLOAD;
+	}
+	if (!(flags & B200SPMV_SKIP_X_UPLOAD) && h->n > 0)
+		CU(cudaMemcpyAsync(h->d_x, x, h->n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+	if (b200spmv_spmv_device_ex(h, h->d_x, h->d_y, h->stream, nullptr))
+		return 1;
+	if (!(flags & B200SPMV_SKIP_Y_DOWNLOAD) && h->m > 0)
+		CU(cudaMemcpyAsync(y, h->d_y, h->m * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+	CU(cudaStreamSynchronize(h->stream));
+	return 0;
+}
+
+extern "C" int b200spmv_spmv_host(b200spmv_t * h, const double * x, double * y)
+{
+	return b200spmv_spmv_host_ex(h, x, y, 0);
+}

@@ -1,0 +1,185 @@
+// common.cuh -- shared declarations of libb200spmv: error plumbing, sm_100a load helpers, handle.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include "../../include/b200spmv.h"
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "libb200spmv is written for sm_100a (B200) only"
+#endif
+
+extern thread_local char g_b200_err[512];
+
+#define B200_FAIL(...)                                                    \
+	do {                                                              \
+		snprintf(g_b200_err, sizeof(g_b200_err), __VA_ARGS__);    \
+		return 1;                                                 \
+	} while (0)
+
+#define CU(call)                                                                                            \
+	do {                                                                                                \
+		cudaError_t e_ = (call);                                                                    \
+		if (e_ != cudaSuccess)                                                                      \
+			B200_FAIL("%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_));     \
+	} while (0)
+
+#define CU_LAUNCH() CU(cudaPeekAtLastError())
+
+// ---------------------------------------------------------------------------------------------
+// Tunables of the nnz-tiled CSR kernel
+// ---------------------------------------------------------------------------------------------
+constexpr int CSR_THREADS = 256;          // threads per tile CTA
+constexpr int SELL_THREADS = 128;         // threads per SELL CTA, two rows per thread
+constexpr int SELL_ROWS_PER_CTA = 2 * SELL_THREADS;
+
+// ---------------------------------------------------------------------------------------------
+// Blackwell load helpers.
+//  * matrix streams (values / col_ind): read exactly once -> 256-bit non-coherent loads that do
+//    not allocate in L1 and are marked evict-first in L2 (SASS: LDG.E.NA.EFL2.256.CONSTANT), so
+//    they do not push x out of the 126 MB L2.
+//  * x gathers: L1-allocating loads with an L2 evict_last cache hint (LDG.E.EL.64.CONSTANT).
+// ---------------------------------------------------------------------------------------------
+struct i32x8 { int v[8]; };
+struct f64x4 { double v[4]; };
+
+__device__ __forceinline__ i32x8 ld_stream_i32x8(const int32_t * p)
+{
+	i32x8 r;
+	asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+	             : "=r"(r.v[0]), "=r"(r.v[1]), "=r"(r.v[2]), "=r"(r.v[3]), "=r"(r.v[4]), "=r"(r.v[5]), "=r"(r.v[6]), "=r"(r.v[7])
+	             : "l"(p));
+	return r;
+}
+
+__device__ __forceinline__ f64x4 ld_stream_f64x4(const double * p)
+{
+	f64x4 r;
+	asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v4.b64 {%0,%1,%2,%3}, [%4];"
+	             : "=d"(r.v[0]), "=d"(r.v[1]), "=d"(r.v[2]), "=d"(r.v[3])
+	             : "l"(p));
+	return r;
+}
+
+__device__ __forceinline__ double2 ld_stream_f64x2(const double * p)
+{
+	double2 r;
+	asm volatile("ld.global.nc.L1::no_allocate.v2.f64 {%0,%1}, [%2];" : "=d"(r.x), "=d"(r.y) : "l"(p));
+	return r;
+}
+
+__device__ __forceinline__ int2 ld_stream_i32x2(const int32_t * p)
+{
+	int2 r;
+	asm volatile("ld.global.nc.L1::no_allocate.v2.s32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p));
+	return r;
+}
+
+__device__ __forceinline__ double ld_stream_f64(const double * p)
+{
+	double r;
+	asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];" : "=d"(r) : "l"(p));
+	return r;
+}
+
+__device__ __forceinline__ int ld_stream_i32(const int32_t * p)
+{
+	int r;
+	asm volatile("ld.global.nc.L1::no_allocate.s32 %0, [%1];" : "=r"(r) : "l"(p));
+	return r;
+}
+
+__device__ __forceinline__ uint64_t make_policy_evict_last()
+{
+	uint64_t pol;
+	asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+	return pol;
+}
+
+template <bool HINT>
+__device__ __forceinline__ double ld_x(const double * p, uint64_t pol)
+{
+	double r;
+	if (HINT)
+		asm volatile("ld.global.nc.L1::evict_last.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(r) : "l"(p), "l"(pol));
+	else
+		asm volatile("ld.global.nc.f64 %0, [%1];" : "=d"(r) : "l"(p));
+	return r;
+}
+
+// y destinations of one product: the caller's y plus optional peer buffers, optional scale / norm.
+struct YOut {
+	double * y;
+	double * peer[8];
+	int n_peer;
+	const double * scale;     // device scalar or nullptr
+	double * norm_partial;    // one slot per CTA or nullptr
+};
+
+__device__ __forceinline__ void y_store(const YOut & o, int64_t row, double v)
+{
+	o.y[row] = v;
+	for (int d = 0; d < o.n_peer; d++)
+		o.peer[d][row] = v;
+}
+
+__device__ __forceinline__ double warp_sum(double v)
+{
+	#pragma unroll
+	for (int o = 16; o > 0; o >>= 1)
+		v += __shfl_xor_sync(0xffffffffu, v, o);
+	return v;
+}
+
+// ---------------------------------------------------------------------------------------------
+// The handle
+// ---------------------------------------------------------------------------------------------
+struct b200spmv {
+	int format, device;
+	int64_t m, n, nnz;
+	int x_hint;
+	cudaStream_t stream;
+	float convert_ms;
+
+	// CSR (device).  col / val are padded with zeros up to a multiple of the tile size + ext.
+	int32_t * d_row_ptr;
+	int32_t * d_col;
+	double * d_val;
+
+	// CSR tile plan
+	int npt;                  // nnz per thread
+	int tile_nnz;             // CSR_THREADS * npt
+	int ext;                  // tail-extension capacity
+	int64_t ntiles;
+	int32_t * d_tile_row;     // [ntiles + 1]
+	int64_t nsplit;
+	int32_t * d_split_row;    // [nsplit]
+	int32_t * d_split_tile;   // [nsplit]
+	double * d_tile_head;     // [ntiles] partial of a split row entering the tile
+	double * d_tile_tail;     // [ntiles] partial of a split row leaving the tile
+
+	// SELL-C-sigma (device)
+	int C;
+	int64_t sigma, nslices, padded;
+	int32_t * d_row_order;
+	int32_t * d_slice_width;
+	int64_t * d_slice_ptr;
+	int32_t * d_scol;
+	double * d_sval;
+
+	// staging for the host-vector entry point, norm partials
+	double * d_x;
+	double * d_y;
+	double * d_norm_partial;
+	int64_t norm_slots;
+};
+
+// convert.cu
+int csr_plan_tiles(b200spmv * h);
+int sell_convert(b200spmv * h);
+int device_exclusive_scan_i64(int64_t * d_data, int64_t n, cudaStream_t st);
+// kernels
+int launch_csr_spmv(b200spmv * h, const double * dx, double * dy, cudaStream_t st, const b200spmv_launch * l);
+int launch_sell_spmv(b200spmv * h, const double * dx, double * dy, cudaStream_t st, const b200spmv_launch * l);
+int launch_norm_reduce(b200spmv * h, int64_t slots, double * d_out, cudaStream_t st);

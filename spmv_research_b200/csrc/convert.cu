@@ -1,0 +1,382 @@
+// convert.cu -- on-GPU format construction: CSR tile plan, SELL-C-sigma conversion, scans.
+//
+// Integer outputs are bit-exact with the reference:
+//   SELL-C-sigma : K/sell-C-s/RISC-V/radix_sort.c:36-122 (stable descending sort of row lengths
+//                  inside sigma windows), sellcs_format.c:137-200 (slice widths / pointers,
+//                  column-major padded slices, zero padding).
+#include "common.cuh"
+
+// ---------------------------------------------------------------------------------------------
+// exclusive scan of int64, in place (three-phase, recursive over block sums)
+// ---------------------------------------------------------------------------------------------
+constexpr int SCAN_THREADS = 256;
+constexpr int SCAN_ITEMS = 8;
+constexpr int SCAN_BLOCK = SCAN_THREADS * SCAN_ITEMS;
+
+__global__ void scan_block_kernel(int64_t * data, int64_t n, int64_t * block_sums)
+{
+	__shared__ int64_t s_warp[SCAN_THREADS / 32];
+	const int64_t base = (int64_t) blockIdx.x * SCAN_BLOCK + (int64_t) threadIdx.x * SCAN_ITEMS;
+	int64_t v[SCAN_ITEMS], tsum = 0;
+	#pragma unroll
+	for (int i = 0; i < SCAN_ITEMS; i++) {
+		v[i] = (base + i < n) ? data[base + i] : 0;
+		tsum += v[i];
+	}
+	// inclusive scan of thread sums across the warp, then across warps
+	int64_t inc = tsum;
+	const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+	#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) {
+		int64_t t = __shfl_up_sync(0xffffffffu, inc, o);
+		if (lane >= o)
+			inc += t;
+	}
+	if (lane == 31)
+		s_warp[wid] = inc;
+	__syncthreads();
+	int64_t woff = 0;
+	for (int w = 0; w < wid; w++)
+		woff += s_warp[w];
+	int64_t run = woff + inc - tsum;
+	#pragma unroll
+	for (int i = 0; i < SCAN_ITEMS; i++) {
+		if (base + i < n)
+			data[base + i] = run;
+		run += v[i];
+	}
+	if (threadIdx.x == SCAN_THREADS - 1 && block_sums)
+		block_sums[blockIdx.x] = run;
+}
+
+__global__ void scan_add_kernel(int64_t * data, int64_t n, const int64_t * block_offsets)
+{
+	const int64_t off = block_offsets[blockIdx.x];
+	const int64_t base = (int64_t) blockIdx.x * SCAN_BLOCK;
+	for (int i = threadIdx.x; i < SCAN_BLOCK; i += SCAN_THREADS)
+		if (base + i < n)
+			data[base + i] += off;
+}
+
+int device_exclusive_scan_i64(int64_t * d_data, int64_t n, cudaStream_t st)
+{
+	if (n <= 0)
+		return 0;
+	const int64_t blocks = (n + SCAN_BLOCK - 1) / SCAN_BLOCK;
+	if (blocks == 1) {
+		scan_block_kernel<<<1, SCAN_THREADS, 0, st>>>(d_data, n, nullptr);
+		CU_LAUNCH();
+		return 0;
+	}
+	int64_t * d_sums;
+	CU(cudaMalloc(&d_sums, blocks * sizeof(int64_t)));
+	scan_block_kernel<<<(unsigned) blocks, SCAN_THREADS, 0, st>>>(d_data, n, d_sums);
+	CU_LAUNCH();
+	int rc = device_exclusive_scan_i64(d_sums, blocks, st);
+	if (!rc) {
+		scan_add_kernel<<<(unsigned) blocks, SCAN_THREADS, 0, st>>>(d_data, n, d_sums);
+		if (cudaPeekAtLastError() != cudaSuccess)
+			rc = 1;
+	}
+	cudaStreamSynchronize(st);
+	cudaFree(d_sums);
+	if (rc)
+		B200_FAIL("scan failed: %s", cudaGetErrorString(cudaGetLastError()));
+	return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// CSR tile plan
+// ---------------------------------------------------------------------------------------------
+// tile_info[t] = { first row whose start offset is >= t*T  (bit 31: a split row enters the tile),
+//                  row_ptr[that row] };  tile_info[ntiles] = { m, nnz }.
+__device__ __forceinline__ int64_t lower_bound_rows(const int32_t * row_ptr, int64_t m, int64_t target)
+{
+	int64_t lo = 0, hi = m;          // first i in [0, m] with row_ptr[i] >= target (row_ptr[m] = nnz)
+	while (lo < hi) {
+		const int64_t mid = (lo + hi) >> 1;
+		if (row_ptr[mid] < target)
+			lo = mid + 1;
+		else
+			hi = mid;
+	}
+	return lo;
+}
+
+__global__ void tile_info_kernel(const int32_t * __restrict__ row_ptr, int64_t m, int64_t nnz, int64_t ntiles, int T, int ext,
+                                 int2 * __restrict__ tile_info, int64_t * __restrict__ split_flag)
+{
+	const int64_t t = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (t > ntiles)
+		return;
+	if (t == ntiles) {
+		tile_info[t] = make_int2((int) m, (int) nnz);
+		return;
+	}
+	const int64_t base = t * (int64_t) T;
+	const int64_t R0 = (t == 0) ? 0 : lower_bound_rows(row_ptr, m, base);
+	const int64_t start0 = row_ptr[R0];
+	int flag = 0;
+	if (R0 > 0 && start0 > base) {
+		// row R0-1 started before this window and reaches into it: split iff it leaves its
+		// owner's window by more than ext
+		const int64_t start_h = row_ptr[R0 - 1];
+		const int64_t k = start_h / T;
+		if (start0 - (k + 1) * (int64_t) T > ext)
+			flag = 1;
+	}
+	tile_info[t] = make_int2((int) R0 | (flag ? (int) 0x80000000 : 0), (int) start0);
+	// does this tile OWN a split row?  (its last owned row leaves the window by more than ext)
+	const int64_t R1 = (t + 1 == ntiles) ? m : lower_bound_rows(row_ptr, m, base + T);
+	const int64_t end_own = row_ptr[R1];
+	split_flag[t] = (R1 > R0 && end_own - (base + T) > ext) ? 1 : 0;
+}
+
+__global__ void split_compact_kernel(const int2 * __restrict__ tile_info, const int64_t * __restrict__ split_pos, int64_t ntiles,
+                                     int64_t nsplit, int32_t * __restrict__ split_row, int32_t * __restrict__ split_tile)
+{
+	const int64_t t = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= ntiles)
+		return;
+	const int64_t pos = split_pos[t];
+	const int64_t nxt = (t + 1 < ntiles) ? split_pos[t + 1] : nsplit;
+	if (nxt > pos) {
+		split_row[pos] = (tile_info[t + 1].x & 0x7fffffff) - 1;
+		split_tile[pos] = (int32_t) t;
+	}
+}
+
+int csr_plan_tiles(b200spmv * h)
+{
+	const int T = h->tile_nnz;
+	h->ntiles = (h->nnz + T - 1) / T;
+	if (h->ntiles < 1)
+		h->ntiles = 1;                       // an all-empty matrix still needs its rows zeroed
+	if (h->ntiles >= 0x7fffffffLL)
+		B200_FAIL("too many tiles");
+	CU(cudaMalloc(&h->d_tile_row, (h->ntiles + 1) * sizeof(int2)));
+	CU(cudaMalloc(&h->d_tile_head, h->ntiles * sizeof(double)));
+	CU(cudaMalloc(&h->d_tile_tail, h->ntiles * sizeof(double)));
+	CU(cudaMemsetAsync(h->d_tile_head, 0, h->ntiles * sizeof(double), h->stream));
+	CU(cudaMemsetAsync(h->d_tile_tail, 0, h->ntiles * sizeof(double), h->stream));
+	int64_t * d_flag;
+	CU(cudaMalloc(&d_flag, h->ntiles * sizeof(int64_t)));
+	const unsigned blocks = (unsigned) ((h->ntiles + 1 + 255) / 256);
+	tile_info_kernel<<<blocks, 256, 0, h->stream>>>(h->d_row_ptr, h->m, h->nnz, h->ntiles, T, h->ext,
+	                                                reinterpret_cast<int2 *>(h->d_tile_row), d_flag);
+	CU_LAUNCH();
+	// number of split rows = last flag + last exclusive-scan value
+	int64_t last_flag = 0, last_pos = 0;
+	CU(cudaMemcpyAsync(&last_flag, d_flag + h->ntiles - 1, sizeof(int64_t), cudaMemcpyDeviceToHost, h->stream));
+	CU(cudaStreamSynchronize(h->stream));
+	if (device_exclusive_scan_i64(d_flag, h->ntiles, h->stream)) {
+		cudaFree(d_flag);
+		return 1;
+	}
+	CU(cudaMemcpyAsync(&last_pos, d_flag + h->ntiles - 1, sizeof(int64_t), cudaMemcpyDeviceToHost, h->stream));
+	CU(cudaStreamSynchronize(h->stream));
+	h->nsplit = last_flag + last_pos;
+	if (h->nsplit > 0) {
+		CU(cudaMalloc(&h->d_split_row, h->nsplit * sizeof(int32_t)));
+		CU(cudaMalloc(&h->d_split_tile, h->nsplit * sizeof(int32_t)));
+		split_compact_kernel<<<(unsigned) ((h->ntiles + 255) / 256), 256, 0, h->stream>>>(
+			reinterpret_cast<const int2 *>(h->d_tile_row), d_flag, h->ntiles, h->nsplit, h->d_split_row, h->d_split_tile);
+		CU_LAUNCH();
+	}
+	CU(cudaStreamSynchronize(h->stream));
+	CU(cudaFree(d_flag));
+	return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// SELL-C-sigma conversion
+// ---------------------------------------------------------------------------------------------
+// The reference's LSD radix passes (radix_sort.c:36-101) are a stable sort by descending row
+// length inside each sigma window.  Sorting the unique 64-bit key ((2^32-1 - len) << 32 | row)
+// ascending yields exactly that order with any comparison network, so a bitonic network is used:
+// windows are padded to a power of two with all-ones keys, which sort to the end.
+constexpr int BITONIC_BLOCK = 4096;                  // keys per CTA in the shared-memory phases
+constexpr int BITONIC_THREADS = 512;
+
+__global__ void sell_keys_kernel(const int32_t * __restrict__ row_ptr, int64_t m, int64_t sigma, int64_t sigma_p, int64_t nslots,
+                                 uint64_t * __restrict__ keys)
+{
+	const int64_t slot = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (slot >= nslots)
+		return;
+	const int64_t w = slot / sigma_p, r = slot % sigma_p;
+	const int64_t row = w * sigma + r;
+	uint64_t key = ~0ULL;
+	if (r < sigma && row < m) {
+		const uint32_t len = (uint32_t) (row_ptr[row + 1] - row_ptr[row]);
+		key = ((uint64_t) (0xFFFFFFFFu - len) << 32) | (uint64_t) (uint32_t) row;
+	}
+	keys[slot] = key;
+}
+
+__device__ __forceinline__ void cmpswap(uint64_t & a, uint64_t & b, bool ascending)
+{
+	if ((a > b) == ascending) {
+		const uint64_t t = a;
+		a = b;
+		b = t;
+	}
+}
+
+// Shared-memory phases over blocks of BITONIC_BLOCK keys.  k_first == 0: all stages k = 2 ..
+// min(BITONIC_BLOCK, sigma_p).  Otherwise: the tail j = BITONIC_BLOCK/2 .. 1 of stage k_first.
+__global__ void __launch_bounds__(BITONIC_THREADS)
+bitonic_smem_kernel(uint64_t * __restrict__ keys, int64_t sigma_p, int64_t k_first)
+{
+	__shared__ uint64_t s[BITONIC_BLOCK];
+	const int64_t base = (int64_t) blockIdx.x * BITONIC_BLOCK;
+	for (int i = threadIdx.x; i < BITONIC_BLOCK; i += BITONIC_THREADS)
+		s[i] = keys[base + i];
+	__syncthreads();
+	const int64_t k_lo = k_first ? k_first : 2;
+	const int64_t k_hi = k_first ? k_first : (sigma_p < BITONIC_BLOCK ? sigma_p : BITONIC_BLOCK);
+	for (int64_t k = k_lo; k <= k_hi; k <<= 1) {
+		int j = (int) ((k >> 1) < BITONIC_BLOCK / 2 ? (k >> 1) : BITONIC_BLOCK / 2);
+		for (; j > 0; j >>= 1) {
+			for (int t = threadIdx.x; t < BITONIC_BLOCK / 2; t += BITONIC_THREADS) {
+				const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));        // index with bit j clear
+				const int64_t li = (base + i) & (sigma_p - 1);
+				cmpswap(s[i], s[i | j], (li & k) == 0);
+			}
+			__syncthreads();
+		}
+	}
+	for (int i = threadIdx.x; i < BITONIC_BLOCK; i += BITONIC_THREADS)
+		keys[base + i] = s[i];
+}
+
+__global__ void bitonic_global_kernel(uint64_t * __restrict__ keys, int64_t npairs, int64_t sigma_p, int64_t j, int64_t k)
+{
+	const int64_t t = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= npairs)
+		return;
+	const int64_t i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+	const int64_t li = i & (sigma_p - 1);
+	uint64_t a = keys[i], b = keys[i | j];
+	if ((a > b) == ((li & k) == 0)) {
+		keys[i] = b;
+		keys[i | j] = a;
+	}
+}
+
+__global__ void sell_order_kernel(const uint64_t * __restrict__ keys, int64_t m, int64_t sigma, int64_t sigma_p, int C,
+                                  int32_t * __restrict__ row_order, int32_t * __restrict__ slice_width, int64_t * __restrict__ slice_size)
+{
+	const int64_t pos = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (pos >= m)
+		return;
+	const int64_t w = pos / sigma, r = pos % sigma;
+	const uint64_t key = keys[w * sigma_p + r];
+	row_order[pos] = (int32_t) (uint32_t) (key & 0xFFFFFFFFu);
+	if (pos % C == 0) {
+		const uint32_t len = 0xFFFFFFFFu - (uint32_t) (key >> 32);
+		slice_width[pos / C] = (int32_t) len;
+		slice_size[pos / C] = (int64_t) len * C;
+	}
+}
+
+// sorted row r, k-th entry -> slice_ptr[r / C] + r % C + k * C   (sellcs_format.c:173-186)
+__global__ void sell_scatter_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict__ col, const double * __restrict__ val,
+                                    const int32_t * __restrict__ row_order, const int64_t * __restrict__ slice_ptr, int64_t m, int C,
+                                    int32_t * __restrict__ scol, double * __restrict__ sval)
+{
+	const int64_t pos = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	const bool valid = pos < m;
+	int64_t src = 0, dst = 0;
+	int len = 0;
+	if (valid) {
+		const int orig = row_order[pos];
+		src = row_ptr[orig];
+		len = row_ptr[orig + 1] - row_ptr[orig];
+		dst = slice_ptr[pos / C] + (pos % C);
+	}
+	const bool longrow = len >= 64;
+	if (!longrow) {
+		for (int k = 0; k < len; k++) {
+			scol[dst + (int64_t) k * C] = col[src + k];
+			sval[dst + (int64_t) k * C] = val[src + k];
+		}
+	}
+	// long rows: the whole warp copies them together (coalesced reads of the CSR row)
+	unsigned mask = __ballot_sync(0xffffffffu, longrow);
+	const int lane = threadIdx.x & 31;
+	while (mask) {
+		const int l = __ffs(mask) - 1;
+		mask &= mask - 1;
+		const int64_t s2 = __shfl_sync(0xffffffffu, src, l);
+		const int64_t d2 = __shfl_sync(0xffffffffu, dst, l);
+		const int n2 = __shfl_sync(0xffffffffu, len, l);
+		for (int k = lane; k < n2; k += 32) {
+			scol[d2 + (int64_t) k * C] = col[s2 + k];
+			sval[d2 + (int64_t) k * C] = val[s2 + k];
+		}
+	}
+}
+
+int sell_convert(b200spmv * h)
+{
+	const int64_t m = h->m;
+	const int C = h->C;
+	const int64_t sigma = h->sigma;
+	cudaStream_t st = h->stream;
+	h->nslices = (m + C - 1) / C;
+	CU(cudaMalloc(&h->d_row_order, (m > 0 ? m : 1) * sizeof(int32_t)));
+	CU(cudaMalloc(&h->d_slice_width, (h->nslices > 0 ? h->nslices : 1) * sizeof(int32_t)));
+	CU(cudaMalloc(&h->d_slice_ptr, (h->nslices + 1) * sizeof(int64_t)));
+	CU(cudaMemsetAsync(h->d_slice_ptr, 0, (h->nslices + 1) * sizeof(int64_t), st));
+	if (m > 0) {
+		int64_t win = sigma < m ? sigma : m;
+		int64_t sigma_p = 1;
+		while (sigma_p < win)
+			sigma_p <<= 1;
+		const int64_t nwin = (m + sigma - 1) / sigma;
+		int64_t nslots = nwin * sigma_p;
+		// the shared-memory phases work on whole blocks: round the key array up with sentinels
+		const int64_t nslots_alloc = (nslots + BITONIC_BLOCK - 1) / BITONIC_BLOCK * BITONIC_BLOCK;
+		uint64_t * d_keys;
+		CU(cudaMalloc(&d_keys, nslots_alloc * sizeof(uint64_t)));
+		CU(cudaMemsetAsync(d_keys, 0xFF, nslots_alloc * sizeof(uint64_t), st));
+		sell_keys_kernel<<<(unsigned) ((nslots + 255) / 256), 256, 0, st>>>(h->d_row_ptr, m, sigma, sigma_p, nslots, d_keys);
+		CU_LAUNCH();
+		const unsigned nblk = (unsigned) (nslots_alloc / BITONIC_BLOCK);
+		if (sigma_p > 1) {
+			bitonic_smem_kernel<<<nblk, BITONIC_THREADS, 0, st>>>(d_keys, sigma_p, 0);
+			CU_LAUNCH();
+			for (int64_t k = 2 * (int64_t) BITONIC_BLOCK; k <= sigma_p; k <<= 1) {
+				const int64_t npairs = nslots_alloc / 2;
+				for (int64_t j = k >> 1; j >= BITONIC_BLOCK; j >>= 1) {
+					bitonic_global_kernel<<<(unsigned) ((npairs + 255) / 256), 256, 0, st>>>(d_keys, npairs, sigma_p, j, k);
+					CU_LAUNCH();
+				}
+				bitonic_smem_kernel<<<nblk, BITONIC_THREADS, 0, st>>>(d_keys, sigma_p, k);
+				CU_LAUNCH();
+			}
+		}
+		sell_order_kernel<<<(unsigned) ((m + 255) / 256), 256, 0, st>>>(d_keys, m, sigma, sigma_p, C, h->d_row_order, h->d_slice_width,
+		                                                                h->d_slice_ptr);
+		CU_LAUNCH();
+		CU(cudaStreamSynchronize(st));
+		CU(cudaFree(d_keys));
+		if (device_exclusive_scan_i64(h->d_slice_ptr, h->nslices + 1, st))
+			return 1;
+	}
+	CU(cudaMemcpyAsync(&h->padded, h->d_slice_ptr + h->nslices, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+	CU(cudaStreamSynchronize(st));
+	const int64_t alloc = h->padded + 8;
+	CU(cudaMalloc(&h->d_scol, alloc * sizeof(int32_t)));
+	CU(cudaMalloc(&h->d_sval, alloc * sizeof(double)));
+	CU(cudaMemsetAsync(h->d_scol, 0, alloc * sizeof(int32_t), st));
+	CU(cudaMemsetAsync(h->d_sval, 0, alloc * sizeof(double), st));
+	if (m > 0) {
+		sell_scatter_kernel<<<(unsigned) ((m + 255) / 256), 256, 0, st>>>(h->d_row_ptr, h->d_col, h->d_val, h->d_row_order, h->d_slice_ptr,
+		                                                                  m, C, h->d_scol, h->d_sval);
+		CU_LAUNCH();
+	}
+	CU(cudaStreamSynchronize(st));
+	return 0;
+}

@@ -1,0 +1,284 @@
+// csr_kernel.cu -- the adaptive, nnz-tiled fp64 CSR SpMV kernel for sm_100a.
+//
+// Computes what the reference's subkernel_csr_scalar computes (K/csr.cpp:334-350:
+// y[i] = sum_j a[j] * x[ja[j]], every row written, empty rows -> 0), laid out for B200:
+//
+//  * the nnz stream is cut into fixed windows ("tiles") of T = 256 * NPT non-zeros, one CTA per
+//    tile, so every values / col_ind load is a 32-byte-aligned, fully coalesced 256-bit streaming
+//    load (LDG.E.NA.EFL2.256) regardless of the row-length distribution -- the nnz-balanced
+//    decomposition of merge-path (K/merge.cpp:256-318) with the row search done once at convert
+//    time (tile_info);
+//  * all stream loads of a tile are issued before the first x gather (8-32 independent 32-byte
+//    loads per thread), products go to shared memory through a conflict-free XOR swizzle;
+//  * a row belongs to the tile in which it STARTS.  The owner finishes the row even when it
+//    leaves the window, by loading up to EXT further non-zeros ("tail extension"), so ordinary
+//    matrices need one launch and no carry fix-up.  Only rows sticking out by more than EXT
+//    ("split" rows: the generator's giant skew rows) are completed by csr_fixup_kernel from
+//    per-tile head/tail partials in a fixed order -- deterministic, no atomics
+//    (cf. cuda_csr_const_nnz_per_thread.cu:578-659,864 which uses atomicAdd + memset);
+//  * per tile the row reduction is binned by the number of rows it owns: thread per row (short
+//    rows, sequential ascending-j sum = the oracle's order), 2..32 lanes per row with shuffle
+//    reduction (long rows), whole CTA for split-row partials.
+#include "common.cuh"
+
+__device__ __forceinline__ int swz(int j) { return j ^ (((j >> 4) & 3) << 1); }
+
+__device__ __forceinline__ double block_sum_range(const double * s_prod, int a, int b, double * s_red)
+{
+	double acc = 0.0;
+	for (int j = a + (int) threadIdx.x; j < b; j += CSR_THREADS)
+		acc += s_prod[swz(j)];
+	acc = warp_sum(acc);
+	__syncthreads();
+	if ((threadIdx.x & 31) == 0)
+		s_red[threadIdx.x >> 5] = acc;
+	__syncthreads();
+	double tot = 0.0;
+	#pragma unroll
+	for (int w = 0; w < CSR_THREADS / 32; w++)
+		tot += s_red[w];
+	return tot;
+}
+
+template <int NPT, bool HINT>
+__global__ void __launch_bounds__(CSR_THREADS, (NPT <= 8) ? 4 : ((NPT <= 16) ? 3 : 2))
+csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict__ col, const double * __restrict__ val,
+                const int2 * __restrict__ tile_info, const double * __restrict__ x,
+                double * __restrict__ tile_head, double * __restrict__ tile_tail,
+                int64_t nnz, int ext_cap, YOut out)
+{
+	constexpr int T = CSR_THREADS * NPT;
+	constexpr int CHUNKS = NPT / 8;
+	extern __shared__ __align__(16) double s_prod[];      // T + ext_cap products
+	__shared__ double s_red[CSR_THREADS / 32];
+
+	const int tid = threadIdx.x;
+	const int64_t tile = blockIdx.x;
+	const int64_t base = tile * (int64_t) T;
+	const uint64_t pol = make_policy_evict_last();
+
+	// 1. all streaming loads of the window, issued back to back
+	i32x8 c[CHUNKS];
+	f64x4 v0[CHUNKS], v1[CHUNKS];
+	#pragma unroll
+	for (int k = 0; k < CHUNKS; k++) {
+		const int64_t idx = base + k * (CSR_THREADS * 8) + tid * 8;
+		c[k] = ld_stream_i32x8(col + idx);
+		v0[k] = ld_stream_f64x4(val + idx);
+		v1[k] = ld_stream_f64x4(val + idx + 4);
+	}
+
+	// 2. tile bookkeeping (independent of the stream loads)
+	const int2 ti0 = tile_info[tile];
+	const int2 ti1 = tile_info[tile + 1];
+	const int R0 = ti0.x & 0x7fffffff;
+	const bool head_split = (ti0.x < 0);
+	const int R1 = ti1.x & 0x7fffffff;
+	const int64_t start0 = ti0.y;                       // row_ptr[R0]
+	const int64_t end_own = ti1.y;                      // row_ptr[R1]
+	const int nrows = R1 - R0;
+	const int64_t lim = (base + T < nnz) ? base + T : nnz;
+	const int64_t over = end_own - (base + T);          // > 0: the last owned row leaves the window
+	const bool tail_split = (nrows > 0) && (over > ext_cap);
+	const double scale = out.scale ? *out.scale : 1.0;
+
+	// 3. gathers and products -> shared memory (swizzled 16-byte units, conflict-free STS.128)
+	#pragma unroll
+	for (int k = 0; k < CHUNKS; k++) {
+		double p[8];
+		#pragma unroll
+		for (int e = 0; e < 4; e++) {
+			p[e] = v0[k].v[e] * ld_x<HINT>(x + c[k].v[e], pol);
+			p[4 + e] = v1[k].v[e] * ld_x<HINT>(x + c[k].v[4 + e], pol);
+		}
+		const int j0 = k * (CSR_THREADS * 8) + tid * 8;
+		const int s = (tid >> 1) & 3;
+		#pragma unroll
+		for (int u = 0; u < 4; u++)
+			*reinterpret_cast<double2 *>(&s_prod[j0 + 2 * (u ^ s)]) = make_double2(p[2 * u], p[2 * u + 1]);
+	}
+
+	// 4. tail extension: finish the last owned row past the window end
+	if (nrows > 0 && over > 0 && !tail_split) {
+		for (int j = tid; j < (int) over; j += CSR_THREADS) {
+			const int64_t idx = base + T + j;
+			s_prod[swz(T + j)] = ld_stream_f64(val + idx) * ld_x<HINT>(x + ld_stream_i32(col + idx), pol);
+		}
+	}
+	__syncthreads();
+
+	// 5. row reduction, binned by rows owned
+	double nrm = 0.0;
+	const int rows_full = tail_split ? nrows - 1 : nrows;      // rows this tile completes
+	if (rows_full > CSR_THREADS / 2) {
+		// thread per row: sequential ascending-j sum (the oracle's summation order)
+		for (int r = tid; r < rows_full; r += CSR_THREADS) {
+			const int i = R0 + r;
+			int a = (int) (row_ptr[i] - base);
+			const int b = (int) (row_ptr[i + 1] - base);
+			double sum = 0.0;
+			for (; a < b; a++)
+				sum += s_prod[swz(a)];
+			sum *= scale;
+			y_store(out, i, sum);
+			nrm += sum * sum;
+		}
+	} else if (rows_full > 0) {
+		// LPR lanes per row, LPR = largest power of two with rows_full * LPR <= CSR_THREADS (max 32)
+		int lpr = 2;
+		while (lpr < 32 && rows_full * (lpr * 2) <= CSR_THREADS)
+			lpr *= 2;
+		const int groups = CSR_THREADS / lpr;
+		const int g = tid / lpr, lane = tid % lpr;
+		for (int rb = 0; rb < rows_full; rb += groups) {
+			const int r = rb + g;
+			double sum = 0.0;
+			if (r < rows_full) {
+				const int i = R0 + r;
+				const int a = (int) (row_ptr[i] - base);
+				const int b = (int) (row_ptr[i + 1] - base);
+				for (int j = a + lane; j < b; j += lpr)
+					sum += s_prod[swz(j)];
+			}
+			for (int o = lpr >> 1; o > 0; o >>= 1)
+				sum += __shfl_xor_sync(0xffffffffu, sum, o);
+			if (r < rows_full && lane == 0) {
+				sum *= scale;
+				y_store(out, R0 + r, sum);
+				nrm += sum * sum;
+			}
+		}
+	}
+
+	// 6. split rows: whole-CTA partial sums over the part of the window they cover
+	if (tail_split) {
+		const int a = (int) (row_ptr[R1 - 1] - base);
+		const double part = block_sum_range(s_prod, a, T, s_red);
+		if (tid == 0)
+			tile_tail[tile] = part;
+	}
+	if (head_split) {
+		const int64_t hend = (start0 < lim) ? start0 : lim;
+		const double part = block_sum_range(s_prod, 0, (int) (hend - base), s_red);
+		if (tid == 0)
+			tile_head[tile] = part;
+	}
+
+	// 7. optional sum of squares of the rows written here (power iteration norm, no atomics)
+	if (out.norm_partial) {
+		nrm = warp_sum(nrm);
+		__syncthreads();
+		if ((tid & 31) == 0)
+			s_red[tid >> 5] = nrm;
+		__syncthreads();
+		if (tid == 0) {
+			double tot = 0.0;
+			#pragma unroll
+			for (int w = 0; w < CSR_THREADS / 32; w++)
+				tot += s_red[w];
+			out.norm_partial[tile] = tot;
+		}
+	}
+}
+
+// One warp per split row: y[row] = tail[owner] + head[owner+1] + ... + head[last], fixed order.
+__global__ void csr_fixup_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict__ split_row,
+                                 const int32_t * __restrict__ split_tile, const double * __restrict__ tile_head,
+                                 const double * __restrict__ tile_tail, int64_t nsplit, int tile_nnz, int64_t ntiles, YOut out)
+{
+	const int64_t s = blockIdx.x;
+	if (s >= nsplit)
+		return;
+	const int lane = threadIdx.x;
+	const int row = split_row[s];
+	const int64_t k = split_tile[s];
+	const int64_t e = row_ptr[row + 1];
+	const int64_t last = (e - 1) / tile_nnz;
+	double acc = (lane == 0) ? tile_tail[k] : 0.0;
+	for (int64_t t = k + 1 + lane; t <= last; t += 32)
+		acc += tile_head[t];
+	acc = warp_sum(acc);
+	if (lane == 0) {
+		const double scale = out.scale ? *out.scale : 1.0;
+		acc *= scale;
+		y_store(out, row, acc);
+		if (out.norm_partial)
+			out.norm_partial[ntiles + s] = acc * acc;
+	}
+}
+
+// Deterministic final reduction of the per-CTA norm partials (single CTA, fixed tree).
+__global__ void norm_reduce_kernel(const double * __restrict__ partial, int64_t n, double * __restrict__ out)
+{
+	__shared__ double s_red[32];
+	double acc = 0.0;
+	for (int64_t i = threadIdx.x; i < n; i += blockDim.x)
+		acc += partial[i];
+	acc = warp_sum(acc);
+	if ((threadIdx.x & 31) == 0)
+		s_red[threadIdx.x >> 5] = acc;
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		double tot = 0.0;
+		for (int w = 0; w < (int) (blockDim.x >> 5); w++)
+			tot += s_red[w];
+		*out = tot;
+	}
+}
+
+int launch_norm_reduce(b200spmv * h, int64_t slots, double * d_out, cudaStream_t st)
+{
+	norm_reduce_kernel<<<1, 1024, 0, st>>>(h->d_norm_partial, slots, d_out);
+	CU_LAUNCH();
+	return 0;
+}
+
+template <int NPT, bool HINT>
+static int launch_tiles(b200spmv * h, const double * dx, cudaStream_t st, const YOut & out)
+{
+	const size_t smem = (size_t) (h->tile_nnz + h->ext) * sizeof(double);
+	static bool attr_set = false;
+	if (!attr_set) {
+		CU(cudaFuncSetAttribute(csr_tile_kernel<NPT, HINT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+		attr_set = true;
+	}
+	csr_tile_kernel<NPT, HINT><<<(unsigned) h->ntiles, CSR_THREADS, smem, st>>>(
+		h->d_row_ptr, h->d_col, h->d_val, reinterpret_cast<const int2 *>(h->d_tile_row), dx,
+		h->d_tile_head, h->d_tile_tail, h->nnz, h->ext, out);
+	CU_LAUNCH();
+	return 0;
+}
+
+int launch_csr_spmv(b200spmv * h, const double * dx, double * dy, cudaStream_t st, const b200spmv_launch * l)
+{
+	YOut out;
+	memset(&out, 0, sizeof(out));
+	out.y = dy;
+	if (l) {
+		if (l->n_peer < 0 || l->n_peer > 8)
+			B200_FAIL("n_peer must be in [0, 8]");
+		out.n_peer = l->n_peer;
+		for (int d = 0; d < l->n_peer; d++)
+			out.peer[d] = l->y_peer[d];
+		out.scale = l->scale;
+		out.norm_partial = l->norm2 ? h->d_norm_partial : nullptr;
+	}
+	int rc;
+	const bool hint = (h->x_hint == 0);
+	switch (h->npt) {
+	case 8:  rc = hint ? launch_tiles<8, true>(h, dx, st, out) : launch_tiles<8, false>(h, dx, st, out); break;
+	case 16: rc = hint ? launch_tiles<16, true>(h, dx, st, out) : launch_tiles<16, false>(h, dx, st, out); break;
+	case 32: rc = hint ? launch_tiles<32, true>(h, dx, st, out) : launch_tiles<32, false>(h, dx, st, out); break;
+	default: B200_FAIL("unsupported csr_nnz_per_thread %d", h->npt);
+	}
+	if (rc)
+		return rc;
+	if (h->nsplit > 0) {
+		csr_fixup_kernel<<<(unsigned) h->nsplit, 32, 0, st>>>(h->d_row_ptr, h->d_split_row, h->d_split_tile, h->d_tile_head,
+		                                                     h->d_tile_tail, h->nsplit, h->tile_nnz, h->ntiles, out);
+		CU_LAUNCH();
+	}
+	if (l && l->norm2)
+		return launch_norm_reduce(h, h->ntiles + h->nsplit, l->norm2, st);
+	return 0;
+}
