@@ -1,0 +1,47 @@
+"""In-tree build of the native libraries (no JIT cache: the built .so files travel with the tree).
+
+  lib/libb200spmv.so : CUDA kernels + C-ABI, nvcc, sm_100a only
+  lib/libb200amg.so  : host-side synthetic matrix source, gcc
+"""
+import os
+import subprocess
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "csrc")
+LIB = os.path.join(HERE, "lib")
+CU_SOURCES = ["capi.cu", "csr_kernel.cu", "sell_kernel.cu", "convert.cu", "partition.cu"]
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
+              "-Xcompiler", "-fPIC", "-shared", "--cudart", "shared"]
+
+
+def _stale(target, deps):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(d) > t for d in deps)
+
+
+def build_spmv(force=False, verbose=False):
+    os.makedirs(LIB, exist_ok=True)
+    so = os.path.join(LIB, "libb200spmv.so")
+    srcs = [os.path.join(CSRC, f) for f in CU_SOURCES]
+    deps = srcs + [os.path.join(CSRC, "common.cuh"), os.path.join(HERE, "..", "include", "b200spmv.h")]
+    if force or _stale(so, deps):
+        nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+        cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", so] + srcs
+        subprocess.check_call(cmd)
+    return so
+
+
+def build_amg(force=False):
+    from . import amg
+    return amg.build(force)
+
+
+def build_all(force=False, verbose=False):
+    return build_spmv(force, verbose), build_amg(force)
+
+
+if __name__ == "__main__":
+    import sys
+    print(build_all(force="--force" in sys.argv, verbose="-v" in sys.argv))

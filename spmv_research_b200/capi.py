@@ -1,0 +1,191 @@
+"""ctypes binding of libb200spmv.so -- the C-ABI declared in include/b200spmv.h.
+
+This module is plumbing only: it never computes anything itself and has no fallback.  If the
+CUDA library is missing or no sm_100 device is present, the calls raise.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(_HERE, "lib", "libb200spmv.so")
+
+CSR_ADAPTIVE = 0
+SELL_C_SIGMA = 1
+SKIP_X_UPLOAD = 1
+SKIP_Y_DOWNLOAD = 2
+X_ROW_ORDER, X_SLICE_WIDTH, X_SLICE_PTR, X_SELL_COL, X_SELL_VAL, X_TILE_ROW, X_SPLIT_ROW, X_SPLIT_TILE = range(1, 9)
+_EXPORT_DTYPE = {X_ROW_ORDER: np.int32, X_SLICE_WIDTH: np.int32, X_SLICE_PTR: np.int64, X_SELL_COL: np.int32,
+                 X_SELL_VAL: np.float64, X_TILE_ROW: np.int32, X_SPLIT_ROW: np.int32, X_SPLIT_TILE: np.int32}
+
+
+class B200Error(RuntimeError):
+    pass
+
+
+class Opts(C.Structure):
+    _fields_ = [("format", C.c_int32), ("device", C.c_int32), ("sell_C", C.c_int32), ("sell_sigma", C.c_int32),
+                ("csr_nnz_per_thread", C.c_int32), ("csr_ext", C.c_int32), ("x_hint", C.c_int32), ("reserved", C.c_int32 * 9)]
+
+
+class Launch(C.Structure):
+    _fields_ = [("scale", C.c_void_p), ("norm2", C.c_void_p), ("y_peer", C.c_void_p * 8), ("n_peer", C.c_int32), ("pad_", C.c_int32)]
+
+
+_lib = None
+
+
+def lib():
+    """Load libb200spmv.so (built in-tree by spmv_research_b200.build); fail loudly if absent."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(SO_PATH):
+        raise B200Error("%s is missing: the CUDA extension was not built (python -m spmv_research_b200.build). "
+                        "There is no CPU fallback." % SO_PATH)
+    L = C.CDLL(SO_PATH)
+    vp, i32, i64 = C.c_void_p, C.c_int32, C.c_int64
+    sig = {
+        "b200spmv_default_opts": (None, [C.POINTER(Opts)]),
+        "b200spmv_create": (C.c_int, [C.POINTER(vp), vp, vp, vp, i64, i64, i64, C.POINTER(Opts)]),
+        "b200spmv_create_device": (C.c_int, [C.POINTER(vp), vp, vp, vp, i64, i64, i64, C.POINTER(Opts)]),
+        "b200spmv_destroy": (None, [vp]),
+        "b200spmv_spmv_host": (C.c_int, [vp, vp, vp]),
+        "b200spmv_spmv_host_ex": (C.c_int, [vp, vp, vp, i32]),
+        "b200spmv_spmv_device": (C.c_int, [vp, vp, vp, vp]),
+        "b200spmv_spmv_device_ex": (C.c_int, [vp, vp, vp, vp, C.POINTER(Launch)]),
+        "b200spmv_launches_per_spmv": (i32, [vp]),
+        "b200spmv_stats": (C.c_int, [vp, C.POINTER(C.c_double), i32]),
+        "b200spmv_export": (C.c_int, [vp, i32, vp, i64, C.POINTER(i64)]),
+        "b200spmv_partition_device": (C.c_int, [vp, i64, i64, i32, vp]),
+        "b200spmv_partition": (C.c_int, [vp, i64, i64, i32, vp]),
+        "b200spmv_merge_coords": (C.c_int, [vp, i32, vp]),
+        "b200spmv_device_count": (C.c_int, [C.POINTER(i32)]),
+        "b200spmv_set_device": (C.c_int, [i32]),
+        "b200spmv_malloc": (C.c_int, [C.POINTER(vp), i64]),
+        "b200spmv_free": (C.c_int, [vp]),
+        "b200spmv_memcpy_h2d": (C.c_int, [vp, vp, i64]),
+        "b200spmv_memcpy_d2h": (C.c_int, [vp, vp, i64]),
+        "b200spmv_malloc_host": (C.c_int, [C.POINTER(vp), i64]),
+        "b200spmv_free_host": (C.c_int, [vp]),
+        "b200spmv_synchronize": (C.c_int, []),
+        "b200spmv_ipc_export": (C.c_int, [vp, vp]),
+        "b200spmv_ipc_import": (C.c_int, [vp, C.POINTER(vp)]),
+        "b200spmv_ipc_close": (C.c_int, [vp]),
+        "b200spmv_time_device": (C.c_int, [vp, vp, vp, i32, i64, vp]),
+        "b200spmv_last_error": (C.c_char_p, []),
+        "b200spmv_version": (C.c_char_p, []),
+    }
+    for name, (res, args) in sig.items():
+        f = getattr(L, name)
+        f.restype = res
+        f.argtypes = args
+    _lib = L
+    return L
+
+
+def check(rc):
+    if rc:
+        raise B200Error(lib().b200spmv_last_error().decode(errors="replace"))
+
+
+def _ptr(a):
+    """Address of a numpy array / torch tensor / raw int."""
+    if a is None:
+        return None
+    if isinstance(a, int):
+        return a
+    if isinstance(a, np.ndarray):
+        return a.ctypes.data
+    if hasattr(a, "data_ptr"):
+        return a.data_ptr()
+    raise TypeError("cannot take the address of %r" % type(a))
+
+
+def default_opts(**kw):
+    o = Opts()
+    lib().b200spmv_default_opts(C.byref(o))
+    for k, v in kw.items():
+        if not hasattr(o, k):
+            raise TypeError("unknown option %s" % k)
+        setattr(o, k, v)
+    return o
+
+
+class Handle:
+    """Owns one b200spmv_t*."""
+
+    def __init__(self, row_ptr, col_ind, values, m, n, nnz, opts=None, device_arrays=False):
+        self._h = C.c_void_p()
+        self.m, self.n, self.nnz = int(m), int(n), int(nnz)
+        self._opts = opts if opts is not None else default_opts()
+        fn = lib().b200spmv_create_device if device_arrays else lib().b200spmv_create
+        check(fn(C.byref(self._h), _ptr(row_ptr), _ptr(col_ind), _ptr(values), self.m, self.n, self.nnz, C.byref(self._opts)))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value and _lib is not None:
+            _lib.b200spmv_destroy(self._h)
+            self._h = C.c_void_p()
+
+    __del__ = close
+
+    def spmv_host(self, x, y, flags=0):
+        assert x.dtype == np.float64 and y.dtype == np.float64 and x.size >= self.n and y.size >= self.m
+        check(lib().b200spmv_spmv_host_ex(self._h, _ptr(x), _ptr(y), flags))
+
+    def spmv_device(self, dx, dy, stream=None, scale=None, norm2=None, peers=()):
+        if scale is None and norm2 is None and not peers:
+            check(lib().b200spmv_spmv_device(self._h, _ptr(dx), _ptr(dy), stream))
+            return
+        l = Launch()
+        l.scale = _ptr(scale)
+        l.norm2 = _ptr(norm2)
+        l.n_peer = len(peers)
+        for i, p in enumerate(peers):
+            l.y_peer[i] = _ptr(p)
+        check(lib().b200spmv_spmv_device_ex(self._h, _ptr(dx), _ptr(dy), stream, C.byref(l)))
+
+    @property
+    def launches_per_spmv(self):
+        return int(lib().b200spmv_launches_per_spmv(self._h))
+
+    def stats(self):
+        out = (C.c_double * 7)()
+        check(lib().b200spmv_stats(self._h, out, 7))
+        keys = ("mem_footprint", "units", "nsplit", "entries", "unit_size", "ext_or_sigma", "convert_ms")
+        return dict(zip(keys, list(out)))
+
+    def export(self, what):
+        cnt = C.c_int64()
+        check(lib().b200spmv_export(self._h, what, None, 0, C.byref(cnt)))
+        a = np.zeros(max(cnt.value, 1), _EXPORT_DTYPE[what])
+        check(lib().b200spmv_export(self._h, what, a.ctypes.data, a.nbytes, C.byref(cnt)))
+        return a[:cnt.value]
+
+    def merge_coords(self, W):
+        out = np.zeros((W + 1, 2), np.int64)
+        check(lib().b200spmv_merge_coords(self._h, W, out.ctypes.data))
+        return out
+
+    def time_device(self, dx, dy, iters, flush_bytes=0):
+        ms = np.zeros(iters, np.float32)
+        check(lib().b200spmv_time_device(self._h, _ptr(dx), _ptr(dy), iters, flush_bytes, ms.ctypes.data))
+        return ms
+
+
+def partition(sums, N, total, W, device=False):
+    """Reference nnz-balanced partitioner evaluated on the GPU: int64[W, 2] of [i_s, i_e)."""
+    out = np.zeros((W, 2), np.int64)
+    fn = lib().b200spmv_partition_device if device else lib().b200spmv_partition
+    check(fn(_ptr(sums), int(N), int(total), int(W), out.ctypes.data))
+    return out
+
+
+def device_count():
+    n = C.c_int32()
+    try:
+        check(lib().b200spmv_device_count(C.byref(n)))
+    except B200Error:
+        return 0
+    return n.value

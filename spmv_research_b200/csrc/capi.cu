@@ -248,3 +248,152 @@ extern "C" int b200spmv_spmv_host(b200spmv_t * h, const double * x, double * y)
 {
 	return b200spmv_spmv_host_ex(h, x, y, 0);
 }
+
+// ---------------------------------------------------------------------------------------------
+// statistics / layout export
+// ---------------------------------------------------------------------------------------------
+extern "C" int b200spmv_stats(const b200spmv_t * h, double * out, int32_t n_out)
+{
+	if (!h || !out)
+		B200_FAIL("NULL argument");
+	double v[7];
+	if (h->format == B200SPMV_CSR_ADAPTIVE) {
+		v[0] = (double) h->nnz * 12.0 + (double) (h->m + 1) * 4.0 + (double) (h->ntiles + 1) * 8.0 + (double) h->ntiles * 16.0 + (double) h->nsplit * 8.0;
+		v[1] = (double) h->ntiles;
+		v[2] = (double) h->nsplit;
+		v[3] = (double) h->nnz;
+		v[4] = (double) h->tile_nnz;
+		v[5] = (double) h->ext;
+	} else {
+		v[0] = (double) h->padded * 12.0 + (double) h->nslices * 4.0 + (double) (h->nslices + 1) * 8.0 + (double) h->m * 4.0;
+		v[1] = (double) h->nslices;
+		v[2] = 0.0;
+		v[3] = (double) h->padded;
+		v[4] = (double) h->C;
+		v[5] = (double) h->sigma;
+	}
+	v[6] = (double) h->convert_ms;
+	for (int i = 0; i < n_out && i < 7; i++)
+		out[i] = v[i];
+	return 0;
+}
+
+extern "C" int b200spmv_export(const b200spmv_t * h, int32_t what, void * dst, int64_t capacity_bytes, int64_t * count_out)
+{
+	if (!h || !count_out)
+		B200_FAIL("NULL argument");
+	CU(cudaSetDevice(h->device));
+	const void * src = nullptr;
+	int64_t count = 0, esize = 4;
+	const bool sell = (h->format == B200SPMV_SELL_C_SIGMA);
+	switch (what) {
+	case B200SPMV_X_ROW_ORDER:   if (!sell) B200_FAIL("not a SELL handle"); src = h->d_row_order; count = h->m; break;
+	case B200SPMV_X_SLICE_WIDTH: if (!sell) B200_FAIL("not a SELL handle"); src = h->d_slice_width; count = h->nslices; break;
+	case B200SPMV_X_SLICE_PTR:   if (!sell) B200_FAIL("not a SELL handle"); src = h->d_slice_ptr; count = h->nslices + 1; esize = 8; break;
+	case B200SPMV_X_SELL_COL:    if (!sell) B200_FAIL("not a SELL handle"); src = h->d_scol; count = h->padded; break;
+	case B200SPMV_X_SELL_VAL:    if (!sell) B200_FAIL("not a SELL handle"); src = h->d_sval; count = h->padded; esize = 8; break;
+	case B200SPMV_X_TILE_ROW:    if (sell) B200_FAIL("not a CSR handle"); src = h->d_tile_row; count = h->ntiles + 1; break;
+	case B200SPMV_X_SPLIT_ROW:   if (sell) B200_FAIL("not a CSR handle"); src = h->d_split_row; count = h->nsplit; break;
+	case B200SPMV_X_SPLIT_TILE:  if (sell) B200_FAIL("not a CSR handle"); src = h->d_split_tile; count = h->nsplit; break;
+	default: B200_FAIL("unknown export selector %d", what);
+	}
+	*count_out = count;
+	if (!dst)
+		return 0;                               // sizing call
+	if (capacity_bytes < count * esize)
+		B200_FAIL("export buffer too small: need %lld bytes", (long long) (count * esize));
+	if (count == 0)
+		return 0;
+	if (what == B200SPMV_X_TILE_ROW) {
+		// tile_info is {row | flag, row_ptr[row]} pairs: copy the first member, drop the flag bit
+		CU(cudaMemcpy2D(dst, 4, src, 8, 4, (size_t) count, cudaMemcpyDeviceToHost));
+		int32_t * d = (int32_t *) dst;
+		for (int64_t i = 0; i < count; i++)
+			d[i] &= 0x7fffffff;
+		return 0;
+	}
+	CU(cudaMemcpy(dst, src, (size_t) (count * esize), cudaMemcpyDeviceToHost));
+	return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// device memory helpers (so that a C host program needs no CUDA runtime of its own)
+// ---------------------------------------------------------------------------------------------
+extern "C" int b200spmv_device_count(int32_t * count)
+{
+	int n = 0;
+	cudaError_t e = cudaGetDeviceCount(&n);
+	*count = (e == cudaSuccess) ? n : 0;
+	if (e != cudaSuccess)
+		B200_FAIL("cudaGetDeviceCount: %s", cudaGetErrorString(e));
+	return 0;
+}
+extern "C" int b200spmv_set_device(int32_t device) { CU(cudaSetDevice(device)); return 0; }
+extern "C" int b200spmv_malloc(void ** dptr, int64_t bytes) { CU(cudaMalloc(dptr, (size_t) (bytes > 0 ? bytes : 1))); return 0; }
+extern "C" int b200spmv_free(void * dptr) { CU(cudaFree(dptr)); return 0; }
+extern "C" int b200spmv_memcpy_h2d(void * dst, const void * src, int64_t bytes) { CU(cudaMemcpy(dst, src, (size_t) bytes, cudaMemcpyHostToDevice)); return 0; }
+extern "C" int b200spmv_memcpy_d2h(void * dst, const void * src, int64_t bytes) { CU(cudaMemcpy(dst, src, (size_t) bytes, cudaMemcpyDeviceToHost)); return 0; }
+extern "C" int b200spmv_malloc_host(void ** hptr, int64_t bytes) { CU(cudaMallocHost(hptr, (size_t) (bytes > 0 ? bytes : 1))); return 0; }
+extern "C" int b200spmv_free_host(void * hptr) { CU(cudaFreeHost(hptr)); return 0; }
+extern "C" int b200spmv_synchronize(void) { CU(cudaDeviceSynchronize()); return 0; }
+
+extern "C" int b200spmv_ipc_export(void * dptr, unsigned char handle_out[64])
+{
+	static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+	cudaIpcMemHandle_t hd;
+	CU(cudaIpcGetMemHandle(&hd, dptr));
+	memcpy(handle_out, &hd, 64);
+	return 0;
+}
+extern "C" int b200spmv_ipc_import(const unsigned char handle[64], void ** dptr_out)
+{
+	cudaIpcMemHandle_t hd;
+	memcpy(&hd, handle, 64);
+	CU(cudaIpcOpenMemHandle(dptr_out, hd, cudaIpcMemLazyEnablePeerAccess));
+	return 0;
+}
+extern "C" int b200spmv_ipc_close(void * dptr) { CU(cudaIpcCloseMemHandle(dptr)); return 0; }
+
+// ---------------------------------------------------------------------------------------------
+// device timing of back-to-back products (CUDA events on the launching stream)
+// ---------------------------------------------------------------------------------------------
+__global__ void flush_kernel(double * buf, int64_t n, double v)
+{
+	for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x)
+		buf[i] = v;
+}
+
+extern "C" int b200spmv_time_device(b200spmv_t * h, const double * dx, double * dy, int32_t iters, int64_t flush_bytes, float * ms_out)
+{
+	if (!h || !dx || !dy || !ms_out || iters < 1)
+		B200_FAIL("bad arguments");
+	CU(cudaSetDevice(h->device));
+	double * d_flush = nullptr;
+	if (flush_bytes > 0)
+		CU(cudaMalloc(&d_flush, (size_t) flush_bytes));
+	cudaEvent_t * ev = (cudaEvent_t *) malloc(2 * (size_t) iters * sizeof(cudaEvent_t));
+	for (int i = 0; i < 2 * iters; i++)
+		cudaEventCreate(&ev[i]);
+	int rc = 0;
+	for (int i = 0; i < iters && !rc; i++) {
+		if (d_flush)
+			flush_kernel<<<148 * 8, 256, 0, h->stream>>>(d_flush, flush_bytes / 8, (double) i);
+		cudaEventRecord(ev[2 * i], h->stream);
+		rc = b200spmv_spmv_device_ex(h, dx, dy, h->stream, nullptr);
+		cudaEventRecord(ev[2 * i + 1], h->stream);
+	}
+	cudaError_t e = cudaStreamSynchronize(h->stream);
+	if (!rc && e == cudaSuccess)
+		for (int i = 0; i < iters; i++)
+			cudaEventElapsedTime(&ms_out[i], ev[2 * i], ev[2 * i + 1]);
+	for (int i = 0; i < 2 * iters; i++)
+		cudaEventDestroy(ev[i]);
+	free(ev);
+	if (d_flush)
+		cudaFree(d_flush);
+	if (rc)
+		return rc;
+	if (e != cudaSuccess)
+		B200_FAIL("b200spmv_time_device: %s", cudaGetErrorString(e));
+	return 0;
+}

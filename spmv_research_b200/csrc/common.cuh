@@ -120,8 +120,10 @@ struct YOut {
 __device__ __forceinline__ void y_store(const YOut & o, int64_t row, double v)
 {
 	o.y[row] = v;
-	for (int d = 0; d < o.n_peer; d++)
-		o.peer[d][row] = v;
+	#pragma unroll
+	for (int d = 0; d < 8; d++)          // unrolled + predicated: keeps the parameter struct out of local memory
+		if (d < o.n_peer)
+			o.peer[d][row] = v;
 }
 
 __device__ __forceinline__ double warp_sum(double v)

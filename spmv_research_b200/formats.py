@@ -1,0 +1,95 @@
+"""Host-side mirror of the reference's per-format plugin interface, over the C-ABI.
+
+Reference (relative to /root/reference/benchmark_code/BENCH/src/spmv_kernels/):
+  struct Matrix_Format { format_name, m, n, nnz, mem_footprint, csr_mem_footprint,
+                         spmv(x, y), statistics_start(), statistics_print_data(buf, n) }   spmv_kernel.h:9-26
+  csr_to_format(row_ptr, col_ind, values, m, n, nnz, symmetric, symmetry_expanded)          spmv_kernel.h:28
+Same names, argument meaning and error behaviour; the compiled equivalent that links into the
+reference harness is host/b200_plugin.cpp.  All arithmetic happens in libb200spmv.so.
+"""
+import numpy as np
+
+from . import capi
+
+FORMAT_NAMES = {capi.CSR_ADAPTIVE: "B200_CSR_ADAPTIVE", capi.SELL_C_SIGMA: "B200_SELL_C_SIGMA"}
+
+
+class MatrixFormat:
+    """Mirror of `struct Matrix_Format`; `spmv(x, y)` follows the reference GPU-plugin
+    convention when `cache_x` is set (x uploaded on the first call only, GPU_clean/cuda_csr.cu:353-382)
+    and otherwise moves x and y across PCIe on every call."""
+
+    def __init__(self, handle, fmt, cache_x=False):
+        self._h = handle
+        self.format = fmt
+        self.m, self.n, self.nnz = handle.m, handle.n, handle.nnz
+        st = handle.stats()
+        self.mem_footprint = st["mem_footprint"]
+        self.csr_mem_footprint = self.nnz * (8 + 4) + (self.m + 1) * 4      # spmv_kernel.h:24
+        self.format_name = FORMAT_NAMES[fmt]
+        self.convert_ms = st["convert_ms"]
+        self.cache_x = cache_x
+        self._x_seen = None
+        self.num_loops = 0
+
+    # -- reference interface ------------------------------------------------------------------
+    def spmv(self, x, y):
+        flags = 0
+        if self.cache_x and self._x_seen == x.ctypes.data:
+            flags |= capi.SKIP_X_UPLOAD
+        self._h.spmv_host(x, y, flags)
+        self._x_seen = x.ctypes.data
+        self.num_loops += 1
+
+    def statistics_start(self):
+        self.num_loops = 0
+
+    def statistics_print_data(self):
+        return ""
+
+    # -- device-resident path (iterated SpMV) -------------------------------------------------
+    def spmv_device(self, dx, dy, stream=None, **kw):
+        self._h.spmv_device(dx, dy, stream, **kw)
+
+    @property
+    def handle(self):
+        return self._h
+
+    @property
+    def gpu_launches_per_spmv(self):
+        return self._h.launches_per_spmv
+
+    def compulsory_bytes(self):
+        """B_c = 8 nnz + 4 nnz + 4 (m+1) + 8 n + 8 m   (identical for CSR and SELL)."""
+        return 12 * self.nnz + 4 * (self.m + 1) + 8 * self.n + 8 * self.m
+
+    def close(self):
+        self._h.close()
+
+
+def statistics_print_labels():
+    return ""
+
+
+def csr_to_format(row_ptr, col_ind, values, m, n, nnz, symmetric=0, symmetry_expanded=0, *, format=capi.CSR_ADAPTIVE,
+                  cache_x=False, **opts):
+    """Mirror of the reference factory.  Inputs are borrowed for the call only (the harness frees
+    them right after, bench.cpp:605-629); the library uploads its own copy."""
+    if symmetric and not symmetry_expanded:
+        # same message as K/csr.cpp:224-225
+        raise capi.B200Error("symmetric matrices have to be expanded to be supported by this format")
+    row_ptr = np.ascontiguousarray(row_ptr, np.int32)
+    col_ind = np.ascontiguousarray(col_ind, np.int32)
+    values = np.ascontiguousarray(values, np.float64)
+    if row_ptr.size != m + 1 or col_ind.size < nnz or values.size < nnz:
+        raise capi.B200Error("CSR array sizes do not match m / nnz")
+    o = capi.default_opts(format=format, **opts)
+    h = capi.Handle(row_ptr, col_ind if nnz else None, values if nnz else None, m, n, nnz, o)
+    return MatrixFormat(h, format, cache_x=cache_x)
+
+
+def csr_to_format_device(d_row_ptr, d_col_ind, d_values, m, n, nnz, *, format=capi.CSR_ADAPTIVE, **opts):
+    """Same, from arrays already resident in HBM (torch tensors or raw device addresses)."""
+    o = capi.default_opts(format=format, **opts)
+    h = capi.Handle(d_row_ptr, d_col_ind, d_values, m, n, nnz, o, device_arrays=True)
+    return MatrixFormat(h, format)

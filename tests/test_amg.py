@@ -1,0 +1,60 @@
+"""The product's host generator (csrc/amg.c) against the reference generator: golden fingerprints
+made from oracle/_ref/libref_amg.so, shard-wise generation, parameter parsing, error behaviour."""
+import numpy as np
+import pytest
+
+import matrices as M
+from spmv_research_b200 import amg
+
+
+def test_generator_fingerprints_vs_golden(golden, golden_matrices):
+    for li, (p, rp, col, val) in enumerate(golden_matrices):
+        assert int(rp[-1]) == int(golden["g%d_nnz" % li])
+        got = np.array([amg.fnv1a64(rp), amg.fnv1a64(col), amg.fnv1a64(val)], np.uint64)
+        assert np.array_equal(got, golden["g%d_fnv" % li]), M.GOLDEN_LINES[li]
+
+
+def test_config1_shape(native):
+    """BASELINE config 1 (1M x 1M, avg 10, std 5, normal, random, seed 14): nnz and max row of SURVEY App. C."""
+    p = amg.MatrixParams.parse("1000000 1000000 10 5 normal random 0.3 0 0.5 0.5 14")
+    rp, bw = amg.row_ptr(p)
+    assert int(rp[-1]) == 10038177 and int(np.max(np.diff(rp))) == 34 and int(np.sum(np.diff(rp) == 0)) == 28580
+
+
+def test_shard_generation_matches_whole(golden_matrices):
+    """Rows [i_s, i_e) generated on their own equal the slice of the whole matrix (any cut points,
+    not only anchor boundaries): what each rank of a row-sharded run relies on."""
+    for (p, rp, col, val) in golden_matrices[:5]:
+        _, bw = amg.row_ptr(p)
+        cuts = [0, 1, p.rows // 3 + 5, p.rows // 2, p.rows - 1, p.rows]
+        for a, b in zip(cuts[:-1], cuts[1:]):
+            c, v = amg.fill(p, rp, bw, a, b)
+            assert np.array_equal(c, col[rp[a]:rp[b]]) and np.array_equal(v, val[rp[a]:rp[b]])
+
+
+def test_csr_wellformed(golden_matrices):
+    for (p, rp, col, val) in golden_matrices:
+        assert rp[0] == 0 and np.all(np.diff(rp) >= 0)
+        assert col.min() >= 0 and col.max() < p.cols and np.all((val >= 0) & (val < 1))
+        for i in np.random.default_rng(1).integers(0, p.rows, 200):
+            assert np.all(np.diff(col[rp[i]:rp[i + 1]]) > 0)           # sorted, unique columns per row
+
+
+def test_vs_reference_generator_direct(oracle):
+    if not oracle.ref_available():
+        pytest.skip("oracle/_ref not built")
+    for line in ["1000 1000 5 1.6667 normal random 0.001 0 0.05 0.5 14", "5000 5000 20 6 normal simple 0.05 0 1.9 0.95 3",
+                 "2500 4000 8 30 gamma diagonal 0.9 3 0.0 0.0 99", "700 700 3 0 normal random 2.0 0 0 0 1"]:
+        p = amg.MatrixParams.parse(line)
+        a = amg.generate(p)
+        b = oracle.ref_amg_generate(p.rows, p.cols, p.avg, p.std, p.distribution, p.placement, p.bw, p.skew, p.neigh, p.crs, p.seed)
+        assert all(np.array_equal(x, y) for x, y in zip(a, b)), line
+
+
+def test_errors_and_parsing(native):
+    with pytest.raises(RuntimeError):
+        amg.row_ptr(amg.MatrixParams(50, 50, 5, 1))                      # reference divides by nr_rows/100
+    with pytest.raises(ValueError):
+        amg.MatrixParams.parse("1 2 3")
+    p = amg.MatrixParams.parse("17099 17099 5.6 4.39 normal random 0.29 61.9 0.8 0.63 14 scircuit")
+    assert p.name == "scircuit" and p.seed == 14 and amg.MatrixParams.parse(p.line()).rows == 17099

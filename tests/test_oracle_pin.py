@@ -1,0 +1,134 @@
+"""Pins the CPU oracle (oracle/spmv_oracle.c): against the committed golden fixture made from the
+reference's own code (tests/golden/make_golden.py) and, when oracle/_ref is present, against that
+code directly on random cases with empty rows, duplicate prefix sums and ragged tails."""
+import numpy as np
+import pytest
+
+import matrices as M
+from tests.golden.make_golden import MERGE_T, PART_W, SELL_CFG
+
+
+def test_partition_vs_golden(oracle, golden, golden_matrices):
+    for li, (p, rp, col, val) in enumerate(golden_matrices):
+        nnz = int(rp[-1])
+        for W in PART_W:
+            assert np.array_equal(oracle.partition(W, rp, p.rows, nnz), golden["g%d_part%d" % (li, W)]), (li, W)
+
+
+def test_merge_path_vs_golden(oracle, golden, golden_matrices):
+    for li, (p, rp, col, val) in enumerate(golden_matrices):
+        m, nnz = p.rows, int(rp[-1])
+        for T in MERGE_T:
+            per = (m + nnz + T - 1) // T
+            got = np.array([oracle.merge_path_search(min(per * t, m + nnz), rp, m, nnz) for t in range(T + 1)], np.int64)
+            assert np.array_equal(got, golden["g%d_merge%d" % (li, T)]), (li, T)
+            _, coords = oracle.merge_csrmv(T, rp, col, val, M.rand_x(p.cols))
+            assert np.array_equal(coords, got)
+
+
+def test_sellcs_vs_golden(oracle, golden, golden_matrices):
+    for li, (p, rp, col, val) in enumerate(golden_matrices):
+        for (C_, sg) in SELL_CFG:
+            S = oracle.sellcs_convert(rp, col, val, C_, sg)
+            got = np.array([oracle.fnv1a64(S[k]) for k in ("row_order", "slice_width", "slice_ptr", "col", "val")], np.uint64)
+            assert np.array_equal(got, golden["g%d_sell_%d_%d" % (li, C_, sg)]), (li, C_, sg)
+
+
+def test_csr_scalar_vs_golden(oracle, golden, golden_matrices):
+    """The serial kernel is pinned up to FMA contraction of the reference build: within the
+    north-star bound, and bit-equal wherever the compiler made the same choice."""
+    for li, (p, rp, col, val) in enumerate(golden_matrices):
+        x = M.rand_x(p.cols)
+        y = oracle.csr_spmv(rp, col, val, x)
+        bound = oracle.row_abs_bound(rp, col, val, x)
+        assert np.all(np.abs(y[::7] - golden["g%d_y_sample" % li]) <= 1e-12 * bound[::7])
+
+
+def test_sell_and_merge_spmv_agree_with_csr(oracle, golden_matrices):
+    for (p, rp, col, val) in golden_matrices[:4]:
+        x = M.rand_x(p.cols)
+        y = oracle.csr_spmv(rp, col, val, x)
+        bound = oracle.row_abs_bound(rp, col, val, x)
+        ys = oracle.sellcs_spmv(oracle.sellcs_convert(rp, col, val, 32, 16384), x)
+        ym, _ = oracle.merge_csrmv(7, rp, col, val, x)
+        assert oracle.within_bound(ys, y, bound) and oracle.within_bound(ym, y, bound)
+
+
+def test_gold_f128_and_rowblocks(oracle):
+    name, rp, col, val, n = M.edge_cases()[4]
+    x = M.rand_x(n)
+    y = oracle.csr_spmv(rp, col, val, x)
+    acc = oracle.check_accuracy(rp, col, val, x, y)
+    assert acc["max_rel"] < 1e-10 and acc["max_ae"] < 1e-12          # bench_spmv.cpp:114-119 pass criterion
+    rb = oracle.adaptive_rowblocks(rp, 64, 4)
+    assert rb[0] == 0 and rb[-1] == len(rp) - 1 and np.all(np.diff(rb) >= 0) and (len(rb) - 1) % 4 == 0
+    for a, b in zip(rb[:-1], rb[1:]):
+        assert b - a <= 1 or rp[b] - rp[a] <= 64                   # multi-row blocks hold <= BLOCK_SIZE nnz
+
+
+# ---- direct comparison with the compiled reference (authoring container; skipped when _ref is absent)
+def _need_ref(oracle):
+    if not oracle.ref_available():
+        pytest.skip("oracle/_ref not built")
+
+
+def test_partition_vs_reference_random(oracle):
+    _need_ref(oracle)
+    rng = np.random.default_rng(3)
+    for _ in range(300):
+        m = int(rng.integers(1, 400))
+        lens = rng.integers(0, 9, m) * (rng.random(m) < rng.random())
+        rp = np.zeros(m + 1, np.int32)
+        np.cumsum(lens, out=rp[1:])
+        rp += int(rng.integers(0, 5))                      # Sums may start anywhere (parallel_util.h:150)
+        total = int(rp[-1] - rp[0])
+        W = int(rng.integers(1, 40))
+        assert np.array_equal(oracle.partition(W, rp, m, total), oracle.ref_partition(W, rp, m, total))
+
+
+def test_merge_search_vs_reference_random(oracle):
+    _need_ref(oracle)
+    rng = np.random.default_rng(4)
+    for _ in range(60):
+        m = int(rng.integers(1, 300))
+        rp, col, val = M.csr_from_lengths(rng.integers(0, 7, m) * (rng.random(m) < 0.7), 50, int(rng.integers(1 << 30)))
+        nnz = int(rp[-1])
+        for d in rng.integers(0, m + nnz + 1, 25):
+            assert oracle.merge_path_search(int(d), rp, m, nnz) == oracle.ref_merge_path_search(int(d), rp, m, nnz)
+        x = M.rand_x(50)
+        T = int(rng.integers(1, 9))
+        y, _ = oracle.merge_csrmv(T, rp, col, val, x)
+        yr = oracle.ref_merge_csrmv(T, rp, col, val, x)
+        assert oracle.within_bound(y, yr, oracle.row_abs_bound(rp, col, val, x))
+
+
+def test_sellcs_vs_reference_random(oracle):
+    _need_ref(oracle)
+    rng = np.random.default_rng(5)
+    for it in range(40):
+        m = int(rng.integers(1, 700))
+        C_ = int(2 ** rng.integers(1, 6))
+        sg = C_ * int(rng.integers(1, 9))
+        rp, col, val = M.csr_from_lengths(rng.integers(0, 20, m) * (rng.random(m) < 0.75), 90, it)
+        A = oracle.sellcs_convert(rp, col, val, C_, sg)
+        for i64 in (True, False):
+            B = oracle.ref_sellcs_convert(rp, col, val, 90, C_, sg, index64=i64)
+            for k in ("row_order", "slice_width", "slice_ptr", "col", "val"):
+                assert np.array_equal(A[k], B[k]), (it, k, i64)
+
+
+def test_csr_vs_reference_plugin(oracle):
+    _need_ref(oracle)
+    for name, rp, col, val, n in M.edge_cases():
+        if len(rp) - 1 < 1 or rp[-1] == 0:
+            continue
+        x = M.rand_x(n)
+        R = oracle.RefCSR(rp, col, val, n)
+        assert R.format_name == "Custom_CSR_B"
+        yr = np.full(len(rp) - 1, 1.0)
+        R.spmv_serial(x, yr)
+        yo = oracle.csr_spmv(rp, col, val, x)
+        assert oracle.within_bound(yo, yr, oracle.row_abs_bound(rp, col, val, x)), name
+        yp = np.full(len(rp) - 1, 1.0)
+        R.spmv(x, yp)                                      # OpenMP compute_csr, nnz-balanced threads
+        assert np.array_equal(yp, yr), name
