@@ -1,0 +1,469 @@
+#!/usr/bin/env python
+"""bench.py -- headline measurement of the B200 SpMV engine (contract: see DESIGN.md "Measurement").
+
+  python bench.py [--gpus 1] [--steps K] [--warmup W]            N=1: stratified sample of the medium dataset
+  torchrun --nproc-per-node N bench.py --gpus N ...              N>1: row-sharded power iteration (config 5 series)
+  python bench.py --impl reference ...                           the reference's CPU CSR kernel on the host cores
+
+One JSON line on stdout (rank 0).  A "step" is one pass of the hot path over the workload:
+one SpMV of every sample matrix (N=1) or one power iteration of the sharded matrix (N>1).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "SpMV GFLOP/s (2*nnz/t), fp64; effective HBM GB/s over compulsory bytes"
+NOMINAL_HBM_GBS = 8000.0
+
+
+def measured_peak():
+    try:
+        pk = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(pk["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, copy)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons during the timed region."""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index=0):
+        self.rows, self.proc, self.index = [], None, index
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.rows.append([c.strip() for c in ln.split(",")])
+
+    def __exit__(self, *a):
+        if self.proc:
+            time.sleep(0.15)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self):
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+                for nm, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+            except Exception:
+                pass
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_csr_runner(rp, col, val, n):
+    """The timed CPU arm: the reference's own OpenMP CSR plugin when oracle/_ref travelled with the
+    tree (kind "reference"), else the oracle port of the same kernel (kind "port")."""
+    from oracle import oracle as O
+    threads = O.max_threads()
+    if O.ref_available():
+        try:
+            R = O.RefCSR(rp, col, val, n)
+            return (lambda x, y: R.spmv(x, y)), "reference", threads
+        except OSError:
+            pass
+    bounds = np.full(2 * threads, -1, np.int64)
+    return (lambda x, y: O.csr_spmv_omp(rp, col, val, x, y, bounds, threads)), "port", threads
+
+
+# C code under oracle/_ref printf()s to stdout ("balance time = ..."); keep the real stdout for the one JSON line.
+_REAL_STDOUT = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(d):
+    os.write(_REAL_STDOUT, (json.dumps(d) + "\n").encode())
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="auto", choices=["auto", "medium_sample", "config1", "g1", "g2", "power"])
+    ap.add_argument("--format", default="csr", choices=["csr", "sell"])
+    ap.add_argument("--rows-per-gpu", type=int, default=4194304)
+    ap.add_argument("--exchange", default="nccl", choices=["nccl", "p2p"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-sell", action="store_true")
+    ap.add_argument("--x", default="ones", choices=["ones", "random"])
+    return ap.parse_args()
+
+
+def workload_params(args, world):
+    from spmv_research_b200 import harness as H
+    wl = args.workload
+    if wl == "auto":
+        wl = "power" if world > 1 else "medium_sample"
+    if wl == "medium_sample":
+        return wl, H.medium_sample()
+    if wl == "config1":
+        return wl, [H.CONFIG1]
+    if wl == "g1":
+        return wl, [H.CONFIG4_G1]
+    if wl == "g2":
+        return wl, [H.CONFIG4_G2]
+    return wl, [H.config5(world, args.rows_per_gpu)]
+
+
+# ------------------------------------------------------------------------------------------------
+# N = 1: one SpMV of every matrix of the workload per step, everything resident in HBM
+# ------------------------------------------------------------------------------------------------
+def run_single(args):
+    import torch
+    import spmv_research_b200 as S
+    from spmv_research_b200 import amg, capi, harness as H
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(0)
+    dev = torch.device("cuda:0")
+    stream = torch.cuda.current_stream().cuda_stream
+    wl, plist = workload_params(args, 1)
+    fmt = S.CSR_ADAPTIVE if args.format == "csr" else S.SELL_C_SIGMA
+    peak, peak_src = measured_peak()
+
+    mats, t_gen = [], 0.0
+    cpu = {"t": 0.0, "flops": 0.0, "kind": None, "cores": 0, "iters": 3, "max_err_over_bound": 0.0}
+    for p in plist:
+        t0 = time.time()
+        rp, col, val = amg.generate(p)
+        t_gen += time.time() - t0
+        m, n, nnz = p.rows, p.cols, int(rp[-1])
+        MF = S.csr_to_format(rp, col, val, m, n, nnz, 0, 0, format=fmt)
+        MF2 = None
+        if not args.no_sell:
+            MF2 = S.csr_to_format(rp, col, val, m, n, nnz, 0, 0, format=(S.SELL_C_SIGMA if fmt == S.CSR_ADAPTIVE else S.CSR_ADAPTIVE))
+        x_h = np.ones(n) if args.x == "ones" else np.random.default_rng(14).uniform(-1, 1, n)
+        dx = torch.from_numpy(x_h).to(dev)
+        dy = torch.full((m,), 1.0, dtype=torch.float64, device=dev)
+        rec = dict(p=p, m=m, n=n, nnz=nnz, MF=MF, MF2=MF2, dx=dx, dy=dy, x_h=x_h, bc=H.compulsory_bytes(m, n, nnz))
+        # CPU baseline leg (rank 0, bounded: 1 warm-up + 3 timed calls per matrix) and a parity spot check
+        if not args.no_cpu_baseline:
+            from oracle import oracle as O
+            run, kind, cores = cpu_csr_runner(rp, col, val, n)
+            y_cpu = np.full(m, 1.0)
+            run(x_h, y_cpu)
+            t0 = time.time()
+            for _ in range(cpu["iters"]):
+                run(x_h, y_cpu)
+            cpu["t"] += time.time() - t0
+            cpu["flops"] += 2.0 * nnz * cpu["iters"]
+            cpu["kind"], cpu["cores"] = kind, cores
+            y_ser = O.csr_spmv(rp, col, val, x_h)
+            bound = O.row_abs_bound(rp, col, val, x_h)
+            y_gpu = np.full(m, 1.0)
+            MF.spmv(x_h, y_gpu)
+            ratio = float(np.max(np.abs(y_gpu - y_ser) / np.maximum(bound, 1e-300)))
+            cpu["max_err_over_bound"] = max(cpu["max_err_over_bound"], ratio)
+            if ratio > 1e-12:
+                raise SystemExit("bench.py: parity check failed on %s (err/bound %.3g)" % (p.line(), ratio))
+        mats.append(rec)
+        del rp, col, val
+
+    def one_step(which="MF", events=None):
+        for i, r in enumerate(mats):
+            if events is not None:
+                events[i][0].record()
+            r[which].spmv_device(r["dx"], r["dy"], stream)
+            if events is not None:
+                events[i][1].record()
+
+    K, W = args.steps, max(args.warmup, 3)
+    for _ in range(W):
+        one_step()
+    torch.cuda.synchronize()
+    ev = [[(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in mats] for _ in range(K)]
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(0) as clk:
+        torch.cuda.synchronize()
+        e0.record()
+        for k in range(K):
+            one_step(events=ev[k])
+        e1.record()
+        torch.cuda.synchronize()
+    ms_total = e0.elapsed_time(e1)
+    ms_step = ms_total / K
+    tot_nnz = sum(r["nnz"] for r in mats)
+    tot_bc = sum(r["bc"] for r in mats)
+    gflops = 2.0 * tot_nnz / (ms_step * 1e-3) * 1e-9
+    eff = tot_bc / (ms_step * 1e-3) * 1e-9
+    per = []
+    kern_ms = 0.0
+    for i, r in enumerate(mats):
+        t = float(np.mean([ev[k][i][0].elapsed_time(ev[k][i][1]) for k in range(K)]))
+        kern_ms += t
+        st = r["MF"].handle.stats()
+        per.append({"matrix": r["p"].line(), "nnz": r["nnz"], "ms": round(t, 5), "gflops": round(2.0 * r["nnz"] / t * 1e-6, 1),
+                    "eff_GBs": round(r["bc"] / t * 1e-6, 1), "frac_of_measured": round(r["bc"] / t * 1e-6 / peak, 4),
+                    "launches": r["MF"].gpu_launches_per_spmv, "split_rows": int(st["nsplit"])})
+    launches = K * sum(r["MF"].gpu_launches_per_spmv for r in mats)
+
+    # the other format, same protocol, reported beside (not the headline)
+    other = None
+    if not args.no_sell:
+        for _ in range(W):
+            one_step("MF2")
+        torch.cuda.synchronize()
+        e0.record()
+        for k in range(K):
+            one_step("MF2", events=ev[k])
+        e1.record()
+        torch.cuda.synchronize()
+        ms2 = e0.elapsed_time(e1) / K
+        other = {"format": mats[0]["MF2"].format_name, "ms_per_step": round(ms2, 5), "gflops": round(2.0 * tot_nnz / ms2 * 1e-6, 1),
+                 "eff_GBs": round(tot_bc / ms2 * 1e-6, 1),
+                 "per_matrix_ms": [round(float(np.mean([ev[k][i][0].elapsed_time(ev[k][i][1]) for k in range(K)])), 5) for i in range(len(mats))]}
+
+    # end to end through the reference-facing call with host buffers: H2D x + kernel + D2H y + sync per call
+    hx, hy = [], []
+    for r in mats:
+        tx = torch.from_numpy(r["x_h"]).pin_memory()
+        ty = torch.full((r["m"] + 64,), 1.0, dtype=torch.float64).pin_memory()
+        hx.append(tx.numpy())
+        hy.append(ty.numpy())
+        r["_pin"] = (tx, ty)
+    for r, x, y in zip(mats, hx, hy):
+        r["MF"].spmv(x, y)
+    Ke = max(3, min(K, 10))
+    t0 = time.perf_counter()
+    for _ in range(Ke):
+        for r, x, y in zip(mats, hx, hy):
+            r["MF"].spmv(x, y)
+    te = (time.perf_counter() - t0) / Ke
+    e2e = {"value": round(2.0 * tot_nnz / te * 1e-9, 2), "unit": "GFLOP/s", "h2d_bytes_per_step": int(sum(8 * r["n"] for r in mats)),
+           "d2h_bytes_per_step": int(sum(8 * r["m"] for r in mats)), "ms_per_step": round(te * 1e3, 4),
+           "call": "Matrix_Format::spmv(x, y) via b200spmv_spmv_host, pinned host x / y"}
+
+    out = {
+        "metric": METRIC, "value": round(gflops, 2), "unit": "GFLOP/s", "n_gpus": 1, "steps": K, "warmup": W,
+        "ms_per_step": round(ms_step, 5), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic (reference artificial-matrix-generator restated bit-exactly, seed 14), x = %s" % args.x,
+        "config": {"workload": wl, "format": mats[0]["MF"].format_name, "matrices": len(mats), "total_nnz": int(tot_nnz),
+                   "compulsory_bytes_per_step": int(tot_bc),
+                   "l2_note": "every matrix >= 320 MB CSR (> 126 MB L2) and a step streams %.1f GB, so nothing of a matrix survives "
+                              "in L2 between its uses; no explicit flush" % (tot_bc * 1e-9),
+                   "generate_s": round(t_gen, 1)},
+        "effective_GBs": round(eff, 1), "roofline_frac_nominal_8TBs": round(eff / NOMINAL_HBM_GBS, 4),
+        "roofline": {"bound": "hbm", "kernel": "csr_tile_kernel" if fmt == S.CSR_ADAPTIVE else "sell_kernel",
+                     "achieved": round(tot_bc / kern_ms * 1e-6, 1), "peak": peak, "unit": "GB/s",
+                     "frac": round(tot_bc / kern_ms * 1e-6 / peak, 4), "traffic": None, "peak_source": peak_src,
+                     "achieved_def": "compulsory bytes B_c = 12 nnz + 12 m + 8 n + 4 per SpMV / CUDA-event time of that SpMV, summed over the sample"},
+        "e2e": e2e, "gpu_launches": int(launches), "clocks": clk.summary(), "per_matrix": per, "other_format": other,
+    }
+    if not args.no_cpu_baseline and cpu["t"] > 0:
+        out["cpu_baseline"] = {"value": round(cpu["flops"] / cpu["t"] * 1e-9, 3), "unit": "GFLOP/s", "cores": cpu["cores"], "kind": cpu["kind"],
+                               "sample": "every matrix of the workload, 1 warm-up + %d timed calls each of the OpenMP CSR kernel" % cpu["iters"],
+                               "parity_max_err_over_bound": cpu["max_err_over_bound"]}
+    emit(out)
+
+
+# ------------------------------------------------------------------------------------------------
+# N >= 1 under torchrun: row-sharded power iteration, one process per GPU
+# ------------------------------------------------------------------------------------------------
+def run_power(args):
+    import torch
+    import torch.distributed as dist
+    import spmv_research_b200 as S
+    from spmv_research_b200 import amg, capi, harness as H, power
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+    fmt = S.CSR_ADAPTIVE if args.format == "csr" else S.SELL_C_SIGMA
+    peak, peak_src = measured_peak()
+    p = H.config5(world, args.rows_per_gpu)
+
+    # every rank runs pass 1 (row lengths; cheap, deterministic), then generates only its own rows
+    t0 = time.time()
+    rp, bw = amg.row_ptr(p)
+    m, n, nnz = p.rows, p.cols, int(rp[-1])
+    capi.check(capi.lib().b200spmv_set_device(local))
+    bounds = power.shard_bounds(rp, m, nnz, world, capi.partition)        # reference partitioner, on the GPU
+    i_s, i_e = int(bounds[rank, 0]), int(bounds[rank, 1])
+    col, val = amg.fill(p, rp, bw, i_s, i_e)
+    t_gen = time.time() - t0
+    rp_loc = (rp[i_s:i_e + 1] - rp[i_s]).astype(np.int32)
+    nnz_loc = int(rp_loc[-1])
+    MF = S.csr_to_format(rp_loc, col, val, i_e - i_s, n, nnz_loc, 0, 0, format=fmt, device=local)
+    del col, val
+
+    def local_spmv(cur, slot, scale, norm2, parity):
+        MF.spmv_device(cur, slot, stream, scale=scale, norm2=norm2)
+
+    it = power.ShardedPowerIteration(n, bounds, rank, world, local_spmv, dev, exchange="nccl")
+    it.set_start(np.ones(n))
+    K, W = args.steps, max(args.warmup, 3)
+    for _ in range(W):
+        it.step()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    # kernel-only time of the local shard (no exchange), for the roofline entry
+    torch.cuda.synchronize()
+    k0.record()
+    for _ in range(5):
+        MF.spmv_device(it.cur, it.nxt[i_s:i_e], stream)
+    k1.record()
+    torch.cuda.synchronize()
+    kern_ms = k0.elapsed_time(k1) / 5
+    it.set_start(np.ones(n))
+    for _ in range(W):
+        it.step()
+    with ClockSampler(local) as clk:
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(K):
+            it.step()
+        e1.record()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    kms = torch.tensor([kern_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(kms, op=dist.ReduceOp.MAX)
+    ms_step = float(ms.item()) / K
+    eig = it.eigenvalue()
+
+    # end to end through the host-vector call: this rank's shard product with x from pinned host memory, y back to the host
+    tx = torch.ones(n, dtype=torch.float64).pin_memory()
+    ty = torch.ones(i_e - i_s + 64, dtype=torch.float64).pin_memory()
+    MF.spmv(tx.numpy(), ty.numpy())
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    Ke = 5
+    for _ in range(Ke):
+        MF.spmv(tx.numpy(), ty.numpy())
+    te = torch.tensor([(time.perf_counter() - t0) / Ke], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    te = float(te.item())
+
+    if rank == 0:
+        bc = H.compulsory_bytes(m, n, nnz)
+        bc_loc = H.compulsory_bytes(i_e - i_s, n, nnz_loc)
+        gflops = 2.0 * nnz / (ms_step * 1e-3) * 1e-9
+        out = {
+            "metric": METRIC, "value": round(gflops, 2), "unit": "GFLOP/s", "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": round(ms_step, 5), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic (reference artificial-matrix-generator restated bit-exactly, seed 14), power iteration from x = 1",
+            "config": {"workload": "power_iteration config5-series: %s" % p.line(), "format": MF.format_name, "rows_per_gpu": args.rows_per_gpu,
+                       "total_nnz": int(nnz), "shard_rows": [int(b[1] - b[0]) for b in bounds], "exchange": "NCCL in-place all-gather of y slots (one broadcast per owner) + scalar all-reduce",
+                       "l2_note": "each shard is %.1f GB (> 126 MB L2); no explicit flush" % (bc_loc * 1e-9), "generate_s": round(t_gen, 1)},
+            "effective_GBs": round(bc / (ms_step * 1e-3) * 1e-9, 1),
+            "roofline_frac_nominal_8TBs": round(bc / (ms_step * 1e-3) * 1e-9 / (NOMINAL_HBM_GBS * world), 4),
+            "roofline": {"bound": "hbm", "kernel": "csr_tile_kernel" if fmt == S.CSR_ADAPTIVE else "sell_kernel",
+                         "achieved": round(bc_loc / float(kms.item()) * 1e-6, 1), "peak": peak, "unit": "GB/s",
+                         "frac": round(bc_loc / float(kms.item()) * 1e-6 / peak, 4), "traffic": None, "peak_source": peak_src,
+                         "achieved_def": "rank-0 shard compulsory bytes / slowest rank's kernel-only SpMV time (CUDA events, 5 launches)"},
+            "e2e": {"value": round(2.0 * nnz / te * 1e-9, 2), "unit": "GFLOP/s", "h2d_bytes_per_step": int(8 * n * world),
+                    "d2h_bytes_per_step": int(8 * m), "ms_per_step": round(te * 1e3, 4),
+                    "call": "per rank Matrix_Format::spmv(x, y) on its row shard, pinned host x / y, max over ranks"},
+            "gpu_launches": int(K * (MF.gpu_launches_per_spmv + 1)), "clocks": clk.summary(), "eigenvalue_estimate": eig,
+        }
+        emit(out)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# ------------------------------------------------------------------------------------------------
+# reference arm: the reference's CPU CSR kernel on the host cores, same workload definition
+# ------------------------------------------------------------------------------------------------
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if rank != 0:
+        return
+    from spmv_research_b200 import amg, harness as H
+    wl, plist = workload_params(args, world)
+    K, W = args.steps, args.warmup
+    items, sample = [], ""
+    if wl == "power":
+        p = plist[0]
+        rp, bw = amg.row_ptr(p)
+        from oracle import oracle as O
+        b = O.partition(world, rp, p.rows, int(rp[-1]))
+        i_s, i_e = int(b[0, 0]), int(b[0, 1])
+        col, val = amg.fill(p, rp, bw, i_s, i_e)
+        items.append(((rp[i_s:i_e + 1] - rp[i_s]).astype(np.int32), col, val, p.cols))
+        sample = "rank-0 row shard (1/%d of the rows, nnz-balanced) of %s; one SpMV per step" % (world, p.line())
+    else:
+        for p in plist:
+            rp, col, val = amg.generate(p)
+            items.append((rp, col, val, p.cols))
+        sample = "every matrix of the %s workload, one SpMV each per step" % wl
+    runners, cores, kind = [], 0, "port"
+    for rp, col, val, n in items:
+        run, kind, cores = cpu_csr_runner(rp, col, val, n)
+        runners.append((run, np.ones(n), np.full(len(rp) - 1, 1.0), int(rp[-1])))
+    for _ in range(max(W, 1)):
+        for run, x, y, nnz in runners:
+            run(x, y)
+    t0 = time.perf_counter()
+    for _ in range(K):
+        for run, x, y, nnz in runners:
+            run(x, y)
+    t = (time.perf_counter() - t0) / K
+    flops = sum(2.0 * r[3] for r in runners)
+    val_ = round(flops / t * 1e-9, 3)
+    emit({"impl": "reference", "metric": METRIC, "value": val_, "unit": "GFLOP/s", "n_gpus": world, "steps": K, "warmup": W,
+          "ms_per_step": round(t * 1e3, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+          "data": "synthetic (same generator and parameter lines as the b200 arm)",
+          "config": {"workload": wl, "format": "Custom_CSR_B (reference OpenMP CSR, K/csr.cpp)"},
+          "cpu_baseline": {"value": val_, "unit": "GFLOP/s", "cores": cores, "kind": kind, "sample": sample},
+          "e2e": {"value": val_, "unit": "GFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world > 1 or args.workload == "power":
+        return run_power(args)
+    return run_single(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,308 @@
+"""Parity tests proper: the CUDA path, called through the C-ABI, against the CPU oracle.
+
+Bar (BASELINE.json north_star): integer outputs bit-exact; y within
+|y - y_ref| <= 1e-12 * sum_j |a_ij x_j| per row of the serial CSR kernel.
+"""
+import numpy as np
+import pytest
+
+import matrices as M
+from tests.golden.make_golden import MERGE_T, PART_W, SELL_CFG
+
+pytestmark = pytest.mark.gpu
+REL = 1e-12
+
+
+@pytest.fixture(scope="module")
+def S(native):
+    import spmv_research_b200 as S
+    if S.capi.device_count() < 1:
+        pytest.fail("no CUDA device visible: the gpu-marked tests must run on a B200")
+    return S
+
+
+def _spmv(S, fmt_kwargs, rp, col, val, n, x):
+    m = len(rp) - 1
+    MF = S.csr_to_format(rp, col, val, m, n, int(rp[-1]), 0, 0, **fmt_kwargs)
+    y = np.full(m + 64, 1.0)               # the harness pre-fills y with 1.0 and over-allocates (bench_spmv.cpp:598-609)
+    MF.spmv(x, y)
+    assert np.all(y[m:] == 1.0), "wrote past y[m]"
+    return MF, y[:m]
+
+
+def _check(oracle, rp, col, val, x, y, what):
+    yr = oracle.csr_spmv(rp, col, val, x)
+    bound = oracle.row_abs_bound(rp, col, val, x)
+    err = np.abs(y - yr)
+    bad = np.nonzero(~(err <= REL * bound))[0]
+    assert bad.size == 0, "%s: %d rows off, first row %d: got %r want %r bound %r" % (
+        what, bad.size, bad[0], y[bad[0]], yr[bad[0]], bound[bad[0]])
+
+
+CSR_VARIANTS = [dict(csr_nnz_per_thread=8), dict(csr_nnz_per_thread=16), dict(csr_nnz_per_thread=32),
+                dict(csr_nnz_per_thread=8, csr_ext=64), dict(csr_nnz_per_thread=8, x_hint=1)]
+
+
+# ------------------------------------------------------------------------------------------ CSR
+def test_csr_generator_matrices(S, oracle, golden, golden_matrices):
+    for li, (p, rp, col, val) in enumerate(golden_matrices):
+        for x in (np.ones(p.cols), M.rand_x(p.cols)):
+            for kw in CSR_VARIANTS:
+                MF, y = _spmv(S, dict(format=S.CSR_ADAPTIVE, **kw), rp, col, val, p.cols, x)
+                _check(oracle, rp, col, val, x, y, "%s %r" % (M.GOLDEN_LINES[li], kw))
+                MF.close()
+        # and against the reference's own y (golden fixture made from K/csr.cpp)
+        x = M.rand_x(p.cols)
+        MF, y = _spmv(S, dict(format=S.CSR_ADAPTIVE), rp, col, val, p.cols, x)
+        bound = oracle.row_abs_bound(rp, col, val, x)
+        assert np.all(np.abs(y[::7] - golden["g%d_y_sample" % li]) <= REL * bound[::7])
+
+
+def test_csr_edge_cases(S, oracle):
+    for name, rp, col, val, n in M.edge_cases():
+        for x in (np.ones(n), M.rand_x(n, 3)):
+            for kw in CSR_VARIANTS:
+                MF, y = _spmv(S, dict(format=S.CSR_ADAPTIVE, **kw), rp, col, val, n, x)
+                _check(oracle, rp, col, val, x, y, "%s %r" % (name, kw))
+                lens = np.diff(rp)
+                assert np.all(y[lens == 0] == 0.0), name          # empty rows are written 0
+                MF.close()
+
+
+def test_csr_split_rows_and_tile_plan(S, oracle):
+    """The tile plan against a numpy model: first owned row per tile, split rows = rows leaving their
+    owner window by more than ext; giant rows take the fix-up launch."""
+    for name, rp, col, val, n in M.edge_cases():
+        m, nnz = len(rp) - 1, int(rp[-1])
+        for npt, ext in ((8, 64), (8, 1024), (16, 2048)):
+            T = 256 * npt
+            MF = S.csr_to_format(rp, col, val, m, n, nnz, format=S.CSR_ADAPTIVE, csr_nnz_per_thread=npt, csr_ext=ext)
+            ntiles = max(1, -(-nnz // T))
+            want = np.minimum(np.searchsorted(rp, np.arange(ntiles) * T, side="left"), m).astype(np.int32)
+            want[0] = 0
+            want = np.append(want, m).astype(np.int32)
+            got = MF.handle.export(S.capi.X_TILE_ROW)
+            assert np.array_equal(got, want), (name, npt)
+            split_rows, split_tiles = [], []
+            for t in range(ntiles):
+                r0, r1 = want[t], want[t + 1]
+                if r1 > r0 and int(rp[r1]) - (t + 1) * T > ext:
+                    split_rows.append(r1 - 1)
+                    split_tiles.append(t)
+            assert np.array_equal(MF.handle.export(S.capi.X_SPLIT_ROW), np.array(split_rows, np.int32)), (name, npt, ext)
+            assert np.array_equal(MF.handle.export(S.capi.X_SPLIT_TILE), np.array(split_tiles, np.int32))
+            assert MF.gpu_launches_per_spmv == (2 if split_rows else 1)
+            MF.close()
+
+
+def test_csr_deterministic_and_repeatable(S, golden_matrices):
+    p, rp, col, val = golden_matrices[3]                       # giant-row head: exercises the fix-up path
+    x = M.rand_x(p.cols)
+    MF = S.csr_to_format(rp, col, val, p.rows, p.cols, int(rp[-1]), csr_ext=64)
+    assert MF.gpu_launches_per_spmv == 2
+    ys = []
+    for _ in range(3):
+        y = np.full(p.rows, 1.0)
+        MF.spmv(x, y)
+        ys.append(y)
+    assert np.array_equal(ys[0], ys[1]) and np.array_equal(ys[0], ys[2])      # no atomics: bit-reproducible
+
+
+def test_csr_short_rows_bit_exact_summation_order(S, oracle):
+    """Thread-per-row bins add the products in ascending j like subkernel_csr_scalar; without FMA
+    contraction on the CPU side that is bit-identical."""
+    name, rp, col, val, n = M.edge_cases()[4]
+    x = M.rand_x(n)
+    MF, y = _spmv(S, dict(format=S.CSR_ADAPTIVE, csr_nnz_per_thread=8), rp, col, val, n, x)
+    seq = np.zeros(len(rp) - 1)
+    for i in range(len(rp) - 1):
+        s = 0.0
+        for j in range(rp[i], rp[i + 1]):
+            s += val[j] * x[col[j]]
+        seq[i] = s
+    full = rp[:-1] < (int(rp[-1]) // 2048) * 2048          # rows owned by tiles that are full (> 128 rows each here)
+    assert full.sum() > 4000 and np.array_equal(y[full], seq[full])
+
+
+# ------------------------------------------------------------------------------------------ SELL-C-sigma
+def test_sell_conversion_bit_exact(S, oracle, golden, golden_matrices):
+    keys = ((S.capi.X_ROW_ORDER, "row_order"), (S.capi.X_SLICE_WIDTH, "slice_width"), (S.capi.X_SLICE_PTR, "slice_ptr"),
+            (S.capi.X_SELL_COL, "col"), (S.capi.X_SELL_VAL, "val"))
+    for li, (p, rp, col, val) in enumerate(golden_matrices):
+        for (C_, sg) in SELL_CFG:
+            MF = S.csr_to_format(rp, col, val, p.rows, p.cols, int(rp[-1]), format=S.SELL_C_SIGMA, sell_C=C_, sell_sigma=sg)
+            O = oracle.sellcs_convert(rp, col, val, C_, sg)
+            fnv = []
+            for sel, k in keys:
+                got = MF.handle.export(sel)
+                assert np.array_equal(got, O[k]), (M.GOLDEN_LINES[li], C_, sg, k)
+                fnv.append(oracle.fnv1a64(got))
+            assert np.array_equal(np.array(fnv, np.uint64), golden["g%d_sell_%d_%d" % (li, C_, sg)])   # = the reference library's output
+            MF.close()
+
+
+def test_sell_conversion_edge_cases(S, oracle):
+    for name, rp, col, val, n in M.edge_cases():
+        m = len(rp) - 1
+        for (C_, sg) in ((32, 16384), (2, 2), (8, 24), (256, 256), (64, 8192)):
+            MF = S.csr_to_format(rp, col, val, m, n, int(rp[-1]), format=S.SELL_C_SIGMA, sell_C=C_, sell_sigma=sg)
+            O = oracle.sellcs_convert(rp, col, val, C_, sg)
+            for sel, k in ((S.capi.X_ROW_ORDER, "row_order"), (S.capi.X_SLICE_WIDTH, "slice_width"), (S.capi.X_SLICE_PTR, "slice_ptr"),
+                           (S.capi.X_SELL_COL, "col"), (S.capi.X_SELL_VAL, "val")):
+                assert np.array_equal(MF.handle.export(sel), O[k]), (name, C_, sg, k)
+            for x in (np.ones(n), M.rand_x(n, 5)):
+                y = np.full(m, 1.0)
+                MF.spmv(x, y)
+                _check(oracle, rp, col, val, x, y, "sell %s C=%d sigma=%d" % (name, C_, sg))
+                assert np.array_equal(y, oracle.sellcs_spmv(O, x)), name      # same fma chain per lane -> bit-equal
+            MF.close()
+
+
+def test_sell_spmv_generator_matrices(S, oracle, golden_matrices):
+    for (p, rp, col, val) in golden_matrices:
+        for x in (np.ones(p.cols), M.rand_x(p.cols)):
+            for kw in (dict(), dict(sell_C=64, sell_sigma=4096), dict(sell_C=4, sell_sigma=64, x_hint=1)):
+                MF, y = _spmv(S, dict(format=S.SELL_C_SIGMA, **kw), rp, col, val, p.cols, x)
+                _check(oracle, rp, col, val, x, y, "sell %r" % kw)
+                MF.close()
+
+
+def test_sell_large_sigma_global_sort(S, oracle):
+    """sigma larger than the shared-memory sort block (4096 keys) takes the global bitonic steps."""
+    rng = np.random.default_rng(21)
+    rp, col, val = M.csr_from_lengths(rng.integers(0, 40, 70000), 5000, 21)
+    for sg in (8192, 16384, 65536, 1 << 20):
+        MF = S.csr_to_format(rp, col, val, 70000, 5000, int(rp[-1]), format=S.SELL_C_SIGMA, sell_C=32, sell_sigma=sg)
+        O = oracle.sellcs_convert(rp, col, val, 32, sg)
+        assert np.array_equal(MF.handle.export(S.capi.X_ROW_ORDER), O["row_order"]), sg
+        assert np.array_equal(MF.handle.export(S.capi.X_SLICE_PTR), O["slice_ptr"]), sg
+        MF.close()
+
+
+# ------------------------------------------------------------------------------------------ partitioners
+def test_partition_bit_exact(S, oracle, golden, golden_matrices):
+    for li, (p, rp, col, val) in enumerate(golden_matrices):
+        for W in PART_W:
+            got = S.capi.partition(rp, p.rows, int(rp[-1]), W)
+            assert np.array_equal(got, golden["g%d_part%d" % (li, W)]), (li, W)
+    rng = np.random.default_rng(3)
+    for _ in range(100):
+        m = int(rng.integers(1, 500))
+        rp = np.zeros(m + 1, np.int32)
+        np.cumsum(rng.integers(0, 9, m) * (rng.random(m) < rng.random()), out=rp[1:])
+        rp += int(rng.integers(0, 5))
+        W = int(rng.integers(1, 40))
+        assert np.array_equal(S.capi.partition(rp, m, int(rp[-1] - rp[0]), W), oracle.partition(W, rp, m, int(rp[-1] - rp[0])))
+    with pytest.raises(S.B200Error, match="Empty Sums array"):
+        S.capi.partition(np.zeros(1, np.int32), 0, 0, 2)
+
+
+def test_merge_coords_bit_exact(S, oracle, golden, golden_matrices):
+    for li, (p, rp, col, val) in enumerate(golden_matrices):
+        MF = S.csr_to_format(rp, col, val, p.rows, p.cols, int(rp[-1]))
+        for T in MERGE_T:
+            assert np.array_equal(MF.handle.merge_coords(T), golden["g%d_merge%d" % (li, T)]), (li, T)
+        T = 148 * 4
+        _, want = oracle.merge_csrmv(T, rp, col, val, np.ones(p.cols))
+        assert np.array_equal(MF.handle.merge_coords(T), want)
+        MF.close()
+
+
+# ------------------------------------------------------------------------------------------ device-resident path
+def test_device_path_scale_norm_peers_shard(S, oracle, golden_matrices):
+    import torch
+    p, rp, col, val = golden_matrices[1]
+    dev = torch.device("cuda:0")
+    st = torch.cuda.current_stream().cuda_stream
+    x = M.rand_x(p.cols)
+    dx = torch.from_numpy(x).to(dev)
+    yr = oracle.csr_spmv(rp, col, val, x)
+    bound = oracle.row_abs_bound(rp, col, val, x)
+    for fmt in (S.CSR_ADAPTIVE, S.SELL_C_SIGMA):
+        MF = S.csr_to_format(rp, col, val, p.rows, p.cols, int(rp[-1]), format=fmt)
+        dy = torch.full((p.rows,), 1.0, dtype=torch.float64, device=dev)
+        peers = [torch.zeros(p.rows, dtype=torch.float64, device=dev) for _ in range(3)]
+        scale = torch.tensor([0.5], dtype=torch.float64, device=dev)
+        norm2 = torch.zeros(1, dtype=torch.float64, device=dev)
+        MF.spmv_device(dx, dy, st, scale=scale, norm2=norm2, peers=peers)
+        torch.cuda.synchronize()
+        y = dy.cpu().numpy()
+        assert np.all(np.abs(y - 0.5 * yr) <= REL * bound)
+        for pb in peers:
+            assert torch.equal(pb, dy)
+        assert abs(norm2.item() - float(np.sum(y * y))) <= 1e-12 * float(np.sum(y * y))
+        MF.close()
+    # a row shard built from device arrays with a non-zero row_ptr offset
+    a, b = p.rows // 3, (2 * p.rows) // 3 + 7
+    d_rp = torch.from_numpy(rp[a:b + 1].copy()).to(dev)
+    d_col = torch.from_numpy(col[rp[a]:rp[b]].copy()).to(dev)
+    d_val = torch.from_numpy(val[rp[a]:rp[b]].copy()).to(dev)
+    for fmt in (S.CSR_ADAPTIVE, S.SELL_C_SIGMA):
+        MF = S.csr_to_format_device(d_rp, d_col, d_val, b - a, p.cols, int(rp[b] - rp[a]), format=fmt)
+        dy = torch.full((b - a,), 1.0, dtype=torch.float64, device=dev)
+        MF.spmv_device(dx, dy, st)
+        torch.cuda.synchronize()
+        assert np.all(np.abs(dy.cpu().numpy() - yr[a:b]) <= REL * bound[a:b])
+        MF.close()
+
+
+def test_host_flags_reference_convention(S, oracle, golden_matrices):
+    """cache_x=True follows the reference GPU plugins: x is uploaded on the first call only
+    (GPU_clean/cuda_csr.cu:353-382), so a changed x at the same address is NOT seen."""
+    p, rp, col, val = golden_matrices[0]
+    x = M.rand_x(p.cols)
+    MF = S.csr_to_format(rp, col, val, p.rows, p.cols, int(rp[-1]), cache_x=True)
+    y1, y2 = np.full(p.rows, 1.0), np.full(p.rows, 1.0)
+    MF.spmv(x, y1)
+    x *= 2.0
+    MF.spmv(x, y2)
+    assert np.array_equal(y1, y2)
+    MF2 = S.csr_to_format(rp, col, val, p.rows, p.cols, int(rp[-1]))
+    MF2.spmv(x, y2)
+    assert np.array_equal(y2, 2.0 * y1)
+
+
+def test_bad_options_fail_loudly(S, golden_matrices):
+    p, rp, col, val = golden_matrices[0]
+    SELL = dict(format=S.SELL_C_SIGMA)
+    for kw in (dict(SELL, sell_C=24), dict(SELL, sell_C=512), dict(SELL, sell_C=32, sell_sigma=48), dict(csr_nnz_per_thread=12),
+               dict(csr_ext=100), dict(format=7), dict(device=99)):
+        with pytest.raises(S.B200Error):
+            S.csr_to_format(rp, col, val, p.rows, p.cols, int(rp[-1]), **kw)
+
+
+# ------------------------------------------------------------------------------------------ full sizes
+def test_config1_full_size(S, oracle):
+    """BASELINE config 1 (1M x 1M, nnz 10 038 177): full comparison with the oracle, CSR and SELL,
+    x = 1 (the harness's vector) and random x; plus linearity A(ax + bz) = aAx + bAz."""
+    from spmv_research_b200 import amg
+    p = amg.MatrixParams.parse("1000000 1000000 10 5 normal random 0.3 0 0.5 0.5 14")
+    rp, col, val = amg.generate(p)
+    assert int(rp[-1]) == 10038177
+    x, z = M.rand_x(p.cols, 1), M.rand_x(p.cols, 2)
+    for fmt in (S.CSR_ADAPTIVE, S.SELL_C_SIGMA):
+        MF = S.csr_to_format(rp, col, val, p.rows, p.cols, int(rp[-1]), format=fmt)
+        ys = {}
+        for name, v in (("ones", np.ones(p.cols)), ("x", x), ("z", z), ("lin", 0.75 * x - 1.5 * z)):
+            y = np.full(p.rows, 1.0)
+            MF.spmv(v, y)
+            _check(oracle, rp, col, val, v, y, "config1 %s fmt %d" % (name, fmt))
+            ys[name] = y
+        babs = oracle.row_abs_bound(rp, col, val, np.abs(x) + np.abs(z))
+        assert np.all(np.abs(ys["lin"] - (0.75 * ys["x"] - 1.5 * ys["z"])) <= 4e-12 * babs)
+        MF.close()
+
+
+def test_giant_row_full_size(S, oracle):
+    """G2-style skew at 200k rows (row 0 has 50 100 non-zeros; SURVEY App. C fingerprint line 2)."""
+    from spmv_research_b200 import amg
+    p = amg.MatrixParams.parse("200000 200000 50 16.6667 gamma random 0.6 1000 0.05 0.05 14")
+    rp, col, val = amg.generate(p)
+    assert int(rp[-1]) == 10050050 and int(np.max(np.diff(rp))) == 50100
+    x = M.rand_x(p.cols, 4)
+    for kw in (dict(format=S.CSR_ADAPTIVE), dict(format=S.CSR_ADAPTIVE, csr_nnz_per_thread=32), dict(format=S.SELL_C_SIGMA)):
+        MF, y = _spmv(S, kw, rp, col, val, p.cols, x)
+        _check(oracle, rp, col, val, x, y, "giant %r" % kw)
+        if kw["format"] == S.CSR_ADAPTIVE:
+            assert MF.gpu_launches_per_spmv == 2
+        MF.close()
