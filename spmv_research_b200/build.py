@@ -11,7 +11,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "lib")
 CU_SOURCES = ["capi.cu", "csr_kernel.cu", "sell_kernel.cu", "convert.cu", "partition.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
-              "-Xcompiler", "-fPIC", "-shared", "--cudart", "shared"]
+              "-Xcompiler", "-fPIC", "-shared", "--cudart", "static"]
 
 
 def _stale(target, deps):
