@@ -95,7 +95,7 @@ void b200spmv_destroy(b200spmv_t * h);
 int b200spmv_spmv_host(b200spmv_t * h, const double * x, double * y);
 int b200spmv_spmv_host_ex(b200spmv_t * h, const double * x, double * y, int32_t flags);
 
-/* y = A x with DEVICE vectors on `stream` (a cudaStream_t, NULL = the handle's own stream); asynchronous. */
+/* y = A x with DEVICE vectors on `stream` (a cudaStream_t; NULL = the CUDA legacy default stream); asynchronous. */
 int b200spmv_spmv_device(b200spmv_t * h, const double * dx, double * dy, void * stream);
 int b200spmv_spmv_device_ex(b200spmv_t * h, const double * dx, double * dy, void * stream, const b200spmv_launch * launch);
 

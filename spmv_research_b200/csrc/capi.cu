@@ -213,7 +213,7 @@ extern "C" int b200spmv_spmv_device_ex(b200spmv_t * h, const double * dx, double
 {
 	if (!h || !dx || !dy)
 		B200_FAIL("NULL argument");
-	cudaStream_t st = stream ? (cudaStream_t) stream : h->stream;
+	cudaStream_t st = (cudaStream_t) stream;       // NULL is the CUDA legacy default stream (what torch's default stream is)
 	if (h->format == B200SPMV_CSR_ADAPTIVE)
 		return launch_csr_spmv(h, dx, dy, st, launch);
 	return launch_sell_spmv(h, dx, dy, st, launch);

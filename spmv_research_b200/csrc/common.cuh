@@ -36,11 +36,18 @@ constexpr int SELL_ROWS_PER_CTA = 2 * SELL_THREADS;
 
 // ---------------------------------------------------------------------------------------------
 // Blackwell load helpers.
-//  * matrix streams (values / col_ind): read exactly once -> 256-bit non-coherent loads that do
-//    not allocate in L1 and are marked evict-first in L2 (SASS: LDG.E.NA.EFL2.256.CONSTANT), so
-//    they do not push x out of the 126 MB L2.
+//  * matrix streams (values / col_ind): read exactly once -> non-coherent loads that do not
+//    allocate in L1 (SASS: LDG.E.NA...CONSTANT) and carry an L2 evict-first policy, so they do
+//    not push x out of the 126 MB L2.  (256-bit variants, LDG.E.NA.EFL2.256, are kept for probes.)
 //  * x gathers: L1-allocating loads with an L2 evict_last cache hint (LDG.E.EL.64.CONSTANT).
 // ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t make_policy_evict_first()
+{
+	uint64_t pol;
+	asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+	return pol;
+}
+
 struct i32x8 { int v[8]; };
 struct f64x4 { double v[4]; };
 
@@ -62,33 +69,34 @@ __device__ __forceinline__ f64x4 ld_stream_f64x4(const double * p)
 	return r;
 }
 
-__device__ __forceinline__ double2 ld_stream_f64x2(const double * p)
+__device__ __forceinline__ double2 ld_stream_f64x2(const double * p, uint64_t pol)
 {
 	double2 r;
-	asm volatile("ld.global.nc.L1::no_allocate.v2.f64 {%0,%1}, [%2];" : "=d"(r.x), "=d"(r.y) : "l"(p));
+	asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.f64 {%0,%1}, [%2], %3;" : "=d"(r.x), "=d"(r.y) : "l"(p), "l"(pol));
 	return r;
 }
 
-__device__ __forceinline__ int2 ld_stream_i32x2(const int32_t * p)
+__device__ __forceinline__ int2 ld_stream_i32x2(const int32_t * p, uint64_t pol)
 {
 	int2 r;
-	asm volatile("ld.global.nc.L1::no_allocate.v2.s32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p));
+	asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.s32 {%0,%1}, [%2], %3;" : "=r"(r.x), "=r"(r.y) : "l"(p), "l"(pol));
 	return r;
 }
 
-__device__ __forceinline__ double ld_stream_f64(const double * p)
+__device__ __forceinline__ double ld_stream_f64(const double * p, uint64_t pol)
 {
 	double r;
-	asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];" : "=d"(r) : "l"(p));
+	asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(r) : "l"(p), "l"(pol));
 	return r;
 }
 
-__device__ __forceinline__ int ld_stream_i32(const int32_t * p)
+__device__ __forceinline__ int ld_stream_i32(const int32_t * p, uint64_t pol)
 {
 	int r;
-	asm volatile("ld.global.nc.L1::no_allocate.s32 %0, [%1];" : "=r"(r) : "l"(p));
+	asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.s32 %0, [%1], %2;" : "=r"(r) : "l"(p), "l"(pol));
 	return r;
 }
+
 
 __device__ __forceinline__ uint64_t make_policy_evict_last()
 {

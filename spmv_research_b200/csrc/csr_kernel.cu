@@ -4,12 +4,16 @@
 // y[i] = sum_j a[j] * x[ja[j]], every row written, empty rows -> 0), laid out for B200:
 //
 //  * the nnz stream is cut into fixed windows ("tiles") of T = 256 * NPT non-zeros, one CTA per
-//    tile, so every values / col_ind load is a 32-byte-aligned, fully coalesced 256-bit streaming
-//    load (LDG.E.NA.EFL2.256) regardless of the row-length distribution -- the nnz-balanced
-//    decomposition of merge-path (K/merge.cpp:256-318) with the row search done once at convert
-//    time (tile_info);
-//  * all stream loads of a tile are issued before the first x gather (8-32 independent 32-byte
-//    loads per thread), products go to shared memory through a conflict-free XOR swizzle;
+//    tile, so every values / col_ind load is aligned and fully coalesced regardless of the
+//    row-length distribution -- the nnz-balanced decomposition of merge-path
+//    (K/merge.cpp:256-318) with the row search done once at convert time (tile_info);
+//  * lane l of a warp takes non-zero 32*k + l of the warp's share ("lane-consecutive"): measured
+//    on B200 (tools/hbm_probe.cu, profiles/) the x gather is limited to one 128-byte L1 wavefront
+//    per clock per SM, and a warp-wide gather costs one wavefront per DISTINCT line, so putting
+//    the neighbouring non-zeros of a row (clustered columns, similar adjacent rows) into ONE
+//    gather instruction is worth up to 1.6x over giving a thread 8 consecutive non-zeros;
+//  * all 2*NPT stream loads of a thread are issued before the first x gather (L1 no-allocate,
+//    L2 evict-first policy), products go to shared memory with conflict-free 64-bit stores;
 //  * a row belongs to the tile in which it STARTS.  The owner finishes the row even when it
 //    leaves the window, by loading up to EXT further non-zeros ("tail extension"), so ordinary
 //    matrices need one launch and no carry fix-up.  Only rows sticking out by more than EXT
@@ -21,7 +25,7 @@
 //    reduction (long rows), whole CTA for split-row partials.
 #include "common.cuh"
 
-__device__ __forceinline__ int swz(int j) { return j ^ (((j >> 4) & 3) << 1); }
+__device__ __forceinline__ int swz(int j) { return j; }      // products are stored in nnz order
 
 __device__ __forceinline__ double block_sum_range(const double * s_prod, int a, int b, double * s_red)
 {
@@ -48,7 +52,6 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
                 int64_t nnz, int ext_cap, YOut out)
 {
 	constexpr int T = CSR_THREADS * NPT;
-	constexpr int CHUNKS = NPT / 8;
 	extern __shared__ __align__(16) double s_prod[];      // T + ext_cap products
 	__shared__ double s_red[CSR_THREADS / 32];
 
@@ -56,16 +59,16 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 	const int64_t tile = blockIdx.x;
 	const int64_t base = tile * (int64_t) T;
 	const uint64_t pol = make_policy_evict_last();
+	const uint64_t pol_stream = make_policy_evict_first();
 
-	// 1. all streaming loads of the window, issued back to back
-	i32x8 c[CHUNKS];
-	f64x4 v0[CHUNKS], v1[CHUNKS];
+	// 1. all streaming loads of the window, issued back to back (lane-consecutive, coalesced)
+	int c[NPT];
+	double v[NPT];
 	#pragma unroll
-	for (int k = 0; k < CHUNKS; k++) {
-		const int64_t idx = base + k * (CSR_THREADS * 8) + tid * 8;
-		c[k] = ld_stream_i32x8(col + idx);
-		v0[k] = ld_stream_f64x4(val + idx);
-		v1[k] = ld_stream_f64x4(val + idx + 4);
+	for (int k = 0; k < NPT; k++) {
+		const int64_t idx = base + k * CSR_THREADS + tid;
+		c[k] = ld_stream_i32(col + idx, pol_stream);
+		v[k] = ld_stream_f64(val + idx, pol_stream);
 	}
 
 	// 2. tile bookkeeping (independent of the stream loads)
@@ -82,27 +85,19 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 	const bool tail_split = (nrows > 0) && (over > ext_cap);
 	const double scale = out.scale ? *out.scale : 1.0;
 
-	// 3. gathers and products -> shared memory (swizzled 16-byte units, conflict-free STS.128)
+	// 3. gathers and products -> shared memory in nnz order (conflict-free STS.64)
 	#pragma unroll
-	for (int k = 0; k < CHUNKS; k++) {
-		double p[8];
-		#pragma unroll
-		for (int e = 0; e < 4; e++) {
-			p[e] = v0[k].v[e] * ld_x<HINT>(x + c[k].v[e], pol);
-			p[4 + e] = v1[k].v[e] * ld_x<HINT>(x + c[k].v[4 + e], pol);
-		}
-		const int j0 = k * (CSR_THREADS * 8) + tid * 8;
-		const int s = (tid >> 1) & 3;
-		#pragma unroll
-		for (int u = 0; u < 4; u++)
-			*reinterpret_cast<double2 *>(&s_prod[j0 + 2 * (u ^ s)]) = make_double2(p[2 * u], p[2 * u + 1]);
-	}
+	for (int k = 0; k < NPT; k++)
+		v[k] *= ld_x<HINT>(x + c[k], pol);
+	#pragma unroll
+	for (int k = 0; k < NPT; k++)
+		s_prod[k * CSR_THREADS + tid] = v[k];
 
 	// 4. tail extension: finish the last owned row past the window end
 	if (nrows > 0 && over > 0 && !tail_split) {
 		for (int j = tid; j < (int) over; j += CSR_THREADS) {
 			const int64_t idx = base + T + j;
-			s_prod[swz(T + j)] = ld_stream_f64(val + idx) * ld_x<HINT>(x + ld_stream_i32(col + idx), pol);
+			s_prod[T + j] = ld_stream_f64(val + idx, pol_stream) * ld_x<HINT>(x + ld_stream_i32(col + idx, pol_stream), pol);
 		}
 	}
 	__syncthreads();

@@ -19,6 +19,7 @@ sell_kernel(const int32_t * __restrict__ row_order, const int32_t * __restrict__
 {
 	__shared__ double s_red[SELL_THREADS / 32];
 	const uint64_t pol = make_policy_evict_last();
+	const uint64_t pol_stream = make_policy_evict_first();
 	const int64_t q = (int64_t) blockIdx.x * SELL_THREADS + threadIdx.x;
 	const int64_t r0 = 2 * q;
 	double nrm = 0.0;
@@ -33,8 +34,8 @@ sell_kernel(const int32_t * __restrict__ row_order, const int32_t * __restrict__
 			int2 c[4];
 			#pragma unroll
 			for (int u = 0; u < 4; u++) {
-				v[u] = ld_stream_f64x2(sval + p + (int64_t) u * C);
-				c[u] = ld_stream_i32x2(scol + p + (int64_t) u * C);
+				v[u] = ld_stream_f64x2(sval + p + (int64_t) u * C, pol_stream);
+				c[u] = ld_stream_i32x2(scol + p + (int64_t) u * C, pol_stream);
 			}
 			#pragma unroll
 			for (int u = 0; u < 4; u++) {
@@ -44,8 +45,8 @@ sell_kernel(const int32_t * __restrict__ row_order, const int32_t * __restrict__
 			p += 4 * (int64_t) C;
 		}
 		for (; k < w; k++) {
-			const double2 v = ld_stream_f64x2(sval + p);
-			const int2 c = ld_stream_i32x2(scol + p);
+			const double2 v = ld_stream_f64x2(sval + p, pol_stream);
+			const int2 c = ld_stream_i32x2(scol + p, pol_stream);
 			acc0 = fma(v.x, ld_x<HINT>(x + c.x, pol), acc0);
 			acc1 = fma(v.y, ld_x<HINT>(x + c.y, pol), acc1);
 			p += C;

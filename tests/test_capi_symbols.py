@@ -34,7 +34,7 @@ def test_b200amg_exports_all_declared_symbols(native):
 
 
 def test_sm100a_only_and_blackwell_loads(native):
-    """The cubin inside the library is sm_100a and carries the 256-bit evict-first streaming loads."""
+    """The cubin inside the library is sm_100a and carries the cache-hinted streaming / gather loads."""
     import shutil
     import subprocess
     from spmv_research_b200 import capi
@@ -45,7 +45,7 @@ def test_sm100a_only_and_blackwell_loads(native):
     archs = set(re.findall(r"sm_\d+a?", lst))
     assert archs == {"sm_100a"}, archs
     sass = subprocess.run([cuobjdump, "-sass", capi.SO_PATH], capture_output=True, text=True).stdout
-    assert "LDG.E.NA.EFL2.256" in sass            # 256-bit, L1 no-allocate, L2 evict-first matrix streams
+    assert "LDG.E.NA.64.CONSTANT" in sass         # L1 no-allocate streaming loads of the matrix arrays
     assert "LDG.E.EL.64.CONSTANT" in sass         # x gathers with the evict-last hint
 
 
