@@ -118,12 +118,16 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-sell", action="store_true")
     ap.add_argument("--x", default="ones", choices=["ones", "random"])
+    ap.add_argument("--line", default=None, help="one generator parameter line to use as the N=1 workload (profiling)")
     return ap.parse_args()
 
 
 def workload_params(args, world):
     from spmv_research_b200 import harness as H
     wl = args.workload
+    if args.line:
+        from spmv_research_b200 import amg
+        return "line", [amg.MatrixParams.parse(args.line)]
     if wl == "auto":
         wl = "power" if world > 1 else "medium_sample"
     if wl == "medium_sample":
