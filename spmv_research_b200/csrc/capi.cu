@@ -63,7 +63,7 @@ static int validate_opts(const b200spmv_opts * in, b200spmv_opts * o, int64_t m,
 	if (o->csr_nnz_per_thread != 8 && o->csr_nnz_per_thread != 16 && o->csr_nnz_per_thread != 32)
 		B200_FAIL("csr_nnz_per_thread must be 8, 16 or 32");
 	if (o->csr_ext == 0)
-		o->csr_ext = (o->csr_nnz_per_thread == 8) ? 1024 : 2048;
+		o->csr_ext = (o->csr_nnz_per_thread <= 8) ? 256 : 2048;     // shared memory comes out of the L1 the x gathers live in
 	if (o->csr_ext < 64 || o->csr_ext % 64 || o->csr_ext > 8192)
 		B200_FAIL("csr_ext must be a multiple of 64 in [64, 8192]");
 	return 0;

@@ -45,7 +45,7 @@ __device__ __forceinline__ double block_sum_range(const double * s_prod, int a, 
 }
 
 template <int NPT, bool HINT>
-__global__ void __launch_bounds__(CSR_THREADS, (NPT <= 8) ? 4 : ((NPT <= 16) ? 3 : 2))
+__global__ void __launch_bounds__(CSR_THREADS, (NPT <= 8) ? 6 : ((NPT <= 16) ? 3 : 2))
 csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict__ col, const double * __restrict__ val,
                 const int2 * __restrict__ tile_info, const double * __restrict__ x,
                 double * __restrict__ tile_head, double * __restrict__ tile_tail,
@@ -54,6 +54,7 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 	constexpr int T = CSR_THREADS * NPT;
 	extern __shared__ __align__(16) double s_prod[];      // T + ext_cap products
 	__shared__ double s_red[CSR_THREADS / 32];
+	__shared__ int s_rp[CSR_THREADS + 1];                 // window-relative row_ptr of the first 256 owned rows
 
 	const int tid = threadIdx.x;
 	const int64_t tile = blockIdx.x;
@@ -84,18 +85,44 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 	const int64_t over = end_own - (base + T);          // > 0: the last owned row leaves the window
 	const bool tail_split = (nrows > 0) && (over > ext_cap);
 	const double scale = out.scale ? *out.scale : 1.0;
+	int rp_pre = 0, rp_pre2 = 0;
+	const int npre = nrows < CSR_THREADS ? nrows : CSR_THREADS;
+	const bool do_ext = (nrows > 0 && over > 0 && !tail_split);
+	int ce = 0;
+	double ve = 0.0;
+	{
+		// the first CSR_THREADS extension entries travel with the window's own loads (one per thread)
+		if (do_ext && tid < over) {
+			ce = ld_stream_i32(col + base + T + tid, pol_stream);
+			ve = ld_stream_f64(val + base + T + tid, pol_stream);
+		}
+		if (tid <= npre)
+			rp_pre = (int) (row_ptr[R0 + tid] - base);
+		if (tid == 0 && npre == CSR_THREADS)
+			rp_pre2 = (int) (row_ptr[R0 + CSR_THREADS] - base);
+	}
 
 	// 3. gathers and products -> shared memory in nnz order (conflict-free STS.64)
 	#pragma unroll
 	for (int k = 0; k < NPT; k++)
 		v[k] *= ld_x<HINT>(x + c[k], pol);
+	if (do_ext && tid < over)
+		ve *= ld_x<HINT>(x + ce, pol);
 	#pragma unroll
 	for (int k = 0; k < NPT; k++)
 		s_prod[k * CSR_THREADS + tid] = v[k];
 
+	{
+		if (do_ext && tid < over)
+			s_prod[T + tid] = ve;
+		if (tid <= npre)
+			s_rp[tid] = rp_pre;
+		if (tid == 0 && npre == CSR_THREADS)
+			s_rp[CSR_THREADS] = rp_pre2;
+	}
 	// 4. tail extension: finish the last owned row past the window end
-	if (nrows > 0 && over > 0 && !tail_split) {
-		for (int j = tid; j < (int) over; j += CSR_THREADS) {
+	if (do_ext) {
+		for (int j = tid + CSR_THREADS; j < (int) over; j += CSR_THREADS) {
 			const int64_t idx = base + T + j;
 			s_prod[T + j] = ld_stream_f64(val + idx, pol_stream) * ld_x<HINT>(x + ld_stream_i32(col + idx, pol_stream), pol);
 		}
@@ -109,8 +136,14 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 		// thread per row: sequential ascending-j sum (the oracle's summation order)
 		for (int r = tid; r < rows_full; r += CSR_THREADS) {
 			const int i = R0 + r;
-			int a = (int) (row_ptr[i] - base);
-			const int b = (int) (row_ptr[i + 1] - base);
+			int a, b;
+			if (r < CSR_THREADS) {
+				a = s_rp[r];
+				b = s_rp[r + 1];
+			} else {
+				a = (int) (row_ptr[i] - base);
+				b = (int) (row_ptr[i + 1] - base);
+			}
 			double sum = 0.0;
 			for (; a < b; a++)
 				sum += s_prod[swz(a)];
@@ -129,9 +162,7 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 			const int r = rb + g;
 			double sum = 0.0;
 			if (r < rows_full) {
-				const int i = R0 + r;
-				const int a = (int) (row_ptr[i] - base);
-				const int b = (int) (row_ptr[i + 1] - base);
+				const int a = s_rp[r], b = s_rp[r + 1];
 				for (int j = a + lane; j < b; j += lpr)
 					sum += s_prod[swz(j)];
 			}

@@ -13,6 +13,7 @@
 #include <vector>
 #include <algorithm>
 #include "../include/b200amg.h"
+#include "../include/b200spmv.h"
 
 #define CK(x) do { cudaError_t e = (x); if (e != cudaSuccess) { printf("CUDA error %s at %d\n", cudaGetErrorString(e), __LINE__); exit(1); } } while (0)
 
@@ -184,6 +185,26 @@ __global__ void __launch_bounds__(TH + 32) k_ring(const int * __restrict__ col, 
 	out[(int64_t) blockIdx.x * TH + tid] = acc;
 }
 
+// simple row-per-thread reference (serial ascending-j sum per row) and per-row bound sum |a x|
+__global__ void k_ref(const int * __restrict__ rp, const int * __restrict__ col, const double * __restrict__ val, const double * __restrict__ x,
+                      int64_t m, double * __restrict__ y, double * __restrict__ bound)
+{
+	const int64_t r = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (r >= m) return;
+	double s = 0, b = 0;
+	for (int j = rp[r]; j < rp[r + 1]; j++) { const double p = val[j] * x[col[j]]; s += p; b += fabs(p); }
+	y[r] = s; bound[r] = b;
+}
+__global__ void k_cmp(const double * __restrict__ y, const double * __restrict__ yref, const double * __restrict__ bound, int64_t m, unsigned long long * nbad, double * worst)
+{
+	const int64_t r = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (r >= m) return;
+	const double e = fabs(y[r] - yref[r]);
+	if (!(e <= 1e-12 * bound[r])) atomicAdd(nbad, 1ULL);
+	const double q = e / fmax(bound[r], 1e-300);
+	if (q > 1e-13) atomicMax((unsigned long long *) worst, (unsigned long long) __double_as_longlong(q));
+}
+
 struct Mat { int64_t m, n, nnz; std::vector<int> rp, col; std::vector<double> val; };
 
 static bool parse_line(const char * s, b200amg_params * p)
@@ -255,6 +276,7 @@ int main(int argc, char ** argv)
 		CK(cudaCreateTextureObject(&tx, &rd, &td, nullptr));
 		const unsigned G = (unsigned) ntiles;
 		std::vector<std::pair<const char *, float>> r;
+		if (getenv("KEXP_FLOORS")) {
 		r.push_back({ "stream (col+val)", time_ms([&] { k_floor<NPT, 0, true><<<G, TH>>>(d_col, d_val, d_x, tx, d_out); }) });
 		r.push_back({ "stream + LDG gather", time_ms([&] { k_floor<NPT, 1, true><<<G, TH>>>(d_col, d_val, d_x, tx, d_out); }) });
 		r.push_back({ "  + 5 shfl64/group", time_ms([&] { k_shfl<NPT, 5><<<G, TH>>>(d_col, d_val, d_x, d_out); }) });
@@ -277,8 +299,45 @@ int main(int argc, char ** argv)
 			ring(k_ring<NPT, 2, 1>, 2, 4, "ring2x4 + gather");
 			ring(k_ring<NPT, 8, 1>, 8, 1, "ring8x1 + gather");
 		}
+		}
 		for (auto & e : r)
 			printf("   %-24s %8.4f ms  %7.0f GB/s(B_c)  %6.1f Gnnz/s\n", e.first, e.second, bc / e.second * 1e-6, M.nnz / e.second * 1e-6);
+		// ---- the library's kernels through the C-ABI, checked against k_ref under the per-row bound ----
+		{
+			int * d_rp; double * d_y, * d_yref, * d_bound; unsigned long long * d_nbad; double * d_worst;
+			CK(cudaMalloc(&d_rp, (M.m + 1) * 4)); CK(cudaMalloc(&d_y, M.m * 8)); CK(cudaMalloc(&d_yref, M.m * 8)); CK(cudaMalloc(&d_bound, M.m * 8));
+			CK(cudaMalloc(&d_nbad, 8)); CK(cudaMalloc(&d_worst, 8));
+			CK(cudaMemcpy(d_rp, M.rp.data(), (M.m + 1) * 4, cudaMemcpyHostToDevice));
+			std::vector<double> hx2(M.n);
+			uint64_t st = 88172645463325252ULL;
+			for (auto & v : hx2) { st ^= st << 13; st ^= st >> 7; st ^= st << 17; v = (double) (st >> 11) / 9007199254740992.0 * 2.0 - 1.0; }
+			double * d_x2; CK(cudaMalloc(&d_x2, M.n * 8)); CK(cudaMemcpy(d_x2, hx2.data(), M.n * 8, cudaMemcpyHostToDevice));
+			k_ref<<<(unsigned) ((M.m + 255) / 256), 256>>>(d_rp, d_col, d_val, d_x2, M.m, d_yref, d_bound);
+			CK(cudaDeviceSynchronize());
+			struct V { const char * name; int fmt, npt, variant, ext; } vs[] = {
+				{ "lib csr auto", B200SPMV_CSR_ADAPTIVE, 0, 0, 0 }, { "lib csr npt8 ext256", B200SPMV_CSR_ADAPTIVE, 8, 0, 256 },
+				{ "lib csr npt16 ext2048", B200SPMV_CSR_ADAPTIVE, 16, 0, 2048 },
+				{ "lib sell C32", B200SPMV_SELL_C_SIGMA, 0, 0, 0 } };
+			for (auto & v : vs) {
+				if (getenv("KEXP_VARIANTS") && !strstr(getenv("KEXP_VARIANTS"), v.name)) continue;
+				b200spmv_opts o; b200spmv_default_opts(&o);
+				o.format = v.fmt; o.csr_nnz_per_thread = v.npt; o.csr_ext = v.ext;
+				b200spmv_t * h = nullptr;
+				if (b200spmv_create_device(&h, d_rp, d_col, d_val, M.m, M.n, M.nnz, &o)) { printf("   %-24s create failed: %s\n", v.name, b200spmv_last_error()); continue; }
+				CK(cudaMemset(d_y, 0xFF, M.m * 8)); CK(cudaMemset(d_nbad, 0, 8)); CK(cudaMemset(d_worst, 0, 8));
+				if (b200spmv_spmv_device(h, d_x2, d_y, nullptr)) { printf("   %-24s spmv failed: %s\n", v.name, b200spmv_last_error()); b200spmv_destroy(h); continue; }
+				k_cmp<<<(unsigned) ((M.m + 255) / 256), 256>>>(d_y, d_yref, d_bound, M.m, d_nbad, d_worst);
+				unsigned long long nbad; double worst;
+				CK(cudaMemcpy(&nbad, d_nbad, 8, cudaMemcpyDeviceToHost)); CK(cudaMemcpy(&worst, d_worst, 8, cudaMemcpyDeviceToHost));
+				std::vector<float> ms(13);
+				if (b200spmv_time_device(h, d_x, d_y, 13, 0, ms.data())) { printf("   time failed: %s\n", b200spmv_last_error()); b200spmv_destroy(h); continue; }
+				std::sort(ms.begin() + 3, ms.end());
+				const float med = ms[8];
+				printf("   %-24s %8.4f ms  %7.0f GB/s(B_c)  %6.1f Gnnz/s   bad rows %llu  max err/bound %.2e\n", v.name, med, bc / med * 1e-6, M.nnz / med * 1e-6, nbad, worst);
+				b200spmv_destroy(h);
+			}
+			cudaFree(d_rp); cudaFree(d_y); cudaFree(d_yref); cudaFree(d_bound); cudaFree(d_nbad); cudaFree(d_worst); cudaFree(d_x2);
+		}
 		cudaDestroyTextureObject(tx);
 		cudaFree(d_col); cudaFree(d_val); cudaFree(d_x); cudaFree(d_out);
 	}
