@@ -81,7 +81,8 @@ static void free_handle(b200spmv * h)
 	if (!h)
 		return;
 	void * ptrs[] = { h->d_row_ptr, h->d_col, h->d_val, h->d_tile_row, h->d_split_row, h->d_split_tile, h->d_tile_head, h->d_tile_tail,
-	                  h->d_row_order, h->d_slice_width, h->d_slice_ptr, h->d_scol, h->d_sval, h->d_x, h->d_y, h->d_norm_partial };
+	                  h->d_row_order, h->d_slice_width, h->d_slice_ptr, h->d_scol, h->d_sval, h->d_x, h->d_y, h->d_norm_partial,
+	                  h->d_sell_items, h->d_sell_cuts, h->d_sell_partial };
 	for (void * p : ptrs)
 		if (p)
 			cudaFree(p);
@@ -159,7 +160,7 @@ static int create_common(b200spmv ** out, const int32_t * row_ptr, const int32_t
 			cudaFree(h->d_val);
 			h->d_col = nullptr;
 			h->d_val = nullptr;
-			norm_slots = (m + SELL_ROWS_PER_CTA - 1) / SELL_ROWS_PER_CTA;
+			norm_slots = (h->sell_nitems + 3) / 4 + (h->sell_ncuts + 3) / 4;
 		}
 		h->norm_slots = norm_slots > 0 ? norm_slots : 1;
 		if (cudaMalloc(&h->d_norm_partial, h->norm_slots * sizeof(double)) != cudaSuccess) break;
@@ -206,7 +207,9 @@ extern "C" int32_t b200spmv_launches_per_spmv(const b200spmv_t * h)
 {
 	if (!h)
 		return 0;
-	return (h->format == B200SPMV_CSR_ADAPTIVE && h->nsplit > 0) ? 2 : 1;
+	if (h->format == B200SPMV_CSR_ADAPTIVE)
+		return h->nsplit > 0 ? 2 : 1;
+	return h->sell_ncuts > 0 ? 2 : 1;
 }
 
 extern "C" int b200spmv_spmv_device_ex(b200spmv_t * h, const double * dx, double * dy, void * stream, const b200spmv_launch * launch)
@@ -265,9 +268,10 @@ extern "C" int b200spmv_stats(const b200spmv_t * h, double * out, int32_t n_out)
 		v[4] = (double) h->tile_nnz;
 		v[5] = (double) h->ext;
 	} else {
-		v[0] = (double) h->padded * 12.0 + (double) h->nslices * 4.0 + (double) (h->nslices + 1) * 8.0 + (double) h->m * 4.0;
+		v[0] = (double) h->padded * 12.0 + (double) h->nslices * 4.0 + (double) (h->nslices + 1) * 8.0 + (double) h->m * 4.0
+		       + (double) h->sell_nitems * 16.0 + (double) h->sell_ncuts * 16.0 + (double) h->sell_nslots * 256.0;
 		v[1] = (double) h->nslices;
-		v[2] = 0.0;
+		v[2] = (double) h->sell_ncuts;
 		v[3] = (double) h->padded;
 		v[4] = (double) h->C;
 		v[5] = (double) h->sigma;

@@ -31,8 +31,8 @@ extern thread_local char g_b200_err[512];
 // Tunables of the nnz-tiled CSR kernel
 // ---------------------------------------------------------------------------------------------
 constexpr int CSR_THREADS = 256;          // threads per tile CTA
-constexpr int SELL_THREADS = 128;         // threads per SELL CTA, two rows per thread
-constexpr int SELL_ROWS_PER_CTA = 2 * SELL_THREADS;
+constexpr int SELL_THREADS = 128;         // threads per SELL CTA: four warps, one work item each
+constexpr int SELL_KCH = 128;             // slice columns per work item
 
 // ---------------------------------------------------------------------------------------------
 // Blackwell load helpers.
@@ -177,6 +177,10 @@ struct b200spmv {
 	int64_t * d_slice_ptr;
 	int32_t * d_scol;
 	double * d_sval;
+	int32_t * d_sell_items;   // int4[sell_nitems]  {slice, first column, partial slot or -1, lane group}
+	int32_t * d_sell_cuts;    // int4[sell_ncuts]   {slice, first partial slot, items, lane group}
+	double * d_sell_partial;  // [sell_nslots * 32]
+	int64_t sell_nitems, sell_ncuts, sell_nslots;
 
 	// staging for the host-vector entry point, norm partials
 	double * d_x;

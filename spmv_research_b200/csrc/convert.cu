@@ -318,6 +318,86 @@ __global__ void sell_scatter_kernel(const int32_t * __restrict__ row_ptr, const 
 	}
 }
 
+// Work items of the SpMV kernel: every slice is cut along k into chunks of SELL_KCH columns and
+// across lanes into groups of 32; a slice cut into n > 1 chunks also gets one "cut" record per lane
+// group that tells sell_fixup_kernel where its n partials lie.
+__global__ void sell_item_count_kernel(const int32_t * __restrict__ slice_width, int64_t nslices, int G,
+                                       int64_t * __restrict__ item_off, int64_t * __restrict__ slot_off, int64_t * __restrict__ cut_off)
+{
+	const int64_t s = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (s > nslices)
+		return;
+	int64_t n = 0;
+	if (s < nslices) {
+		n = (slice_width[s] + SELL_KCH - 1) / SELL_KCH;
+		if (n < 1)
+			n = 1;                       // zero-width slices still zero their rows
+	}
+	item_off[s] = n * G;
+	slot_off[s] = (n > 1) ? n * G : 0;
+	cut_off[s] = (n > 1) ? G : 0;
+}
+
+__global__ void sell_item_fill_kernel(const int32_t * __restrict__ slice_width, int64_t nslices, int G, const int64_t * __restrict__ item_off,
+                                      const int64_t * __restrict__ slot_off, const int64_t * __restrict__ cut_off,
+                                      int4 * __restrict__ items, int4 * __restrict__ cuts)
+{
+	const int64_t s = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (s >= nslices)
+		return;
+	int n = (slice_width[s] + SELL_KCH - 1) / SELL_KCH;
+	if (n < 1)
+		n = 1;
+	int64_t io = item_off[s];
+	const int64_t so = slot_off[s], co = cut_off[s];
+	for (int g = 0; g < G; g++) {
+		for (int j = 0; j < n; j++)
+			items[io++] = make_int4((int) s, j * SELL_KCH, (n > 1) ? (int) (so + (int64_t) g * n + j) : -1, g);
+		if (n > 1)
+			cuts[co + g] = make_int4((int) s, (int) (so + (int64_t) g * n), n, g);
+	}
+}
+
+static int sell_plan_items(b200spmv * h)
+{
+	cudaStream_t st = h->stream;
+	const int64_t ns = h->nslices;
+	const int G = h->C >= 32 ? h->C / 32 : 1;
+	h->sell_nitems = h->sell_ncuts = h->sell_nslots = 0;
+	if (ns == 0)
+		return 0;
+	int64_t * d_off;
+	CU(cudaMalloc(&d_off, 3 * (ns + 1) * sizeof(int64_t)));
+	int64_t * d_item = d_off, * d_slot = d_off + (ns + 1), * d_cut = d_off + 2 * (ns + 1);
+	sell_item_count_kernel<<<(unsigned) ((ns + 1 + 255) / 256), 256, 0, st>>>(h->d_slice_width, ns, G, d_item, d_slot, d_cut);
+	CU_LAUNCH();
+	if (device_exclusive_scan_i64(d_item, ns + 1, st) || device_exclusive_scan_i64(d_slot, ns + 1, st) || device_exclusive_scan_i64(d_cut, ns + 1, st)) {
+		cudaFree(d_off);
+		return 1;
+	}
+	int64_t tot[3];
+	CU(cudaMemcpyAsync(&tot[0], d_item + ns, 8, cudaMemcpyDeviceToHost, st));
+	CU(cudaMemcpyAsync(&tot[1], d_slot + ns, 8, cudaMemcpyDeviceToHost, st));
+	CU(cudaMemcpyAsync(&tot[2], d_cut + ns, 8, cudaMemcpyDeviceToHost, st));
+	CU(cudaStreamSynchronize(st));
+	h->sell_nitems = tot[0];
+	h->sell_nslots = tot[1];
+	h->sell_ncuts = tot[2];
+	if (tot[1] >= 0x7fffffffLL / 32 || tot[0] >= 0x7fffffffLL) {
+		cudaFree(d_off);
+		B200_FAIL("SELL-C-sigma plan too large (%lld items)", (long long) tot[0]);
+	}
+	CU(cudaMalloc(&h->d_sell_items, (size_t) tot[0] * sizeof(int4)));
+	CU(cudaMalloc(&h->d_sell_cuts, (size_t) (tot[2] > 0 ? tot[2] : 1) * sizeof(int4)));
+	CU(cudaMalloc(&h->d_sell_partial, (size_t) (tot[1] > 0 ? tot[1] : 1) * 32 * sizeof(double)));
+	sell_item_fill_kernel<<<(unsigned) ((ns + 255) / 256), 256, 0, st>>>(h->d_slice_width, ns, G, d_item, d_slot, d_cut,
+	                                                                    reinterpret_cast<int4 *>(h->d_sell_items), reinterpret_cast<int4 *>(h->d_sell_cuts));
+	CU_LAUNCH();
+	CU(cudaStreamSynchronize(st));
+	CU(cudaFree(d_off));
+	return 0;
+}
+
 int sell_convert(b200spmv * h)
 {
 	const int64_t m = h->m;
@@ -378,5 +458,5 @@ int sell_convert(b200spmv * h)
 		CU_LAUNCH();
 	}
 	CU(cudaStreamSynchronize(st));
-	return 0;
+	return sell_plan_items(h);
 }

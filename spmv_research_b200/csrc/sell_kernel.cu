@@ -4,66 +4,82 @@
 // slice, acc[lane] += val[k*C+lane] * x[col[k*C+lane]] for k < slice_width, then
 // y[row_order[slice*C+lane]] = acc[lane]; the ragged last slice stores min(C, m - s*C) lanes.
 //
-// B200 mapping: one thread owns TWO adjacent lanes (sorted rows 2q, 2q+1) of a slice, so each
-// step is one 128-bit values load + one 64-bit col_ind load, contiguous across the threads of a
-// slice (column-major slices are coalesced by construction); four steps are in flight per thread
-// before the first x gather; no reduction is needed because a lane is a row.  Padding entries
-// are (col 0, val 0.0) exactly as the reference writes them and are multiplied like real ones.
+// B200 mapping: the unit of work is an ITEM = (slice, group of 32 lanes, chunk of SELL_KCH slice
+// columns), one warp per item, lane = sorted row.  Each k step of a warp is one 256-byte values
+// load and one 128-byte col_ind load (column-major slices are coalesced by construction), eight
+// steps in flight per lane before the first x gather; no reduction is needed because a lane is a
+// row.  Cutting slices along k bounds the sequential depth of a lane: a slice holding one of the
+// generator's giant skew rows (width 500 100 at config 4) becomes thousands of items instead of
+// one 500 100-step loop.  Slices cut into several items write per-item partials that
+// sell_fixup_kernel adds in chunk order (deterministic, no atomics).  Padding entries are
+// (col 0, val 0.0) exactly as the reference writes them and are multiplied like real ones.
 #include "common.cuh"
 
 template <bool HINT>
 __global__ void __launch_bounds__(SELL_THREADS, 8)
-sell_kernel(const int32_t * __restrict__ row_order, const int32_t * __restrict__ slice_width,
-            const int64_t * __restrict__ slice_ptr, const int32_t * __restrict__ scol, const double * __restrict__ sval,
-            const double * __restrict__ x, int64_t m, int C, int c_shift, YOut out)
+sell_kernel(const int4 * __restrict__ items, int64_t nitems, const int32_t * __restrict__ row_order,
+            const int32_t * __restrict__ slice_width, const int64_t * __restrict__ slice_ptr,
+            const int32_t * __restrict__ scol, const double * __restrict__ sval, const double * __restrict__ x,
+            double * __restrict__ partial, int64_t m, int C, YOut out)
 {
 	__shared__ double s_red[SELL_THREADS / 32];
 	const uint64_t pol = make_policy_evict_last();
 	const uint64_t pol_stream = make_policy_evict_first();
-	const int64_t q = (int64_t) blockIdx.x * SELL_THREADS + threadIdx.x;
-	const int64_t r0 = 2 * q;
+	const int lane = threadIdx.x & 31;
+	const int64_t it = (int64_t) blockIdx.x * (SELL_THREADS / 32) + (threadIdx.x >> 5);
 	double nrm = 0.0;
-	if (r0 < m) {
-		const int64_t s = r0 >> c_shift;
+	if (it < nitems) {
+		const int4 item = items[it];                 // x: slice, y: first column, z: partial slot or -1, w: lane group
+		const int64_t s = item.x;
 		const int w = slice_width[s];
-		int64_t p = slice_ptr[s] + (r0 & (C - 1));
-		double acc0 = 0.0, acc1 = 0.0;
-		int k = 0;
-		for (; k + 4 <= w; k += 4) {
-			double2 v[4];
-			int2 c[4];
+		int k1 = (item.y + SELL_KCH < w) ? item.y + SELL_KCH : w;
+		if (lane >= C)
+			k1 = item.y;                             // C < 32: the upper lanes of the warp idle
+		int64_t p = slice_ptr[s] + (int64_t) item.y * C + item.w * 32 + lane;
+		double acc = 0.0;
+		int k = item.y;
+		for (; k + 8 <= k1; k += 8) {
+			double v[8];
+			int c[8];
 			#pragma unroll
-			for (int u = 0; u < 4; u++) {
-				v[u] = ld_stream_f64x2(sval + p + (int64_t) u * C, pol_stream);
-				c[u] = ld_stream_i32x2(scol + p + (int64_t) u * C, pol_stream);
+			for (int u = 0; u < 8; u++) {
+				v[u] = ld_stream_f64(sval + p + (int64_t) u * C, pol_stream);
+				c[u] = ld_stream_i32(scol + p + (int64_t) u * C, pol_stream);
 			}
 			#pragma unroll
-			for (int u = 0; u < 4; u++) {
-				acc0 = fma(v[u].x, ld_x<HINT>(x + c[u].x, pol), acc0);
-				acc1 = fma(v[u].y, ld_x<HINT>(x + c[u].y, pol), acc1);
+			for (int u = 0; u < 8; u++)
+				acc = fma(v[u], ld_x<HINT>(x + c[u], pol), acc);
+			p += 8 * (int64_t) C;
+		}
+		if (k < k1) {
+			double v[8];
+			int c[8];
+			#pragma unroll
+			for (int u = 0; u < 8; u++) {
+				const bool on = (k + u < k1);
+				v[u] = on ? ld_stream_f64(sval + p + (int64_t) u * C, pol_stream) : 0.0;
+				c[u] = on ? ld_stream_i32(scol + p + (int64_t) u * C, pol_stream) : 0;
 			}
-			p += 4 * (int64_t) C;
+			#pragma unroll
+			for (int u = 0; u < 8; u++)
+				if (k + u < k1)
+					acc = fma(v[u], ld_x<HINT>(x + c[u], pol), acc);
 		}
-		for (; k < w; k++) {
-			const double2 v = ld_stream_f64x2(sval + p, pol_stream);
-			const int2 c = ld_stream_i32x2(scol + p, pol_stream);
-			acc0 = fma(v.x, ld_x<HINT>(x + c.x, pol), acc0);
-			acc1 = fma(v.y, ld_x<HINT>(x + c.y, pol), acc1);
-			p += C;
-		}
-		const double scale = out.scale ? *out.scale : 1.0;
-		acc0 *= scale;
-		acc1 *= scale;
-		y_store(out, row_order[r0], acc0);
-		nrm = acc0 * acc0;
-		if (r0 + 1 < m) {
-			y_store(out, row_order[r0 + 1], acc1);
-			nrm += acc1 * acc1;
+		if (item.z >= 0) {
+			partial[(int64_t) item.z * 32 + lane] = acc;
+		} else {
+			const int64_t r = s * C + item.w * 32 + lane;
+			if (r < m && lane < C) {
+				const double scale = out.scale ? *out.scale : 1.0;
+				acc *= scale;
+				y_store(out, row_order[r], acc);
+				nrm = acc * acc;
+			}
 		}
 	}
 	if (out.norm_partial) {
 		nrm = warp_sum(nrm);
-		if ((threadIdx.x & 31) == 0)
+		if (lane == 0)
 			s_red[threadIdx.x >> 5] = nrm;
 		__syncthreads();
 		if (threadIdx.x == 0) {
@@ -72,6 +88,43 @@ sell_kernel(const int32_t * __restrict__ row_order, const int32_t * __restrict__
 			for (int wv = 0; wv < SELL_THREADS / 32; wv++)
 				tot += s_red[wv];
 			out.norm_partial[blockIdx.x] = tot;
+		}
+	}
+}
+
+// One warp per cut (slice, lane group): y = sum of its items' partials in chunk order.
+__global__ void __launch_bounds__(SELL_THREADS)
+sell_fixup_kernel(const int4 * __restrict__ cuts, int64_t ncuts, const int32_t * __restrict__ row_order,
+                  const double * __restrict__ partial, int64_t m, int C, int64_t norm_base, YOut out)
+{
+	__shared__ double s_red[SELL_THREADS / 32];
+	const int lane = threadIdx.x & 31;
+	const int64_t q = (int64_t) blockIdx.x * (SELL_THREADS / 32) + (threadIdx.x >> 5);
+	double nrm = 0.0;
+	if (q < ncuts) {
+		const int4 cut = cuts[q];                    // x: slice, y: first partial slot, z: number of items, w: lane group
+		double acc = 0.0;
+		for (int j = 0; j < cut.z; j++)
+			acc += partial[((int64_t) cut.y + j) * 32 + lane];
+		const int64_t r = (int64_t) cut.x * C + cut.w * 32 + lane;
+		if (r < m && lane < C) {
+			const double scale = out.scale ? *out.scale : 1.0;
+			acc *= scale;
+			y_store(out, row_order[r], acc);
+			nrm = acc * acc;
+		}
+	}
+	if (out.norm_partial) {
+		nrm = warp_sum(nrm);
+		if (lane == 0)
+			s_red[threadIdx.x >> 5] = nrm;
+		__syncthreads();
+		if (threadIdx.x == 0) {
+			double tot = 0.0;
+			#pragma unroll
+			for (int wv = 0; wv < SELL_THREADS / 32; wv++)
+				tot += s_red[wv];
+			out.norm_partial[norm_base + blockIdx.x] = tot;
 		}
 	}
 }
@@ -90,20 +143,25 @@ int launch_sell_spmv(b200spmv * h, const double * dx, double * dy, cudaStream_t 
 		out.scale = l->scale;
 		out.norm_partial = l->norm2 ? h->d_norm_partial : nullptr;
 	}
-	const int64_t ctas = (h->m + SELL_ROWS_PER_CTA - 1) / SELL_ROWS_PER_CTA;
-	if (ctas == 0)
-		return 0;
-	int shift = 0;
-	while ((1 << shift) < h->C)
-		shift++;
-	if (h->x_hint == 0)
-		sell_kernel<true><<<(unsigned) ctas, SELL_THREADS, 0, st>>>(h->d_row_order, h->d_slice_width, h->d_slice_ptr, h->d_scol,
-		                                                           h->d_sval, dx, h->m, h->C, shift, out);
-	else
-		sell_kernel<false><<<(unsigned) ctas, SELL_THREADS, 0, st>>>(h->d_row_order, h->d_slice_width, h->d_slice_ptr, h->d_scol,
-		                                                            h->d_sval, dx, h->m, h->C, shift, out);
-	CU_LAUNCH();
+	constexpr int WPC = SELL_THREADS / 32;
+	const int64_t ctas = (h->sell_nitems + WPC - 1) / WPC;
+	const int64_t fix_ctas = (h->sell_ncuts + WPC - 1) / WPC;
+	if (ctas > 0) {
+		const int4 * items = reinterpret_cast<const int4 *>(h->d_sell_items);
+		if (h->x_hint == 0)
+			sell_kernel<true><<<(unsigned) ctas, SELL_THREADS, 0, st>>>(items, h->sell_nitems, h->d_row_order, h->d_slice_width, h->d_slice_ptr,
+			                                                           h->d_scol, h->d_sval, dx, h->d_sell_partial, h->m, h->C, out);
+		else
+			sell_kernel<false><<<(unsigned) ctas, SELL_THREADS, 0, st>>>(items, h->sell_nitems, h->d_row_order, h->d_slice_width, h->d_slice_ptr,
+			                                                            h->d_scol, h->d_sval, dx, h->d_sell_partial, h->m, h->C, out);
+		CU_LAUNCH();
+	}
+	if (fix_ctas > 0) {
+		sell_fixup_kernel<<<(unsigned) fix_ctas, SELL_THREADS, 0, st>>>(reinterpret_cast<const int4 *>(h->d_sell_cuts), h->sell_ncuts, h->d_row_order,
+		                                                               h->d_sell_partial, h->m, h->C, ctas, out);
+		CU_LAUNCH();
+	}
 	if (l && l->norm2)
-		return launch_norm_reduce(h, ctas, l->norm2, st);
+		return launch_norm_reduce(h, ctas + fix_ctas, l->norm2, st);
 	return 0;
 }

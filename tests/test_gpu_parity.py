@@ -154,7 +154,10 @@ def test_sell_conversion_edge_cases(S, oracle):
                 y = np.full(m, 1.0)
                 MF.spmv(x, y)
                 _check(oracle, rp, col, val, x, y, "sell %s C=%d sigma=%d" % (name, C_, sg))
-                assert np.array_equal(y, oracle.sellcs_spmv(O, x)), name      # same fma chain per lane -> bit-equal
+                if len(O["slice_width"]) == 0 or int(np.max(O["slice_width"])) <= 128:
+                    # slices no wider than one k chunk (SELL_KCH): same fma chain per lane as the reference kernel -> bit-equal;
+                    # wider slices are cut into chunks whose partials are added in chunk order (bounded by _check above)
+                    assert np.array_equal(y, oracle.sellcs_spmv(O, x)), name
             MF.close()
 
 
