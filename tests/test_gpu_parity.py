@@ -309,3 +309,24 @@ def test_giant_row_full_size(S, oracle):
         if kw["format"] == S.CSR_ADAPTIVE:
             assert MF.gpu_launches_per_spmv == 2
         MF.close()
+
+
+@pytest.mark.gpu
+def test_reference_harness_drives_the_plugin(S, oracle, tmp_path):
+    """Drop-in proof: the reference's unmodified harness (bench.cpp + bench_spmv.cpp, built by oracle/Makefile) linked with
+    host/b200_plugin.cpp loads a Matrix Market file, calls csr_to_format + spmv(x, y) in its own timing loop and validates
+    y against its _Float128 Kahan gold (bench_spmv.cpp:108-235): no "Test failed", tiny mae, our format name in its CSV row."""
+    from spmv_research_b200 import amg, refharness as RH
+    if not RH.available("spmv_b200_csr_d.exe"):
+        pytest.skip("oracle/_ref harness executables not built (needs /root/reference at build time)")
+    p = amg.MatrixParams.parse("30000 30000 12 6 normal random 0.3 50 0.5 0.5 14")
+    rp, col, val = amg.generate(p)
+    path = str(tmp_path / "amg_30000.mtx")
+    RH.write_matrix_market(path, rp, col, val, p.cols)
+    for exe, name in (("spmv_b200_csr_d.exe", "B200_CSR_ADAPTIVE"), ("spmv_b200_sell_d.exe", "B200_SELL_C_SIGMA")):
+        r = RH.run(exe, [path], gpu_kernel=True, threads=4)
+        assert r["returncode"] == 0, r["stderr"][-2000:]
+        assert not r["test_failed"], r["stdout"][-2000:]
+        assert name in r["csv"], r["csv"]
+        assert r["errors"]["max_ae"] < 1e-11 and r["errors"]["mae"] < 1e-12, r["errors"]
+        assert r["loops"] >= 64                       # the reference's >= 64 iterations / >= 2 s rule (bench_spmv.cpp:335-382)
