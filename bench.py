@@ -11,6 +11,11 @@ one SpMV of every sample matrix (N=1) or one power iteration of the sharded matr
 import argparse
 import json
 import os
+
+# torchrun sets OMP_NUM_THREADS=1; the host-side generator (OpenMP) should use this rank's share of the cores.
+if int(os.environ.get("WORLD_SIZE", "1")) > 1 and os.environ.get("B200_KEEP_OMP") != "1":
+    os.environ["OMP_NUM_THREADS"] = str(max(1, (os.cpu_count() or 1) // int(os.environ.get("LOCAL_WORLD_SIZE", os.environ["WORLD_SIZE"]))))
+
 import subprocess
 import sys
 import threading
@@ -114,9 +119,10 @@ def parse_args():
     ap.add_argument("--workload", default="auto", choices=["auto", "medium_sample", "config1", "g1", "g2", "power"])
     ap.add_argument("--format", default="csr", choices=["csr", "sell"])
     ap.add_argument("--rows-per-gpu", type=int, default=4194304)
-    ap.add_argument("--exchange", default="nccl", choices=["nccl", "p2p"])
+    ap.add_argument("--exchange", default="p2p", choices=["nccl", "p2p"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-sell", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="N>1: time an eager step loop instead of CUDA-graph replays")
     ap.add_argument("--x", default="ones", choices=["ones", "random"])
     ap.add_argument("--line", default=None, help="one generator parameter line to use as the N=1 workload (profiling)")
     return ap.parse_args()
@@ -329,10 +335,21 @@ def run_power(args):
     MF = S.csr_to_format(rp_loc, col, val, i_e - i_s, n, nnz_loc, 0, 0, format=fmt, device=local)
     del col, val
 
-    def local_spmv(cur, slot, scale, norm2, parity):
-        MF.spmv_device(cur, slot, stream, scale=scale, norm2=norm2)
+    exchange = args.exchange if world > 1 else "nccl"
+    pv = None
+    if exchange == "p2p":
+        # fused exchange: the SpMV epilogue stores every finished row into all peers' next-x buffers over NVLink
+        pv = power.PeerVectors(n, rank, world, dev)
 
-    it = power.ShardedPowerIteration(n, bounds, rank, world, local_spmv, dev, exchange="nccl")
+    def local_spmv(cur, slot, scale, norm2, parity):
+        peers = ()
+        if pv is not None:
+            b = 1 - parity
+            peers = [pv.peer[b][q] + 8 * i_s for q in range(world) if q != rank]
+        MF.spmv_device(cur, slot, torch.cuda.current_stream().cuda_stream, scale=scale, norm2=norm2, peers=peers)
+
+    it = power.ShardedPowerIteration(n, bounds, rank, world, local_spmv, dev, exchange=exchange,
+                                     buffers=(pv.tensors if pv is not None else None))
     it.set_start(np.ones(n))
     K, W = args.steps, max(args.warmup, 3)
     for _ in range(W):
@@ -350,24 +367,87 @@ def run_power(args):
     it.set_start(np.ones(n))
     for _ in range(W):
         it.step()
+    # two iterations (one per buffer parity) captured into a CUDA graph: K timed iterations = ceil(K/2) replays
+    launch_mode = "eager"
+    if not args.no_graph:
+        try:
+            it.capture_pair()
+            launch_mode = "cuda_graph(2 iterations per replay)"
+        except Exception as ex:                      # capture unsupported for this collective: keep the eager loop, say so
+            launch_mode = "eager (graph capture failed: %s)" % str(ex).splitlines()[0][:120]
+            torch.cuda.synchronize()
+    K_run = K
     with ClockSampler(local) as clk:
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
         e0.record()
-        for _ in range(K):
-            it.step()
+        if launch_mode.startswith("cuda_graph"):
+            it.replay(K // 2)
+            if K % 2:
+                it.step()
+        else:
+            for _ in range(K):
+                it.step()
         e1.record()
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
-    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    ms = torch.tensor([e0.elapsed_time(e1) * K / K_run], dtype=torch.float64, device=dev)
     kms = torch.tensor([kern_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         dist.all_reduce(kms, op=dist.ReduceOp.MAX)
     ms_step = float(ms.item()) / K
     eig = it.eigenvalue()
+
+    # the plain-NCCL exchange (all-gather of y slots after the kernel), same protocol, reported beside the fused one
+    nccl_cmp = None
+    if world > 1 and exchange == "p2p":
+        def plain_spmv(cur, slot, scale, norm2, parity):
+            MF.spmv_device(cur, slot, stream, scale=scale, norm2=norm2)
+        it2 = power.ShardedPowerIteration(n, bounds, rank, world, plain_spmv, dev, exchange="nccl")
+        it2.set_start(np.ones(n))
+        for _ in range(W):
+            it2.step()
+        dist.barrier()
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(K):
+            it2.step()
+        e1.record()
+        torch.cuda.synchronize()
+        ms2 = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        dist.all_reduce(ms2, op=dist.ReduceOp.MAX)
+        nccl_cmp = {"ms_per_step": round(float(ms2.item()) / K, 5), "gflops": round(2.0 * nnz / (float(ms2.item()) / K * 1e-3) * 1e-9, 2),
+                    "eigenvalue_estimate": it2.eigenvalue(),
+                    "exchange": "NCCL in-place all-gather of y slots (one broadcast per owner) + scalar all-reduce"}
+        del it2
+
+    # the N = 1 member of the same weak-scaling series (rows_per_gpu rows), timed on rank 0 alone while the others wait:
+    # lets the scaling of THIS workload be read off one line (the default N = 1 bench line is the medium-dataset sample)
+    n1_same = None
+    if world > 1:
+        if rank == 0:
+            p1 = H.config5(1, args.rows_per_gpu)
+            rp1, col1, val1 = amg.generate(p1)
+            MF1 = S.csr_to_format(rp1, col1, val1, p1.rows, p1.cols, int(rp1[-1]), 0, 0, format=fmt, device=local)
+            it1 = power.ShardedPowerIteration(p1.cols, np.array([[0, p1.rows]], np.int64), 0, 1,
+                                              lambda cur, slot, scale, norm2, parity: MF1.spmv_device(cur, slot, stream, scale=scale, norm2=norm2), dev)
+            it1.set_start(np.ones(p1.cols))
+            for _ in range(W):
+                it1.step()
+            torch.cuda.synchronize()
+            e0.record()
+            for _ in range(K):
+                it1.step()
+            e1.record()
+            torch.cuda.synchronize()
+            t1 = e0.elapsed_time(e1) / K
+            n1_same = {"matrix": p1.line(), "ms_per_step": round(t1, 5), "gflops": round(2.0 * int(rp1[-1]) / t1 * 1e-6, 2)}
+            MF1.close()
+            del it1, rp1, col1, val1
+        dist.barrier()
 
     # end to end through the host-vector call: this rank's shard product with x from pinned host memory, y back to the host
     tx = torch.ones(n, dtype=torch.float64).pin_memory()
@@ -393,7 +473,8 @@ def run_power(args):
             "ms_per_step": round(ms_step, 5), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic (reference artificial-matrix-generator restated bit-exactly, seed 14), power iteration from x = 1",
             "config": {"workload": "power_iteration config5-series: %s" % p.line(), "format": MF.format_name, "rows_per_gpu": args.rows_per_gpu,
-                       "total_nnz": int(nnz), "shard_rows": [int(b[1] - b[0]) for b in bounds], "exchange": "NCCL in-place all-gather of y slots (one broadcast per owner) + scalar all-reduce",
+                       "total_nnz": int(nnz), "shard_rows": [int(b[1] - b[0]) for b in bounds], "exchange": ("fused: SpMV epilogue stores y rows into every peer's next-x buffer over NVLink (CUDA IPC) + NCCL scalar all-reduce"
+                                    if exchange == "p2p" else "NCCL in-place all-gather of y slots (one broadcast per owner) + scalar all-reduce"),
                        "l2_note": "each shard is %.1f GB (> 126 MB L2); no explicit flush" % (bc_loc * 1e-9), "generate_s": round(t_gen, 1)},
             "effective_GBs": round(bc / (ms_step * 1e-3) * 1e-9, 1),
             "roofline_frac_nominal_8TBs": round(bc / (ms_step * 1e-3) * 1e-9 / (NOMINAL_HBM_GBS * world), 4),
@@ -404,11 +485,25 @@ def run_power(args):
             "e2e": {"value": round(2.0 * nnz / te * 1e-9, 2), "unit": "GFLOP/s", "h2d_bytes_per_step": int(8 * n * world),
                     "d2h_bytes_per_step": int(8 * m), "ms_per_step": round(te * 1e3, 4),
                     "call": "per rank Matrix_Format::spmv(x, y) on its row shard, pinned host x / y, max over ranks"},
-            "gpu_launches": int(K * (MF.gpu_launches_per_spmv + 1)), "clocks": clk.summary(), "eigenvalue_estimate": eig,
+            "gpu_launches": int(K * (MF.gpu_launches_per_spmv + 1)), "clocks": clk.summary(), "eigenvalue_estimate": eig, "launch": launch_mode, "nccl_exchange": nccl_cmp, "n1_same_series": n1_same,
         }
         emit(out)
+    # Teardown.  A captured graph holding NCCL kernels must be released before the communicator, and a communicator
+    # teardown that stalls must not keep the GPUs leased: a watchdog ends the process 30 s after the line is out.
+    def _bail():
+        os._exit(0)
+    wd = threading.Timer(30.0, _bail)
+    wd.daemon = True
+    wd.start()
+    torch.cuda.synchronize()
+    if getattr(it, "_graph", None) is not None:
+        it._graph.reset()
+        it._graph = None
+    torch.cuda.synchronize()
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
+    wd.cancel()
 
 
 # ------------------------------------------------------------------------------------------------

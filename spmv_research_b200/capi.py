@@ -189,3 +189,27 @@ def device_count():
     except B200Error:
         return 0
     return n.value
+
+
+def malloc(nbytes):
+    """cudaMalloc through the library (a base allocation: its IPC handle maps exactly this address)."""
+    p = C.c_void_p()
+    check(lib().b200spmv_malloc(C.byref(p), int(nbytes)))
+    return p.value
+
+
+def free(ptr):
+    check(lib().b200spmv_free(C.c_void_p(ptr)))
+
+
+def ipc_export(ptr):
+    buf = (C.c_ubyte * 64)()
+    check(lib().b200spmv_ipc_export(C.c_void_p(ptr), buf))
+    return bytes(buf)
+
+
+def ipc_import(handle_bytes):
+    buf = (C.c_ubyte * 64).from_buffer_copy(handle_bytes)
+    p = C.c_void_p()
+    check(lib().b200spmv_ipc_import(buf, C.byref(p)))
+    return p.value

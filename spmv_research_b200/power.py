@@ -35,25 +35,58 @@ def allgather_rows(vec, bounds, group=None):
         w.wait()
 
 
+class _RawCuda:
+    """__cuda_array_interface__ view of n doubles at a raw device address."""
+
+    def __init__(self, ptr, n):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f8", "data": (ptr, False), "version": 3, "strides": None}
+
+
+class PeerVectors:
+    """Two full-length x buffers per rank in plain cudaMalloc memory, each mapped into every peer of the box with
+    CUDA IPC (b200spmv_ipc_*): peer[b][q] is the address, valid in THIS process, of rank q's buffer b."""
+
+    def __init__(self, n, rank, world, device):
+        from . import capi
+        self.n = n
+        self.ptr = [capi.malloc(8 * n) for _ in range(2)]
+        self._views = [_RawCuda(p, n) for p in self.ptr]
+        self.tensors = [torch.as_tensor(v, device=device) for v in self._views]
+        for t in self.tensors:
+            t.zero_()
+        torch.cuda.synchronize()
+        mine = [capi.ipc_export(p) for p in self.ptr]
+        every = [None] * world
+        dist.all_gather_object(every, mine)
+        self.peer = [[self.ptr[b] if q == rank else capi.ipc_import(every[q][b]) for q in range(world)] for b in range(2)]
+
+
 class ShardedPowerIteration:
     """local_spmv(x_full, y_slot, scale, norm2, parity) computes y_slot = scale * (A_p x_full) and
     norm2 = sum(y_slot^2); parity (0/1) says which of the two x buffers is being written (p2p stores)."""
 
-    def __init__(self, n, bounds, rank, world, local_spmv, device, exchange="nccl", dtype=torch.float64):
+    def __init__(self, n, bounds, rank, world, local_spmv, device, exchange="nccl", dtype=torch.float64, buffers=None):
         self.n, self.bounds, self.rank, self.world = n, bounds, rank, world
         self.i_s, self.i_e = int(bounds[rank, 0]), int(bounds[rank, 1])
         self.local_spmv = local_spmv
         self.device = device
         self.exchange = exchange
-        self.cur = torch.zeros(n, dtype=dtype, device=device)
-        self.nxt = torch.zeros(n, dtype=dtype, device=device)
+        if buffers is not None:
+            self.cur, self.nxt = buffers          # parity 0 writes buffers[1], parity 1 writes buffers[0]
+        else:
+            self.cur = torch.zeros(n, dtype=dtype, device=device)
+            self.nxt = torch.zeros(n, dtype=dtype, device=device)
         self.scale = torch.ones(1, dtype=dtype, device=device)
         self.norm2 = torch.zeros(1, dtype=dtype, device=device)
-        self.eig = None
+        self.eig = torch.zeros(1, dtype=dtype, device=device)
         self.parity = 0
+        self._graph = None
 
     def set_start(self, x0):
         """x0: full-length start vector (same on every rank)."""
+        if self.parity:                       # restart from buffer 0 so that peer-store targets stay in step on every rank
+            self.cur, self.nxt = self.nxt, self.cur
+            self.parity = 0
         self.cur.copy_(torch.as_tensor(x0, dtype=self.cur.dtype))
         self.scale.fill_(1.0 / float(np.linalg.norm(np.asarray(x0))))
 
@@ -65,10 +98,29 @@ class ShardedPowerIteration:
         if self.world > 1:
             dist.all_reduce(self.norm2)          # also orders iteration k+1 after every rank's stores of iteration k
         # ||u'|| = ||A x|| with ||x|| = 1: the dominant-eigenvalue estimate; next scale = 1 / ||u'||
-        self.eig = torch.sqrt(self.norm2)
+        torch.sqrt(self.norm2, out=self.eig)
         torch.reciprocal(self.eig, out=self.scale)
         self.cur, self.nxt = self.nxt, self.cur
         self.parity ^= 1
+
+    def capture_pair(self):
+        """Captures two consecutive iterations (one of each buffer parity) into a CUDA graph; replay() then runs
+        2 iterations per launch with no host work in between.  local_spmv must launch on torch's CURRENT stream."""
+        self.step()                       # warm both parities outside capture (lazy init inside kernels / NCCL)
+        self.step()
+        if self.parity:                   # capture from an even iteration so that python-side state survives replays
+            self.step()
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self.step()
+            self.step()
+        self._graph = g
+        return g
+
+    def replay(self, pairs):
+        for _ in range(pairs):
+            self._graph.replay()
 
     def eigenvalue(self):
         return float(self.eig.item())
