@@ -39,17 +39,21 @@ def measured_peak():
 
 
 class ClockSampler:
-    """Samples nvidia-smi clocks / throttle reasons during the timed region."""
+    """Samples nvidia-smi clocks / throttle reasons while the GPU runs the benchmark's steps.  The timed region of a
+    default run lasts tens of milliseconds, shorter than one nvidia-smi period, so the caller keeps the SAME steps
+    running for a further `soak` seconds straight after the timed region (untimed) and the samples taken between
+    mark_start() and the end of that soak are summarised; `window` in the summary says so."""
     Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
 
-    def __init__(self, index=0):
-        self.rows, self.proc, self.index = [], None, index
+    def __init__(self, index=0, soak=0.6):
+        self.rows, self.proc, self.index, self.soak_s = [], None, index, soak
+        self.t0 = self.t1 = None
 
     def __enter__(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
-                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                                          "-lms", "50"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
         except Exception:
@@ -58,11 +62,24 @@ class ClockSampler:
 
     def _read(self):
         for ln in self.proc.stdout:
-            self.rows.append([c.strip() for c in ln.split(",")])
+            self.rows.append((time.time(), [c.strip() for c in ln.split(",")]))
+
+    def mark_start(self):
+        self.t0 = time.time()
+
+    def soak(self, step_fn, sync_fn):
+        """Keeps the load of the timed region on the GPU for soak_s more seconds (not timed), then closes the window."""
+        end = time.time() + self.soak_s
+        while time.time() < end:
+            step_fn()
+            sync_fn()
+        self.t1 = time.time()
 
     def __exit__(self, *a):
+        if self.t1 is None:
+            self.t1 = time.time()
         if self.proc:
-            time.sleep(0.15)
+            time.sleep(0.1)
             self.proc.terminate()
             try:
                 self.proc.wait(timeout=5)
@@ -70,12 +87,16 @@ class ClockSampler:
                 self.proc.kill()
 
     def summary(self):
-        sm, mx, reasons = [], [], set()
+        sm, mx, pw, reasons = [], [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        t0 = (self.t0 or 0.0) + 0.06            # a sample reports the state of the preceding period
+        for ts, r in self.rows:
+            if ts < t0 or ts > (self.t1 or ts) + 0.06:
+                continue
             try:
                 sm.append(float(r[0]))
                 mx.append(float(r[1]))
+                pw.append(float(r[2]))
                 for nm, v in zip(names, r[3:7]):
                     if v.lower().startswith("active"):
                         reasons.add(nm)
@@ -83,7 +104,8 @@ class ClockSampler:
                 pass
         if not sm:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons), "samples": len(sm)}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "power_w_max": float(max(pw)), "reasons": sorted(reasons),
+                "samples": len(sm), "window": "timed region + %.1f s of the same steps run straight after it (untimed)" % self.soak_s}
 
 
 def cpu_csr_runner(rp, col, val, n):
@@ -217,11 +239,13 @@ def run_single(args):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with ClockSampler(0) as clk:
         torch.cuda.synchronize()
+        clk.mark_start()
         e0.record()
         for k in range(K):
             one_step(events=ev[k])
         e1.record()
         torch.cuda.synchronize()
+        clk.soak(one_step, torch.cuda.synchronize)
     ms_total = e0.elapsed_time(e1)
     ms_step = ms_total / K
     tot_nnz = sum(r["nnz"] for r in mats)
@@ -381,6 +405,7 @@ def run_power(args):
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
+        clk.mark_start()
         e0.record()
         if launch_mode.startswith("cuda_graph"):
             it.replay(K // 2)
@@ -391,6 +416,20 @@ def run_power(args):
                 it.step()
         e1.record()
         torch.cuda.synchronize()
+        # keep the same load running for the clock sampler: a fixed number of further iterations (identical on every rank)
+        n_soak = int(0.6 / max(e0.elapsed_time(e1) / K * 1e-3, 1e-5))
+        if world > 1:
+            tn = torch.tensor([n_soak], dtype=torch.int64, device=dev)
+            dist.all_reduce(tn, op=dist.ReduceOp.MAX)
+            n_soak = int(tn.item())
+        n_soak = min(n_soak, 4000)
+        if launch_mode.startswith("cuda_graph"):
+            it.replay(n_soak // 2 + 1)
+        else:
+            for _ in range(n_soak):
+                it.step()
+        torch.cuda.synchronize()
+        clk.t1 = time.time()
         if world > 1:
             dist.barrier()
     ms = torch.tensor([e0.elapsed_time(e1) * K / K_run], dtype=torch.float64, device=dev)
