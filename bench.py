@@ -141,9 +141,11 @@ def parse_args():
     ap.add_argument("--workload", default="auto", choices=["auto", "medium_sample", "config1", "g1", "g2", "power"])
     ap.add_argument("--format", default="csr", choices=["csr", "sell"])
     ap.add_argument("--rows-per-gpu", type=int, default=4194304)
-    ap.add_argument("--exchange", default="p2p", choices=["nccl", "p2p"])
+    ap.add_argument("--exchange", default="mc", choices=["nccl", "p2p", "mc"],
+                    help="N>1: mc = fused stores to an NVSwitch multicast address (falls back to p2p), p2p = fused unicast peer stores, nccl = all-gather")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-sell", action="store_true")
+    ap.add_argument("--no-nccl-leg", action="store_true", help="N>1: skip the plain-NCCL comparison leg")
     ap.add_argument("--no-graph", action="store_true", help="N>1: time an eager step loop instead of CUDA-graph replays")
     ap.add_argument("--x", default="ones", choices=["ones", "random"])
     ap.add_argument("--line", default=None, help="one generator parameter line to use as the N=1 workload (profiling)")
@@ -360,14 +362,36 @@ def run_power(args):
     del col, val
 
     exchange = args.exchange if world > 1 else "nccl"
-    pv = None
+    pv, mc_note = None, None
+    if exchange == "mc":
+        # fused exchange through NVSwitch multicast: every finished row is stored once, the switch replicates it.
+        # Every rank must agree before and after the (collective) symmetric-memory rendezvous, else fall back to p2p.
+        ok = torch.tensor([1 if power.multicast_supported(local) else 0], dtype=torch.int32, device=dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if int(ok.item()):
+            try:
+                pv = power.MulticastVectors(n, rank, world, dev)
+            except Exception as ex:
+                mc_note = "multicast setup failed: %s" % str(ex).splitlines()[0][:160]
+                pv = None
+            ok = torch.tensor([1 if pv is not None else 0], dtype=torch.int32, device=dev)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            if not int(ok.item()):
+                pv = None
+                mc_note = mc_note or "multicast setup failed on another rank"
+        else:
+            mc_note = "CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED is 0 on some rank"
+        if pv is None:
+            exchange = "p2p"
     if exchange == "p2p":
         # fused exchange: the SpMV epilogue stores every finished row into all peers' next-x buffers over NVLink
         pv = power.PeerVectors(n, rank, world, dev)
 
     def local_spmv(cur, slot, scale, norm2, parity):
         peers = ()
-        if pv is not None:
+        if exchange == "mc":
+            peers = [pv.mc[1 - parity] + 8 * i_s]
+        elif pv is not None:
             b = 1 - parity
             peers = [pv.peer[b][q] + 8 * i_s for q in range(world) if q != rank]
         MF.spmv_device(cur, slot, torch.cuda.current_stream().cuda_stream, scale=scale, norm2=norm2, peers=peers)
@@ -442,7 +466,7 @@ def run_power(args):
 
     # the plain-NCCL exchange (all-gather of y slots after the kernel), same protocol, reported beside the fused one
     nccl_cmp = None
-    if world > 1 and exchange == "p2p":
+    if world > 1 and exchange in ("p2p", "mc") and not args.no_nccl_leg:
         def plain_spmv(cur, slot, scale, norm2, parity):
             MF.spmv_device(cur, slot, stream, scale=scale, norm2=norm2)
         it2 = power.ShardedPowerIteration(n, bounds, rank, world, plain_spmv, dev, exchange="nccl")
@@ -512,8 +536,10 @@ def run_power(args):
             "ms_per_step": round(ms_step, 5), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic (reference artificial-matrix-generator restated bit-exactly, seed 14), power iteration from x = 1",
             "config": {"workload": "power_iteration config5-series: %s" % p.line(), "format": MF.format_name, "rows_per_gpu": args.rows_per_gpu,
-                       "total_nnz": int(nnz), "shard_rows": [int(b[1] - b[0]) for b in bounds], "exchange": ("fused: SpMV epilogue stores y rows into every peer's next-x buffer over NVLink (CUDA IPC) + NCCL scalar all-reduce"
-                                    if exchange == "p2p" else "NCCL in-place all-gather of y slots (one broadcast per owner) + scalar all-reduce"),
+                       "total_nnz": int(nnz), "shard_rows": [int(b[1] - b[0]) for b in bounds], "exchange": {"mc": "fused: SpMV epilogue stores each y row once to an NVSwitch multicast address (NVLS) mapped over every rank's next-x buffer + NCCL scalar all-reduce",
+                                    "p2p": "fused: SpMV epilogue stores y rows into every peer's next-x buffer over NVLink (CUDA IPC) + NCCL scalar all-reduce",
+                                    "nccl": "NCCL in-place all-gather of y slots (one broadcast per owner) + scalar all-reduce"}[exchange],
+                       "exchange_note": mc_note,
                        "l2_note": "each shard is %.1f GB (> 126 MB L2); no explicit flush" % (bc_loc * 1e-9), "generate_s": round(t_gen, 1)},
             "effective_GBs": round(bc / (ms_step * 1e-3) * 1e-9, 1),
             "roofline_frac_nominal_8TBs": round(bc / (ms_step * 1e-3) * 1e-9 / (NOMINAL_HBM_GBS * world), 4),

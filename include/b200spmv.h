@@ -63,7 +63,7 @@ typedef struct b200spmv_opts {
 	int32_t device;           /* CUDA device ordinal, -1 = current                                      */
 	int32_t sell_C;           /* slice height: power of two in [2, 256]; default 32                     */
 	int32_t sell_sigma;       /* sort window, multiple of sell_C; default 16384 (K/sell_c_s.cpp:59)     */
-	int32_t csr_nnz_per_thread; /* 8 | 16 | 32 non-zeros per thread of a 256-thread tile; 0 = auto      */
+	int32_t csr_nnz_per_thread; /* 4 | 8 | 16 | 32 non-zeros per thread of a 256-thread tile; 0 = auto  */
 	int32_t csr_ext;          /* tail-extension capacity in nnz (multiple of 8); 0 = auto               */
 	int32_t x_hint;           /* 0: L2 evict_last hint on x gathers (default), 1: plain loads           */
 	int32_t reserved[9];

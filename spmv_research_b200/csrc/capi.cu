@@ -60,8 +60,8 @@ static int validate_opts(const b200spmv_opts * in, b200spmv_opts * o, int64_t m,
 		const double avg = m > 0 ? (double) nnz / (double) m : 0.0;
 		o->csr_nnz_per_thread = (avg > 96.0) ? 16 : 8;
 	}
-	if (o->csr_nnz_per_thread != 8 && o->csr_nnz_per_thread != 16 && o->csr_nnz_per_thread != 32)
-		B200_FAIL("csr_nnz_per_thread must be 8, 16 or 32");
+	if (o->csr_nnz_per_thread != 4 && o->csr_nnz_per_thread != 8 && o->csr_nnz_per_thread != 16 && o->csr_nnz_per_thread != 32)
+		B200_FAIL("csr_nnz_per_thread must be 4, 8, 16 or 32");
 	if (o->csr_ext == 0)
 		o->csr_ext = (o->csr_nnz_per_thread <= 8) ? 256 : 2048;     // shared memory comes out of the L1 the x gathers live in
 	if (o->csr_ext < 64 || o->csr_ext % 64 || o->csr_ext > 8192)

@@ -45,7 +45,7 @@ __device__ __forceinline__ double block_sum_range(const double * s_prod, int a, 
 }
 
 template <int NPT, bool HINT>
-__global__ void __launch_bounds__(CSR_THREADS, (NPT <= 8) ? 6 : ((NPT <= 16) ? 3 : 2))
+__global__ void __launch_bounds__(CSR_THREADS, (NPT <= 4) ? 8 : ((NPT <= 8) ? 6 : ((NPT <= 16) ? 3 : 2)))
 csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict__ col, const double * __restrict__ val,
                 const int2 * __restrict__ tile_info, const double * __restrict__ x,
                 double * __restrict__ tile_head, double * __restrict__ tile_tail,
@@ -292,6 +292,7 @@ int launch_csr_spmv(b200spmv * h, const double * dx, double * dy, cudaStream_t s
 	int rc;
 	const bool hint = (h->x_hint == 0);
 	switch (h->npt) {
+	case 4:  rc = hint ? launch_tiles<4, true>(h, dx, st, out) : launch_tiles<4, false>(h, dx, st, out); break;
 	case 8:  rc = hint ? launch_tiles<8, true>(h, dx, st, out) : launch_tiles<8, false>(h, dx, st, out); break;
 	case 16: rc = hint ? launch_tiles<16, true>(h, dx, st, out) : launch_tiles<16, false>(h, dx, st, out); break;
 	case 32: rc = hint ? launch_tiles<32, true>(h, dx, st, out) : launch_tiles<32, false>(h, dx, st, out); break;

@@ -10,7 +10,9 @@ comes out of the same kernel, then the slots are exchanged (all-gather with uneq
 one broadcast per owner, in place) and one scalar all-reduce gives the next norm.
 `exchange="p2p"` instead lets the SpMV epilogue store every finished row into all peers' next-x
 buffers over NVLink (CUDA IPC mappings), so the only collective left is the scalar all-reduce,
-which also orders the iterations.
+which also orders the iterations.  `exchange="mc"` stores each finished row ONCE to an NVSwitch
+multicast address (NVLS) that the switch replicates into every GPU's next-x buffer, so a rank's
+NVLink egress is 8 bytes per row instead of 8 * (P - 1).
 torch.distributed is plumbing here; the arithmetic is in libb200spmv.so.
 """
 import numpy as np
@@ -59,6 +61,56 @@ class PeerVectors:
         every = [None] * world
         dist.all_gather_object(every, mine)
         self.peer = [[self.ptr[b] if q == rank else capi.ipc_import(every[q][b]) for q in range(world)] for b in range(2)]
+
+
+def multicast_supported(device_index):
+    """CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED of one device (driver query through cuda-python); False on any failure."""
+    try:
+        from cuda.bindings import driver
+        err, = driver.cuInit(0)
+        err, dev = driver.cuDeviceGet(int(device_index))
+        if int(err) != 0:
+            return False
+        err, v = driver.cuDeviceGetAttribute(driver.CUdevice_attribute.CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, dev)
+        return int(err) == 0 and int(v) != 0
+    except Exception:
+        return False
+
+
+class MulticastVectors:
+    """Two full-length x buffers per rank in symmetric memory bound to an NVSwitch multicast object.
+    torch.distributed._symmetric_memory is the plumbing (cuMemCreate / cuMulticastCreate / handle exchange);
+    the stores are issued by the SpMV epilogue of libb200spmv.  mc[b] is the multicast address of buffer b
+    (a store to mc[b] + off lands at offset off of EVERY rank's buffer b, this rank's included);
+    peer[b][q] is the unicast address of rank q's buffer b.  Raises when the box has no multicast support."""
+
+    def __init__(self, n, rank, world, device):
+        import os
+        os.environ.setdefault("TORCH_SYMMMEM_IMPLICIT_POOL", "0")      # one allocation per tensor: offset 0 in its block
+        import torch.distributed._symmetric_memory as symm_mem
+        try:
+            symm_mem.set_backend("CUDA")          # cuMem* + multicast objects (not NVSHMEM / NCCL windows)
+        except Exception:
+            pass
+        self.n = n
+        self.tensors, self.hdl, self.mc, self.peer = [], [], [], []
+        for _ in range(2):
+            t = symm_mem.empty(n, dtype=torch.float64, device=device)
+            h = symm_mem.rendezvous(t, dist.group.WORLD)
+            off = int(getattr(h, "offset", 0) or 0)
+            mc = int(h.multicast_ptr or 0)
+            if mc == 0:
+                raise RuntimeError("symmetric memory has no multicast mapping on this box")
+            ptrs = [int(q) + off for q in h.buffer_ptrs]
+            if ptrs[rank] != t.data_ptr():
+                raise RuntimeError("symmetric memory: local buffer address does not match the tensor")
+            t.zero_()
+            self.tensors.append(t)
+            self.hdl.append(h)
+            self.mc.append(mc + off)
+            self.peer.append(ptrs)
+        torch.cuda.synchronize()
+        dist.barrier()
 
 
 class ShardedPowerIteration:

@@ -19,7 +19,8 @@ lines = [H.CONFIG1.line()] + [p.line() for p in H.medium_sample()]
 if mode == "full":
     lines += ["8388607 8388607 50 16.6667 gamma random 0.6 10000 0.05 0.05 14", "8388607 8388607 50 150 gamma random 0.6 0 0.05 0.05 14",
               "4194304 4194304 60 20 normal random 0.3 0 0.5 0.5 14"]
-variants = [("csr npt8", dict(format=S.CSR_ADAPTIVE, csr_nnz_per_thread=8)),
+variants = [("csr npt4", dict(format=S.CSR_ADAPTIVE, csr_nnz_per_thread=4)),
+            ("csr npt8", dict(format=S.CSR_ADAPTIVE, csr_nnz_per_thread=8)),
             ("csr npt16", dict(format=S.CSR_ADAPTIVE, csr_nnz_per_thread=16)),
             ("csr npt32", dict(format=S.CSR_ADAPTIVE, csr_nnz_per_thread=32)),
             ("csr npt8 nohint", dict(format=S.CSR_ADAPTIVE, csr_nnz_per_thread=8, x_hint=1)),
