@@ -139,7 +139,8 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="auto", choices=["auto", "medium_sample", "config1", "g1", "g2", "power"])
-    ap.add_argument("--format", default="csr", choices=["csr", "sell"])
+    ap.add_argument("--format", default=None, choices=["auto", "csr", "sell"],
+                    help="default: auto at N=1 (both formats built, the faster kept per matrix), csr at N>1")
     ap.add_argument("--rows-per-gpu", type=int, default=4194304)
     ap.add_argument("--exchange", default="mc", choices=["nccl", "p2p", "mc"],
                     help="N>1: mc = fused stores to an NVSwitch multicast address (falls back to p2p), p2p = fused unicast peer stores, nccl = all-gather")
@@ -184,7 +185,9 @@ def run_single(args):
     dev = torch.device("cuda:0")
     stream = torch.cuda.current_stream().cuda_stream
     wl, plist = workload_params(args, 1)
-    fmt = S.CSR_ADAPTIVE if args.format == "csr" else S.SELL_C_SIGMA
+    FM = {"auto": S.AUTO, "csr": S.CSR_ADAPTIVE, "sell": S.SELL_C_SIGMA}
+    fmt = FM[args.format or "auto"]
+    others = [] if args.no_sell else [f for f in (S.CSR_ADAPTIVE, S.SELL_C_SIGMA) if f != fmt]
     peak, peak_src = measured_peak()
 
     mats, t_gen = [], 0.0
@@ -195,13 +198,11 @@ def run_single(args):
         t_gen += time.time() - t0
         m, n, nnz = p.rows, p.cols, int(rp[-1])
         MF = S.csr_to_format(rp, col, val, m, n, nnz, 0, 0, format=fmt)
-        MF2 = None
-        if not args.no_sell:
-            MF2 = S.csr_to_format(rp, col, val, m, n, nnz, 0, 0, format=(S.SELL_C_SIGMA if fmt == S.CSR_ADAPTIVE else S.CSR_ADAPTIVE))
+        MFo = [S.csr_to_format(rp, col, val, m, n, nnz, 0, 0, format=f) for f in others]
         x_h = np.ones(n) if args.x == "ones" else np.random.default_rng(14).uniform(-1, 1, n)
         dx = torch.from_numpy(x_h).to(dev)
         dy = torch.full((m,), 1.0, dtype=torch.float64, device=dev)
-        rec = dict(p=p, m=m, n=n, nnz=nnz, MF=MF, MF2=MF2, dx=dx, dy=dy, x_h=x_h, bc=H.compulsory_bytes(m, n, nnz))
+        rec = dict(p=p, m=m, n=n, nnz=nnz, MF=MF, MFo=MFo, dx=dx, dy=dy, x_h=x_h, bc=H.compulsory_bytes(m, n, nnz))
         # CPU baseline leg (rank 0, bounded: 1 warm-up + 3 timed calls per matrix) and a parity spot check
         if not args.no_cpu_baseline:
             from oracle import oracle as O
@@ -225,11 +226,11 @@ def run_single(args):
         mats.append(rec)
         del rp, col, val
 
-    def one_step(which="MF", events=None):
+    def one_step(which=-1, events=None):
         for i, r in enumerate(mats):
             if events is not None:
                 events[i][0].record()
-            r[which].spmv_device(r["dx"], r["dy"], stream)
+            (r["MF"] if which < 0 else r["MFo"][which]).spmv_device(r["dx"], r["dy"], stream)
             if events is not None:
                 events[i][1].record()
 
@@ -260,26 +261,26 @@ def run_single(args):
         t = float(np.mean([ev[k][i][0].elapsed_time(ev[k][i][1]) for k in range(K)]))
         kern_ms += t
         st = r["MF"].handle.stats()
-        per.append({"matrix": r["p"].line(), "nnz": r["nnz"], "ms": round(t, 5), "gflops": round(2.0 * r["nnz"] / t * 1e-6, 1),
+        per.append({"matrix": r["p"].line(), "format": r["MF"].format_name, "trial_ms": r["MF"].trial_ms, "nnz": r["nnz"], "ms": round(t, 5), "gflops": round(2.0 * r["nnz"] / t * 1e-6, 1),
                     "eff_GBs": round(r["bc"] / t * 1e-6, 1), "frac_of_measured": round(r["bc"] / t * 1e-6 / peak, 4),
                     "launches": r["MF"].gpu_launches_per_spmv, "split_rows": int(st["nsplit"])})
     launches = K * sum(r["MF"].gpu_launches_per_spmv for r in mats)
 
     # the other format, same protocol, reported beside (not the headline)
-    other = None
-    if not args.no_sell:
+    other = []
+    for oi in range(len(others)):
         for _ in range(W):
-            one_step("MF2")
+            one_step(oi)
         torch.cuda.synchronize()
         e0.record()
         for k in range(K):
-            one_step("MF2", events=ev[k])
+            one_step(oi, events=ev[k])
         e1.record()
         torch.cuda.synchronize()
         ms2 = e0.elapsed_time(e1) / K
-        other = {"format": mats[0]["MF2"].format_name, "ms_per_step": round(ms2, 5), "gflops": round(2.0 * tot_nnz / ms2 * 1e-6, 1),
-                 "eff_GBs": round(tot_bc / ms2 * 1e-6, 1),
-                 "per_matrix_ms": [round(float(np.mean([ev[k][i][0].elapsed_time(ev[k][i][1]) for k in range(K)])), 5) for i in range(len(mats))]}
+        other.append({"format": mats[0]["MFo"][oi].format_name, "ms_per_step": round(ms2, 5), "gflops": round(2.0 * tot_nnz / ms2 * 1e-6, 1),
+                      "eff_GBs": round(tot_bc / ms2 * 1e-6, 1),
+                      "per_matrix_ms": [round(float(np.mean([ev[k][i][0].elapsed_time(ev[k][i][1]) for k in range(K)])), 5) for i in range(len(mats))]})
 
     # end to end through the reference-facing call with host buffers: H2D x + kernel + D2H y + sync per call
     hx, hy = [], []
@@ -305,17 +306,19 @@ def run_single(args):
         "metric": METRIC, "value": round(gflops, 2), "unit": "GFLOP/s", "n_gpus": 1, "steps": K, "warmup": W,
         "ms_per_step": round(ms_step, 5), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic (reference artificial-matrix-generator restated bit-exactly, seed 14), x = %s" % args.x,
-        "config": {"workload": wl, "format": mats[0]["MF"].format_name, "matrices": len(mats), "total_nnz": int(tot_nnz),
+        "config": {"workload": wl, "format": {S.AUTO: "B200_AUTO (per matrix: CSR-adaptive or SELL-C-sigma, picked by a device-timed trial inside csr_to_format)",
+                                                  S.CSR_ADAPTIVE: "B200_CSR_ADAPTIVE", S.SELL_C_SIGMA: "B200_SELL_C_SIGMA"}[fmt], "matrices": len(mats), "total_nnz": int(tot_nnz),
                    "compulsory_bytes_per_step": int(tot_bc),
                    "l2_note": "every matrix >= 320 MB CSR (> 126 MB L2) and a step streams %.1f GB, so nothing of a matrix survives "
                               "in L2 between its uses; no explicit flush" % (tot_bc * 1e-9),
                    "generate_s": round(t_gen, 1)},
         "effective_GBs": round(eff, 1), "roofline_frac_nominal_8TBs": round(eff / NOMINAL_HBM_GBS, 4),
-        "roofline": {"bound": "hbm", "kernel": "csr_tile_kernel" if fmt == S.CSR_ADAPTIVE else "sell_kernel",
+        "roofline": {"bound": "hbm", "kernel": {S.AUTO: "csr_tile_kernel / sell_kernel (per matrix, see per_matrix[].format)",
+                                                S.CSR_ADAPTIVE: "csr_tile_kernel", S.SELL_C_SIGMA: "sell_kernel"}[fmt],
                      "achieved": round(tot_bc / kern_ms * 1e-6, 1), "peak": peak, "unit": "GB/s",
                      "frac": round(tot_bc / kern_ms * 1e-6 / peak, 4), "traffic": None, "peak_source": peak_src,
                      "achieved_def": "compulsory bytes B_c = 12 nnz + 12 m + 8 n + 4 per SpMV / CUDA-event time of that SpMV, summed over the sample"},
-        "e2e": e2e, "gpu_launches": int(launches), "clocks": clk.summary(), "per_matrix": per, "other_format": other,
+        "e2e": e2e, "gpu_launches": int(launches), "clocks": clk.summary(), "per_matrix": per, "other_formats": other,
     }
     if not args.no_cpu_baseline and cpu["t"] > 0:
         out["cpu_baseline"] = {"value": round(cpu["flops"] / cpu["t"] * 1e-9, 3), "unit": "GFLOP/s", "cores": cpu["cores"], "kind": cpu["kind"],
@@ -343,7 +346,7 @@ def run_power(args):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
     stream = torch.cuda.current_stream().cuda_stream
-    fmt = S.CSR_ADAPTIVE if args.format == "csr" else S.SELL_C_SIGMA
+    fmt = {"auto": S.AUTO, "csr": S.CSR_ADAPTIVE, "sell": S.SELL_C_SIGMA}[args.format or "csr"]
     peak, peak_src = measured_peak()
     p = H.config5(world, args.rows_per_gpu)
 
@@ -543,7 +546,7 @@ def run_power(args):
                        "l2_note": "each shard is %.1f GB (> 126 MB L2); no explicit flush" % (bc_loc * 1e-9), "generate_s": round(t_gen, 1)},
             "effective_GBs": round(bc / (ms_step * 1e-3) * 1e-9, 1),
             "roofline_frac_nominal_8TBs": round(bc / (ms_step * 1e-3) * 1e-9 / (NOMINAL_HBM_GBS * world), 4),
-            "roofline": {"bound": "hbm", "kernel": "csr_tile_kernel" if fmt == S.CSR_ADAPTIVE else "sell_kernel",
+            "roofline": {"bound": "hbm", "kernel": "csr_tile_kernel" if MF.format == S.CSR_ADAPTIVE else "sell_kernel",
                          "achieved": round(bc_loc / float(kms.item()) * 1e-6, 1), "peak": peak, "unit": "GB/s",
                          "frac": round(bc_loc / float(kms.item()) * 1e-6 / peak, 4), "traffic": None, "peak_source": peak_src,
                          "achieved_def": "rank-0 shard compulsory bytes / slowest rank's kernel-only SpMV time (CUDA events, 5 launches)"},

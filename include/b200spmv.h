@@ -37,7 +37,9 @@ typedef struct b200spmv b200spmv_t;
 
 enum {
 	B200SPMV_CSR_ADAPTIVE = 0,   /* nnz-tiled adaptive CSR (thread / sub-warp / warp / block per row) */
-	B200SPMV_SELL_C_SIGMA = 1    /* SELL-C-sigma, converted on the GPU                               */
+	B200SPMV_SELL_C_SIGMA = 1,   /* SELL-C-sigma, converted on the GPU                               */
+	B200SPMV_AUTO         = 2    /* both are built at create time, each timed on the device for a few
+	                                products, the faster one is kept (b200spmv_format() says which)  */
 };
 
 /* b200spmv_spmv_host_ex flags */
@@ -66,7 +68,10 @@ typedef struct b200spmv_opts {
 	int32_t csr_nnz_per_thread; /* 4 | 8 | 16 | 32 non-zeros per thread of a 256-thread tile; 0 = auto  */
 	int32_t csr_ext;          /* tail-extension capacity in nnz (multiple of 8); 0 = auto               */
 	int32_t x_hint;           /* 0: L2 evict_last hint on x gathers (default), 1: plain loads           */
-	int32_t reserved[9];
+	int32_t sell_sigma_alt;   /* AUTO only: second sort window tried (0 = default 256, -1 = none)       */
+	int32_t sell_variant;     /* SELL kernel shape (k steps in flight x resident warps per SM): 0 = 8 x 32
+	                             (default), 1 = 8 x 48, 2 = 4 x 64, 3 = 16 x 16                          */
+	int32_t reserved[7];
 } b200spmv_opts;
 
 /* extra outputs / inputs of one device-resident product (all pointers are DEVICE pointers) */
@@ -99,11 +104,15 @@ int b200spmv_spmv_host_ex(b200spmv_t * h, const double * x, double * y, int32_t 
 int b200spmv_spmv_device(b200spmv_t * h, const double * dx, double * dy, void * stream);
 int b200spmv_spmv_device_ex(b200spmv_t * h, const double * dx, double * dy, void * stream, const b200spmv_launch * launch);
 
+/* The format that runs: B200SPMV_CSR_ADAPTIVE or B200SPMV_SELL_C_SIGMA (what AUTO resolved to). */
+int32_t b200spmv_format(const b200spmv_t * h);
+
 /* Number of kernel launches one b200spmv_spmv_device call issues for this handle (1 or 2). */
 int32_t b200spmv_launches_per_spmv(const b200spmv_t * h);
 
 /* Format statistics: out[0]=mem_footprint bytes, [1]=ntiles or nslices, [2]=nsplit rows,
- * [3]=padded entries (SELL) or nnz, [4]=tile nnz (CSR) or C (SELL), [5]=ext capacity or sigma, [6]=convert ms. */
+ * [3]=padded entries (SELL) or nnz, [4]=tile nnz (CSR) or C (SELL), [5]=ext capacity or sigma, [6]=convert ms,
+ * [7..9]=AUTO trial ms per product of CSR, SELL(sell_sigma), SELL(sell_sigma_alt); 0 = not tried. */
 int b200spmv_stats(const b200spmv_t * h, double * out, int32_t n_out);
 
 int b200spmv_export(const b200spmv_t * h, int32_t what, void * dst_host, int64_t capacity_bytes, int64_t * count_out);

@@ -13,6 +13,7 @@ SO_PATH = os.path.join(_HERE, "lib", "libb200spmv.so")
 
 CSR_ADAPTIVE = 0
 SELL_C_SIGMA = 1
+AUTO = 2
 SKIP_X_UPLOAD = 1
 SKIP_Y_DOWNLOAD = 2
 X_ROW_ORDER, X_SLICE_WIDTH, X_SLICE_PTR, X_SELL_COL, X_SELL_VAL, X_TILE_ROW, X_SPLIT_ROW, X_SPLIT_TILE = range(1, 9)
@@ -26,7 +27,7 @@ class B200Error(RuntimeError):
 
 class Opts(C.Structure):
     _fields_ = [("format", C.c_int32), ("device", C.c_int32), ("sell_C", C.c_int32), ("sell_sigma", C.c_int32),
-                ("csr_nnz_per_thread", C.c_int32), ("csr_ext", C.c_int32), ("x_hint", C.c_int32), ("reserved", C.c_int32 * 9)]
+                ("csr_nnz_per_thread", C.c_int32), ("csr_ext", C.c_int32), ("x_hint", C.c_int32), ("sell_sigma_alt", C.c_int32), ("sell_variant", C.c_int32), ("reserved", C.c_int32 * 7)]
 
 
 class Launch(C.Structure):
@@ -56,6 +57,7 @@ def lib():
         "b200spmv_spmv_device": (C.c_int, [vp, vp, vp, vp]),
         "b200spmv_spmv_device_ex": (C.c_int, [vp, vp, vp, vp, C.POINTER(Launch)]),
         "b200spmv_launches_per_spmv": (i32, [vp]),
+        "b200spmv_format": (i32, [vp]),
         "b200spmv_stats": (C.c_int, [vp, C.POINTER(C.c_double), i32]),
         "b200spmv_export": (C.c_int, [vp, i32, vp, i64, C.POINTER(i64)]),
         "b200spmv_partition_device": (C.c_int, [vp, i64, i64, i32, vp]),
@@ -150,10 +152,16 @@ class Handle:
     def launches_per_spmv(self):
         return int(lib().b200spmv_launches_per_spmv(self._h))
 
+    @property
+    def format(self):
+        """The format that runs (AUTO handles report what they resolved to)."""
+        return int(lib().b200spmv_format(self._h))
+
     def stats(self):
-        out = (C.c_double * 7)()
-        check(lib().b200spmv_stats(self._h, out, 7))
-        keys = ("mem_footprint", "units", "nsplit", "entries", "unit_size", "ext_or_sigma", "convert_ms")
+        out = (C.c_double * 10)()
+        check(lib().b200spmv_stats(self._h, out, 10))
+        keys = ("mem_footprint", "units", "nsplit", "entries", "unit_size", "ext_or_sigma", "convert_ms",
+                "trial_ms_csr", "trial_ms_sell", "trial_ms_sell_alt")
         return dict(zip(keys, list(out)))
 
     def export(self, what):

@@ -45,8 +45,12 @@ static int validate_opts(const b200spmv_opts * in, b200spmv_opts * o, int64_t m,
 		B200_FAIL("negative dimension");
 	if (m >= 0x7fffffffLL || n > 0x7fffffffLL || nnz > 0x7fffffffLL)
 		B200_FAIL("m, n and nnz must fit int32 indices (INT_T = int32_t)");
-	if (o->format != B200SPMV_CSR_ADAPTIVE && o->format != B200SPMV_SELL_C_SIGMA)
+	if (o->format != B200SPMV_CSR_ADAPTIVE && o->format != B200SPMV_SELL_C_SIGMA && o->format != B200SPMV_AUTO)
 		B200_FAIL("unknown format %d", o->format);
+	if (o->sell_sigma_alt == 0)
+		o->sell_sigma_alt = 256;
+	if (o->sell_variant < 0 || o->sell_variant > 3)
+		B200_FAIL("sell_variant must be in [0, 3]");
 	if (o->sell_C == 0)
 		o->sell_C = 32;
 	if (o->sell_sigma == 0)
@@ -57,8 +61,8 @@ static int validate_opts(const b200spmv_opts * in, b200spmv_opts * o, int64_t m,
 		B200_FAIL("sell_sigma must be a positive multiple of sell_C");
 	if (o->csr_nnz_per_thread == 0) {
 		// auto: larger windows for longer rows keep the tail extension a small fraction of the window
-		const double avg = m > 0 ? (double) nnz / (double) m : 0.0;
-		o->csr_nnz_per_thread = (avg > 96.0) ? 16 : 8;
+		// measured on B200 (profiles/r01e_sweep.txt): 2 048-nnz tiles win for every row length, also avg 500
+		o->csr_nnz_per_thread = 8;
 	}
 	if (o->csr_nnz_per_thread != 4 && o->csr_nnz_per_thread != 8 && o->csr_nnz_per_thread != 16 && o->csr_nnz_per_thread != 32)
 		B200_FAIL("csr_nnz_per_thread must be 4, 8, 16 or 32");
@@ -74,6 +78,129 @@ __global__ void rebase_row_ptr_kernel(const int32_t * __restrict__ in, int32_t *
 	const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
 	if (i < m1)
 		out[i] = in[i] - in[0];
+}
+
+static void free_sell(b200spmv * h)
+{
+	void ** ptrs[] = { (void **) &h->d_row_order, (void **) &h->d_slice_width, (void **) &h->d_slice_ptr, (void **) &h->d_scol,
+	                   (void **) &h->d_sval, (void **) &h->d_sell_items, (void **) &h->d_sell_cuts, (void **) &h->d_sell_partial };
+	for (void ** p : ptrs) {
+		if (*p)
+			cudaFree(*p);
+		*p = nullptr;
+	}
+	h->sell_nitems = h->sell_ncuts = h->sell_nslots = 0;
+	h->nslices = h->padded = 0;
+}
+
+static void free_csr_plan(b200spmv * h, bool arrays)
+{
+	void ** ptrs[] = { (void **) &h->d_tile_row, (void **) &h->d_split_row, (void **) &h->d_split_tile, (void **) &h->d_tile_head,
+	                   (void **) &h->d_tile_tail };
+	for (void ** p : ptrs) {
+		if (*p)
+			cudaFree(*p);
+		*p = nullptr;
+	}
+	if (arrays) {
+		if (h->d_col) cudaFree(h->d_col);
+		if (h->d_val) cudaFree(h->d_val);
+		h->d_col = nullptr;
+		h->d_val = nullptr;
+	}
+}
+
+// AUTO trial: median of 5 device-timed products (after 2 untimed) of the format h->format currently names.
+static int trial_ms(b200spmv * h, cudaEvent_t e0, cudaEvent_t e1, float * out)
+{
+	float t[5];
+	for (int i = 0; i < 7; i++) {
+		if (i >= 2)
+			CU(cudaEventRecord(e0, h->stream));
+		const int rc = (h->format == B200SPMV_CSR_ADAPTIVE) ? launch_csr_spmv(h, h->d_x, h->d_y, h->stream, nullptr)
+		                                                    : launch_sell_spmv(h, h->d_x, h->d_y, h->stream, nullptr);
+		if (rc)
+			return 1;
+		if (i >= 2) {
+			CU(cudaEventRecord(e1, h->stream));
+			CU(cudaEventSynchronize(e1));
+			CU(cudaEventElapsedTime(&t[i - 2], e0, e1));
+		}
+	}
+	for (int i = 1; i < 5; i++)
+		for (int j = i; j > 0 && t[j] < t[j - 1]; j--) {
+			const float x = t[j]; t[j] = t[j - 1]; t[j - 1] = x;
+		}
+	*out = t[2];
+	return 0;
+}
+
+// B200SPMV_AUTO: plan CSR, convert SELL-C-sigma for each candidate window, time each on the device, keep the fastest.
+// The gather pattern depends on col_ind only, so a zero x vector times the same memory traffic as a real one.
+static int auto_select_impl(b200spmv * h, const b200spmv_opts & o, cudaEvent_t e0, cudaEvent_t e1);
+
+static int auto_select(b200spmv * h, const b200spmv_opts & o)
+{
+	cudaEvent_t e0 = nullptr, e1 = nullptr;
+	CU(cudaEventCreate(&e0));
+	CU(cudaEventCreate(&e1));
+	const int rc = auto_select_impl(h, o, e0, e1);
+	cudaEventDestroy(e0);
+	cudaEventDestroy(e1);
+	return rc;
+}
+
+static int auto_select_impl(b200spmv * h, const b200spmv_opts & o, cudaEvent_t e0, cudaEvent_t e1)
+{
+	CU(cudaMalloc(&h->d_x, (h->n > 0 ? h->n : 1) * sizeof(double)));
+	CU(cudaMalloc(&h->d_y, (h->m > 0 ? h->m : 1) * sizeof(double)));
+	CU(cudaMemsetAsync(h->d_x, 0, (h->n > 0 ? h->n : 1) * sizeof(double), h->stream));
+	h->format = B200SPMV_CSR_ADAPTIVE;
+	if (csr_plan_tiles(h))
+		return 1;
+	if (h->nnz == 0 || h->m == 0)
+		return 0;                                   // nothing to time: CSR
+	if (trial_ms(h, e0, e1, &h->trial_ms[0]))
+		return 1;
+	float best = h->trial_ms[0];
+	int64_t best_sigma = 0;                         // 0 = CSR
+	int64_t cand[2] = { o.sell_sigma, o.sell_sigma_alt > 0 ? (int64_t) o.sell_sigma_alt : 0 };
+	if (cand[1] == cand[0] || (cand[1] > 0 && (cand[1] < h->C || cand[1] % h->C)))
+		cand[1] = 0;
+	h->sell_pad_limit = h->nnz + h->nnz / 2 + 64 * (int64_t) h->C;      // > 50 % padding cannot win: skip the candidate
+	h->format = B200SPMV_SELL_C_SIGMA;
+	for (int c = 0; c < 2; c++) {
+		if (cand[c] <= 0)
+			continue;
+		h->sigma = cand[c];
+		const int rc = sell_convert(h);
+		if (rc == 1)
+			return 1;
+		if (rc == 0) {
+			if (trial_ms(h, e0, e1, &h->trial_ms[1 + c]))
+				return 1;
+			if (h->trial_ms[1 + c] < best) {
+				best = h->trial_ms[1 + c];
+				best_sigma = cand[c];
+			}
+		}
+		// keep the arrays only when this is the last candidate and it is the winner; otherwise rebuild the winner below
+		if (!(best_sigma == cand[c] && (c == 1 || cand[1] <= 0)))
+			free_sell(h);
+	}
+	h->sell_pad_limit = 0;
+	if (best_sigma == 0) {
+		free_sell(h);
+		h->format = B200SPMV_CSR_ADAPTIVE;
+		h->sigma = o.sell_sigma;
+		return 0;
+	}
+	h->sigma = best_sigma;
+	if (!h->d_scol && sell_convert(h))
+		return 1;
+	free_csr_plan(h, true);
+	h->ntiles = h->nsplit = 0;
+	return 0;
 }
 
 static void free_handle(b200spmv * h)
@@ -109,6 +236,7 @@ static int create_common(b200spmv ** out, const int32_t * row_ptr, const int32_t
 	if (!h)
 		B200_FAIL("out of host memory");
 	h->format = o.format;
+	h->requested_format = o.format;
 	CU(cudaGetDevice(&h->device));
 	h->m = m;
 	h->n = n;
@@ -119,6 +247,7 @@ static int create_common(b200spmv ** out, const int32_t * row_ptr, const int32_t
 	h->ext = o.csr_ext;
 	h->C = o.sell_C;
 	h->sigma = o.sell_sigma;
+	h->sell_variant = o.sell_variant;
 	int rc = 1;
 	cudaEvent_t e0 = nullptr, e1 = nullptr;
 	do {
@@ -150,7 +279,11 @@ static int create_common(b200spmv ** out, const int32_t * row_ptr, const int32_t
 		}
 		if (cudaStreamSynchronize(h->stream) != cudaSuccess) break;
 		int64_t norm_slots;
-		if (h->format == B200SPMV_CSR_ADAPTIVE) {
+		if (h->format == B200SPMV_AUTO) {
+			if (auto_select(h, o)) goto fail;           // convert_ms of an AUTO handle includes the trials
+			norm_slots = (h->format == B200SPMV_CSR_ADAPTIVE) ? h->ntiles + h->nsplit
+			                                                   : (h->sell_nitems + 3) / 4 + (h->sell_ncuts + 3) / 4;
+		} else if (h->format == B200SPMV_CSR_ADAPTIVE) {
 			if (csr_plan_tiles(h)) goto fail;
 			norm_slots = h->ntiles + h->nsplit;
 		} else {
@@ -203,6 +336,8 @@ extern "C" void b200spmv_destroy(b200spmv_t * h)
 	}
 }
 
+extern "C" int32_t b200spmv_format(const b200spmv_t * h) { return h ? h->format : -1; }
+
 extern "C" int32_t b200spmv_launches_per_spmv(const b200spmv_t * h)
 {
 	if (!h)
@@ -235,8 +370,10 @@ extern "C" int b200spmv_spmv_host_ex(b200spmv_t * h, const double * x, double * 
 	if (!h->d_x) {
 		CU(cudaMalloc(&h->d_x, (h->n > 0 ? h->n : 1) * sizeof(double)));
 		CU(cudaMalloc(&h->d_y, (h->m > 0 ? h->m : 1) * sizeof(double)));
-		flags &= ~B200SPMV_SKIP_X_UPLOAD;
 	}
+	if (!h->x_uploaded)
+		flags &= ~B200SPMV_SKIP_X_UPLOAD;           // nothing to reuse yet
+	h->x_uploaded = 1;
 	if (!(flags & B200SPMV_SKIP_X_UPLOAD) && h->n > 0)
 		CU(cudaMemcpyAsync(h->d_x, x, h->n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
 	if (b200spmv_spmv_device_ex(h, h->d_x, h->d_y, h->stream, nullptr))
@@ -259,7 +396,9 @@ extern "C" int b200spmv_stats(const b200spmv_t * h, double * out, int32_t n_out)
 {
 	if (!h || !out)
 		B200_FAIL("NULL argument");
-	double v[7];
+	double v[10];
+	for (int i = 0; i < 3; i++)
+		v[7 + i] = (double) h->trial_ms[i];
 	if (h->format == B200SPMV_CSR_ADAPTIVE) {
 		v[0] = (double) h->nnz * 12.0 + (double) (h->m + 1) * 4.0 + (double) (h->ntiles + 1) * 8.0 + (double) h->ntiles * 16.0 + (double) h->nsplit * 8.0;
 		v[1] = (double) h->ntiles;
@@ -277,7 +416,7 @@ extern "C" int b200spmv_stats(const b200spmv_t * h, double * out, int32_t n_out)
 		v[5] = (double) h->sigma;
 	}
 	v[6] = (double) h->convert_ms;
-	for (int i = 0; i < n_out && i < 7; i++)
+	for (int i = 0; i < n_out && i < 10; i++)
 		out[i] = v[i];
 	return 0;
 }

@@ -146,7 +146,11 @@ __device__ __forceinline__ double warp_sum(double v)
 // The handle
 // ---------------------------------------------------------------------------------------------
 struct b200spmv {
-	int format, device;
+	int format, device;           // format: the format that runs (AUTO resolves to CSR or SELL at create time)
+	int requested_format;
+	int x_uploaded;               // the host-vector entry point has staged an x at least once
+	float trial_ms[4];            // AUTO: measured product time of {CSR, SELL sigma, SELL sigma_alt, -}; 0 = not tried
+	int64_t sell_pad_limit;       // AUTO: a SELL candidate padded beyond this many entries is skipped (0 = no limit)
 	int64_t m, n, nnz;
 	int x_hint;
 	cudaStream_t stream;
@@ -171,6 +175,7 @@ struct b200spmv {
 
 	// SELL-C-sigma (device)
 	int C;
+	int sell_variant;         // kernel shape: 0 = 8 steps x 32 warps/SM, 1 = 8 x 48, 2 = 4 x 64, 3 = 16 x 16
 	int64_t sigma, nslices, padded;
 	int32_t * d_row_order;
 	int32_t * d_slice_width;

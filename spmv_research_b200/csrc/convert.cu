@@ -338,7 +338,13 @@ __global__ void sell_item_count_kernel(const int32_t * __restrict__ slice_width,
 	cut_off[s] = (n > 1) ? G : 0;
 }
 
-__global__ void sell_item_fill_kernel(const int32_t * __restrict__ slice_width, int64_t nslices, int G, const int64_t * __restrict__ item_off,
+// Item record (16 bytes, everything the SpMV warp needs, no dependent look-ups):
+//   x = low 32 bits of the first entry's offset in scol / sval (slice_ptr[s] + k0 * C + 32 * g)
+//   y = bits 0-15: high bits of that offset, bits 16-31: number of slice columns in this item (<= SELL_KCH)
+//   z = partial slot, or -1 when the item is the whole slice (the warp stores y itself)
+//   w = sorted-row index of lane 0 (s * C + 32 * g)
+__global__ void sell_item_fill_kernel(const int32_t * __restrict__ slice_width, const int64_t * __restrict__ slice_ptr, int C,
+                                      int64_t nslices, int G, const int64_t * __restrict__ item_off,
                                       const int64_t * __restrict__ slot_off, const int64_t * __restrict__ cut_off,
                                       int4 * __restrict__ items, int4 * __restrict__ cuts)
 {
@@ -351,8 +357,13 @@ __global__ void sell_item_fill_kernel(const int32_t * __restrict__ slice_width, 
 	int64_t io = item_off[s];
 	const int64_t so = slot_off[s], co = cut_off[s];
 	for (int g = 0; g < G; g++) {
-		for (int j = 0; j < n; j++)
-			items[io++] = make_int4((int) s, j * SELL_KCH, (n > 1) ? (int) (so + (int64_t) g * n + j) : -1, g);
+		for (int j = 0; j < n; j++) {
+			const int64_t off = slice_ptr[s] + (int64_t) j * SELL_KCH * C + 32 * g;
+			int kc = slice_width[s] - j * SELL_KCH;
+			kc = kc < 0 ? 0 : (kc > SELL_KCH ? SELL_KCH : kc);
+			items[io++] = make_int4((int) (uint32_t) (off & 0xffffffffLL), (int) ((off >> 32) & 0xffff) | (kc << 16),
+			                        (n > 1) ? (int) (so + (int64_t) g * n + j) : -1, (int) (s * C + 32 * g));
+		}
 		if (n > 1)
 			cuts[co + g] = make_int4((int) s, (int) (so + (int64_t) g * n), n, g);
 	}
@@ -390,7 +401,11 @@ static int sell_plan_items(b200spmv * h)
 	CU(cudaMalloc(&h->d_sell_items, (size_t) tot[0] * sizeof(int4)));
 	CU(cudaMalloc(&h->d_sell_cuts, (size_t) (tot[2] > 0 ? tot[2] : 1) * sizeof(int4)));
 	CU(cudaMalloc(&h->d_sell_partial, (size_t) (tot[1] > 0 ? tot[1] : 1) * 32 * sizeof(double)));
-	sell_item_fill_kernel<<<(unsigned) ((ns + 255) / 256), 256, 0, st>>>(h->d_slice_width, ns, G, d_item, d_slot, d_cut,
+	if (h->padded >= (1LL << 47)) {
+		cudaFree(d_off);
+		B200_FAIL("SELL-C-sigma padded size does not fit the item record");
+	}
+	sell_item_fill_kernel<<<(unsigned) ((ns + 255) / 256), 256, 0, st>>>(h->d_slice_width, h->d_slice_ptr, h->C, ns, G, d_item, d_slot, d_cut,
 	                                                                    reinterpret_cast<int4 *>(h->d_sell_items), reinterpret_cast<int4 *>(h->d_sell_cuts));
 	CU_LAUNCH();
 	CU(cudaStreamSynchronize(st));
@@ -447,6 +462,8 @@ int sell_convert(b200spmv * h)
 	}
 	CU(cudaMemcpyAsync(&h->padded, h->d_slice_ptr + h->nslices, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
 	CU(cudaStreamSynchronize(st));
+	if (h->sell_pad_limit > 0 && h->padded > h->sell_pad_limit)
+		return 2;                                   // AUTO trial: too much padding, candidate skipped (not an error)
 	const int64_t alloc = h->padded + 8;
 	CU(cudaMalloc(&h->d_scol, alloc * sizeof(int32_t)));
 	CU(cudaMalloc(&h->d_sval, alloc * sizeof(double)));

@@ -15,10 +15,9 @@
 // (col 0, val 0.0) exactly as the reference writes them and are multiplied like real ones.
 #include "common.cuh"
 
-template <bool HINT>
-__global__ void __launch_bounds__(SELL_THREADS, 8)
+template <bool HINT, int U, int MINB>
+__global__ void __launch_bounds__(SELL_THREADS, MINB)
 sell_kernel(const int4 * __restrict__ items, int64_t nitems, const int32_t * __restrict__ row_order,
-            const int32_t * __restrict__ slice_width, const int64_t * __restrict__ slice_ptr,
             const int32_t * __restrict__ scol, const double * __restrict__ sval, const double * __restrict__ x,
             double * __restrict__ partial, int64_t m, int C, YOut out)
 {
@@ -29,52 +28,52 @@ sell_kernel(const int4 * __restrict__ items, int64_t nitems, const int32_t * __r
 	const int64_t it = (int64_t) blockIdx.x * (SELL_THREADS / 32) + (threadIdx.x >> 5);
 	double nrm = 0.0;
 	if (it < nitems) {
-		const int4 item = items[it];                 // x: slice, y: first column, z: partial slot or -1, w: lane group
-		const int64_t s = item.x;
-		const int w = slice_width[s];
-		int k1 = (item.y + SELL_KCH < w) ? item.y + SELL_KCH : w;
+		const int4 item = items[it];                 // packed by sell_item_fill_kernel: offset, column count, slot, first sorted row
+		int kc = (int) ((uint32_t) item.y >> 16);
 		if (lane >= C)
-			k1 = item.y;                             // C < 32: the upper lanes of the warp idle
-		int64_t p = slice_ptr[s] + (int64_t) item.y * C + item.w * 32 + lane;
+			kc = 0;                                  // C < 32: the upper lanes of the warp idle
+		int64_t p = ((int64_t) (item.y & 0xffff) << 32) + (int64_t) (uint32_t) item.x + lane;
+		const int64_t r = (int64_t) item.w + lane;
+		// the destination row travels with the first stream loads instead of after the last gather
+		int dst_row = 0;
+		if (item.z < 0 && r < m && lane < C)
+			dst_row = row_order[r];
 		double acc = 0.0;
-		int k = item.y;
-		for (; k + 8 <= k1; k += 8) {
-			double v[8];
-			int c[8];
+		int k = 0;
+		for (; k + U <= kc; k += U) {
+			double v[U];
+			int c[U];
 			#pragma unroll
-			for (int u = 0; u < 8; u++) {
+			for (int u = 0; u < U; u++) {
 				v[u] = ld_stream_f64(sval + p + (int64_t) u * C, pol_stream);
 				c[u] = ld_stream_i32(scol + p + (int64_t) u * C, pol_stream);
 			}
 			#pragma unroll
-			for (int u = 0; u < 8; u++)
+			for (int u = 0; u < U; u++)
 				acc = fma(v[u], ld_x<HINT>(x + c[u], pol), acc);
-			p += 8 * (int64_t) C;
+			p += U * (int64_t) C;
 		}
-		if (k < k1) {
-			double v[8];
-			int c[8];
+		if (k < kc) {
+			double v[U];
+			int c[U];
 			#pragma unroll
-			for (int u = 0; u < 8; u++) {
-				const bool on = (k + u < k1);
+			for (int u = 0; u < U; u++) {
+				const bool on = (k + u < kc);
 				v[u] = on ? ld_stream_f64(sval + p + (int64_t) u * C, pol_stream) : 0.0;
 				c[u] = on ? ld_stream_i32(scol + p + (int64_t) u * C, pol_stream) : 0;
 			}
 			#pragma unroll
-			for (int u = 0; u < 8; u++)
-				if (k + u < k1)
+			for (int u = 0; u < U; u++)
+				if (k + u < kc)
 					acc = fma(v[u], ld_x<HINT>(x + c[u], pol), acc);
 		}
 		if (item.z >= 0) {
 			partial[(int64_t) item.z * 32 + lane] = acc;
-		} else {
-			const int64_t r = s * C + item.w * 32 + lane;
-			if (r < m && lane < C) {
-				const double scale = out.scale ? *out.scale : 1.0;
-				acc *= scale;
-				y_store(out, row_order[r], acc);
-				nrm = acc * acc;
-			}
+		} else if (r < m && lane < C) {
+			const double scale = out.scale ? *out.scale : 1.0;
+			acc *= scale;
+			y_store(out, dst_row, acc);
+			nrm = acc * acc;
 		}
 	}
 	if (out.norm_partial) {
@@ -148,12 +147,17 @@ int launch_sell_spmv(b200spmv * h, const double * dx, double * dy, cudaStream_t 
 	const int64_t fix_ctas = (h->sell_ncuts + WPC - 1) / WPC;
 	if (ctas > 0) {
 		const int4 * items = reinterpret_cast<const int4 *>(h->d_sell_items);
-		if (h->x_hint == 0)
-			sell_kernel<true><<<(unsigned) ctas, SELL_THREADS, 0, st>>>(items, h->sell_nitems, h->d_row_order, h->d_slice_width, h->d_slice_ptr,
-			                                                           h->d_scol, h->d_sval, dx, h->d_sell_partial, h->m, h->C, out);
-		else
-			sell_kernel<false><<<(unsigned) ctas, SELL_THREADS, 0, st>>>(items, h->sell_nitems, h->d_row_order, h->d_slice_width, h->d_slice_ptr,
-			                                                            h->d_scol, h->d_sval, dx, h->d_sell_partial, h->m, h->C, out);
+		#define SELL_LAUNCH(HINT, U, MINB)                                                                                          \
+			sell_kernel<HINT, U, MINB><<<(unsigned) ctas, SELL_THREADS, 0, st>>>(items, h->sell_nitems, h->d_row_order, h->d_scol, \
+			                                                                     h->d_sval, dx, h->d_sell_partial, h->m, h->C, out)
+		const bool hint = (h->x_hint == 0);
+		switch (h->sell_variant) {
+		case 1:  if (hint) SELL_LAUNCH(true, 8, 12); else SELL_LAUNCH(false, 8, 12); break;    // 48 warps / SM, 8 steps in flight
+		case 2:  if (hint) SELL_LAUNCH(true, 4, 16); else SELL_LAUNCH(false, 4, 16); break;    // 64 warps / SM, 4 steps in flight
+		case 3:  if (hint) SELL_LAUNCH(true, 16, 4); else SELL_LAUNCH(false, 16, 4); break;    // 16 warps / SM, 16 steps in flight
+		default: if (hint) SELL_LAUNCH(true, 8, 8); else SELL_LAUNCH(false, 8, 8); break;      // 32 warps / SM, 8 steps in flight
+		}
+		#undef SELL_LAUNCH
 		CU_LAUNCH();
 	}
 	if (fix_ctas > 0) {

@@ -26,7 +26,11 @@ class MatrixFormat:
         st = handle.stats()
         self.mem_footprint = st["mem_footprint"]
         self.csr_mem_footprint = self.nnz * (8 + 4) + (self.m + 1) * 4      # spmv_kernel.h:24
-        self.format_name = FORMAT_NAMES[fmt]
+        self.requested_format = fmt
+        self.format = handle.format                     # AUTO resolves to CSR or SELL at create time
+        self.format_name = ("B200_AUTO:" if fmt == capi.AUTO else "") + FORMAT_NAMES[self.format]
+        self.sigma = int(st["ext_or_sigma"]) if self.format == capi.SELL_C_SIGMA else None
+        self.trial_ms = {k[9:]: round(st[k], 5) for k in ("trial_ms_csr", "trial_ms_sell", "trial_ms_sell_alt") if st[k] > 0}
         self.convert_ms = st["convert_ms"]
         self.cache_x = cache_x
         self._x_seen = None

@@ -13,8 +13,9 @@
  * No CUDA in this file: every device operation goes through the C-ABI of include/b200spmv.h, so the
  * harness's ordinary C++ compiler builds it (no nvcc pass, no _nv suffix needed).
  *
- * Build-time switch:  -DB200_FORMAT_SELL  selects SELL-C-sigma (format name B200_SELL_C_SIGMA), default is
- *                     the adaptive CSR kernel (B200_CSR_ADAPTIVE).
+ * Build-time switch:  -DB200_FORMAT_SELL  selects SELL-C-sigma (format name B200_SELL_C_SIGMA), -DB200_FORMAT_AUTO builds
+ *                     both at csr_to_format time, times them on the device and keeps the faster (B200_AUTO_CSR /
+ *                     B200_AUTO_SELL); default is the adaptive CSR kernel (B200_CSR_ADAPTIVE).
  * Run-time switches (environment, read once in csr_to_format):
  *     B200SPMV_TRANSFER = first | always   x upload / y download on the first spmv call only (the reference's
  *                         GPU-plugin convention, spmv_kernels/GPU_clean/cuda_csr.cu:353-430; default) or on every call
@@ -59,7 +60,10 @@ struct B200_Format : Matrix_Format
 		static_assert(sizeof(ValueType) == 8 && sizeof(ValueTypeReference) == 8, "libb200spmv is the fp64 (_d) build");
 		b200spmv_opts o;
 		b200spmv_default_opts(&o);
-		#ifdef B200_FORMAT_SELL
+		#if defined(B200_FORMAT_AUTO)
+			o.format = B200SPMV_AUTO;
+			format_name = (char *) "B200_AUTO";
+		#elif defined(B200_FORMAT_SELL)
 			o.format = B200SPMV_SELL_C_SIGMA;
 			format_name = (char *) "B200_SELL_C_SIGMA";
 		#else
@@ -83,6 +87,9 @@ struct B200_Format : Matrix_Format
 			b200_die("stats");
 		mem_footprint = stats[0];
 		convert_ms = stats[6];
+		#if defined(B200_FORMAT_AUTO)
+			format_name = (char *) (b200spmv_format(handle) == B200SPMV_SELL_C_SIGMA ? "B200_AUTO_SELL" : "B200_AUTO_CSR");
+		#endif
 	}
 
 	~B200_Format()

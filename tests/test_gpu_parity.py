@@ -182,6 +182,44 @@ def test_sell_large_sigma_global_sort(S, oracle):
         MF.close()
 
 
+# ------------------------------------------------------------------------------------------ AUTO
+def test_auto_format_resolves_and_matches(S, oracle, golden_matrices):
+    """B200SPMV_AUTO builds both formats, times them on the device and keeps one: whatever it keeps must pass the
+    same per-row bound, export the layout of the kept format bit-exactly, and report its trial times."""
+    for (p, rp, col, val) in golden_matrices:
+        x = M.rand_x(p.cols)
+        MF, y = _spmv(S, dict(format=S.AUTO), rp, col, val, p.cols, x)
+        assert MF.format in (S.CSR_ADAPTIVE, S.SELL_C_SIGMA) and MF.format_name.startswith("B200_AUTO:")
+        assert "csr" in MF.trial_ms and MF.trial_ms["csr"] > 0
+        _check(oracle, rp, col, val, x, y, "auto -> %s" % MF.format_name)
+        if MF.format == S.SELL_C_SIGMA:
+            O = oracle.sellcs_convert(rp, col, val, 32, MF.sigma)
+            assert np.array_equal(MF.handle.export(S.capi.X_ROW_ORDER), O["row_order"])
+            assert np.array_equal(MF.handle.export(S.capi.X_SLICE_PTR), O["slice_ptr"])
+        # the reference GPU-plugin convention on an AUTO handle: the first call must upload x even when asked to skip
+        y2 = np.full(p.rows, 7.0)
+        MF.handle.spmv_host(x, y2, 0)
+        assert np.array_equal(y2, y)
+        MF.close()
+    # empty matrix and a matrix of empty rows resolve without timing anything
+    rp = np.zeros(6, np.int32)
+    MF = S.csr_to_format(rp, np.zeros(0, np.int32), np.zeros(0), 5, 5, 0, format=S.AUTO)
+    y = np.full(5, 3.0)
+    MF.spmv(np.ones(5), y)
+    assert np.all(y == 0.0)
+    MF.close()
+
+
+def test_auto_skip_flag_on_first_call(S, oracle, golden_matrices):
+    p, rp, col, val = golden_matrices[0]
+    x = M.rand_x(p.cols)
+    MF = S.csr_to_format(rp, col, val, p.rows, p.cols, int(rp[-1]), format=S.AUTO)
+    y = np.full(p.rows, 1.0)
+    MF.handle.spmv_host(x, y, S.capi.SKIP_X_UPLOAD)          # nothing staged yet: must upload anyway
+    _check(oracle, rp, col, val, x, y, "auto first call with SKIP_X_UPLOAD")
+    MF.close()
+
+
 # ------------------------------------------------------------------------------------------ partitioners
 def test_partition_bit_exact(S, oracle, golden, golden_matrices):
     for li, (p, rp, col, val) in enumerate(golden_matrices):
@@ -323,10 +361,11 @@ def test_reference_harness_drives_the_plugin(S, oracle, tmp_path):
     rp, col, val = amg.generate(p)
     path = str(tmp_path / "amg_30000.mtx")
     RH.write_matrix_market(path, rp, col, val, p.cols)
-    for exe, name in (("spmv_b200_csr_d.exe", "B200_CSR_ADAPTIVE"), ("spmv_b200_sell_d.exe", "B200_SELL_C_SIGMA")):
+    for exe, name in (("spmv_b200_csr_d.exe", "B200_CSR_ADAPTIVE"), ("spmv_b200_sell_d.exe", "B200_SELL_C_SIGMA"),
+                      ("spmv_b200_auto_d.exe", "B200_AUTO_")):
         r = RH.run(exe, [path], gpu_kernel=True, threads=4)
         assert r["returncode"] == 0, r["stderr"][-2000:]
         assert not r["test_failed"], r["stdout"][-2000:]
-        assert name in r["csv"], r["csv"]
+        assert any(name in f for f in r["csv"]), r["csv"]
         assert r["errors"]["max_ae"] < 1e-11 and r["errors"]["mae"] < 1e-12, r["errors"]
         assert r["loops"] >= 64                       # the reference's >= 64 iterations / >= 2 s rule (bench_spmv.cpp:335-382)

@@ -19,16 +19,19 @@ lines = [H.CONFIG1.line()] + [p.line() for p in H.medium_sample()]
 if mode == "full":
     lines += ["8388607 8388607 50 16.6667 gamma random 0.6 10000 0.05 0.05 14", "8388607 8388607 50 150 gamma random 0.6 0 0.05 0.05 14",
               "4194304 4194304 60 20 normal random 0.3 0 0.5 0.5 14"]
-variants = [("csr npt4", dict(format=S.CSR_ADAPTIVE, csr_nnz_per_thread=4)),
-            ("csr npt8", dict(format=S.CSR_ADAPTIVE, csr_nnz_per_thread=8)),
-            ("csr npt16", dict(format=S.CSR_ADAPTIVE, csr_nnz_per_thread=16)),
-            ("csr npt32", dict(format=S.CSR_ADAPTIVE, csr_nnz_per_thread=32)),
-            ("csr npt8 nohint", dict(format=S.CSR_ADAPTIVE, csr_nnz_per_thread=8, x_hint=1)),
-            ("sell C32 s16384", dict(format=S.SELL_C_SIGMA, sell_C=32, sell_sigma=16384)),
-            ("sell C32 s256", dict(format=S.SELL_C_SIGMA, sell_C=32, sell_sigma=256)),
-            ("sell C64 s16384", dict(format=S.SELL_C_SIGMA, sell_C=64, sell_sigma=16384)),
-            ("sell C128 s16384", dict(format=S.SELL_C_SIGMA, sell_C=128, sell_sigma=16384)),
-            ("sell C32 nohint", dict(format=S.SELL_C_SIGMA, sell_C=32, sell_sigma=16384, x_hint=1))]
+variants = [("csr npt8", dict(format=S.CSR_ADAPTIVE, csr_nnz_per_thread=8)),
+            ("sell s16384 v0", dict(format=S.SELL_C_SIGMA, sell_sigma=16384)),
+            ("sell s16384 v1", dict(format=S.SELL_C_SIGMA, sell_sigma=16384, sell_variant=1)),
+            ("sell s16384 v2", dict(format=S.SELL_C_SIGMA, sell_sigma=16384, sell_variant=2)),
+            ("sell s16384 v3", dict(format=S.SELL_C_SIGMA, sell_sigma=16384, sell_variant=3)),
+            ("sell s256 v0", dict(format=S.SELL_C_SIGMA, sell_sigma=256)),
+            ("sell s256 v1", dict(format=S.SELL_C_SIGMA, sell_sigma=256, sell_variant=1)),
+            ("sell s1024 v1", dict(format=S.SELL_C_SIGMA, sell_sigma=1024, sell_variant=1)),
+            ("sell s64 v1", dict(format=S.SELL_C_SIGMA, sell_sigma=64, sell_variant=1)),
+            ("auto", dict(format=S.AUTO))]
+if os.environ.get("SWEEP_CSR"):
+    variants = [("csr npt4", dict(format=S.CSR_ADAPTIVE, csr_nnz_per_thread=4)), ("csr npt8", dict(format=S.CSR_ADAPTIVE, csr_nnz_per_thread=8)),
+                ("csr npt16", dict(format=S.CSR_ADAPTIVE, csr_nnz_per_thread=16)), ("csr npt8 nohint", dict(format=S.CSR_ADAPTIVE, csr_nnz_per_thread=8, x_hint=1))]
 dev = torch.device("cuda:0")
 print("%-72s %-18s %9s %9s %8s %8s %9s" % ("matrix", "variant", "ms(med)", "ms(min)", "GB/s", "GFLOP/s", "conv ms"))
 for ln in lines:
@@ -44,7 +47,8 @@ for ln in lines:
         MF.handle.time_device(dx, dy, 3, flush)
         ms = MF.handle.time_device(dx, dy, 15, flush)
         med, mn = float(np.median(ms)), float(ms.min())
-        print("%-72s %-18s %9.4f %9.4f %8.0f %8.0f %9.2f" % (ln, name, med, mn, bc / med * 1e-6, 2.0 * nnz / med * 1e-6, MF.convert_ms), flush=True)
+        print("%-72s %-18s %9.4f %9.4f %8.0f %8.0f %9.2f %s" % (ln, name, med, mn, bc / med * 1e-6, 2.0 * nnz / med * 1e-6, MF.convert_ms,
+                                                              (MF.format_name + " " + str(MF.trial_ms)) if name == "auto" else ""), flush=True)
         MF.close()
     del dx, dy
     torch.cuda.empty_cache()
