@@ -146,6 +146,7 @@ def parse_args():
                     help="N>1: mc = fused stores to an NVSwitch multicast address (falls back to p2p), p2p = fused unicast peer stores, nccl = all-gather")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-sell", action="store_true")
+    ap.add_argument("--full-exchange", action="store_true", help="N>1: send every y row to the peers, not only the referenced column band")
     ap.add_argument("--no-nccl-leg", action="store_true", help="N>1: skip the plain-NCCL comparison leg")
     ap.add_argument("--no-graph", action="store_true", help="N>1: time an eager step loop instead of CUDA-graph replays")
     ap.add_argument("--x", default="ones", choices=["ones", "random"])
@@ -298,7 +299,8 @@ def run_single(args):
         for r, x, y in zip(mats, hx, hy):
             r["MF"].spmv(x, y)
     te = (time.perf_counter() - t0) / Ke
-    e2e = {"value": round(2.0 * tot_nnz / te * 1e-9, 2), "unit": "GFLOP/s", "h2d_bytes_per_step": int(sum(8 * r["n"] for r in mats)),
+    e2e = {"value": round(2.0 * tot_nnz / te * 1e-9, 2), "unit": "GFLOP/s", "h2d_bytes_per_step": int(sum(8 * (r["MF"].handle.col_range()[1] - r["MF"].handle.col_range()[0]) for r in mats)),
+           "h2d_note": "x is uploaded for the referenced column band [col_lo, col_hi) only (8 n = %d bytes would be the full vectors)" % int(sum(8 * r["n"] for r in mats)),
            "d2h_bytes_per_step": int(sum(8 * r["m"] for r in mats)), "ms_per_step": round(te * 1e3, 4),
            "call": "Matrix_Format::spmv(x, y) via b200spmv_spmv_host, pinned host x / y"}
 
@@ -390,6 +392,16 @@ def run_power(args):
         # fused exchange: the SpMV epilogue stores every finished row into all peers' next-x buffers over NVLink
         pv = power.PeerVectors(n, rank, world, dev)
 
+    # rows of the next x that ANY rank reads: the union of the shards' referenced column bands.  Only those rows are sent.
+    peer_rows = None
+    band = (0, n)
+    if world > 1 and not args.full_exchange:
+        lo, hi = MF.handle.col_range()
+        t = torch.tensor([-lo, hi], dtype=torch.int64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        band = (int(-t[0].item()), int(t[1].item()))
+        peer_rows = (min(max(band[0] - i_s, 0), i_e - i_s), min(max(band[1] - i_s, 0), i_e - i_s))
+
     def local_spmv(cur, slot, scale, norm2, parity):
         peers = ()
         if exchange == "mc":
@@ -397,7 +409,8 @@ def run_power(args):
         elif pv is not None:
             b = 1 - parity
             peers = [pv.peer[b][q] + 8 * i_s for q in range(world) if q != rank]
-        MF.spmv_device(cur, slot, torch.cuda.current_stream().cuda_stream, scale=scale, norm2=norm2, peers=peers)
+        MF.spmv_device(cur, slot, torch.cuda.current_stream().cuda_stream, scale=scale, norm2=norm2, peers=peers,
+                       peer_rows=(peer_rows if peers else None))
 
     it = power.ShardedPowerIteration(n, bounds, rank, world, local_spmv, dev, exchange=exchange,
                                      buffers=(pv.tensors if pv is not None else None))
@@ -488,6 +501,12 @@ def run_power(args):
         nccl_cmp = {"ms_per_step": round(float(ms2.item()) / K, 5), "gflops": round(2.0 * nnz / (float(ms2.item()) / K * 1e-3) * 1e-9, 2),
                     "eigenvalue_estimate": it2.eigenvalue(),
                     "exchange": "NCCL in-place all-gather of y slots (one broadcast per owner) + scalar all-reduce"}
+        # both legs ran W + K (+ graph warm-up) iterations from the same start on different exchange paths: the eigenvalue
+        # estimates converge to the same value; a fused exchange that dropped or misplaced rows would not
+        rel = abs(nccl_cmp["eigenvalue_estimate"] - eig) / abs(nccl_cmp["eigenvalue_estimate"])
+        nccl_cmp["fused_vs_nccl_eigenvalue_rel_diff"] = rel
+        if rank == 0 and not rel < 1e-6:
+            raise SystemExit("bench.py: fused exchange disagrees with the NCCL all-gather (rel diff %.3g)" % rel)
         del it2
 
     # the N = 1 member of the same weak-scaling series (rows_per_gpu rows), timed on rank 0 alone while the others wait:
@@ -543,6 +562,7 @@ def run_power(args):
                                     "p2p": "fused: SpMV epilogue stores y rows into every peer's next-x buffer over NVLink (CUDA IPC) + NCCL scalar all-reduce",
                                     "nccl": "NCCL in-place all-gather of y slots (one broadcast per owner) + scalar all-reduce"}[exchange],
                        "exchange_note": mc_note,
+                       "exchange_rows": "rows [%d, %d) of %d (the union of the shards' referenced column bands)" % (band[0], band[1], n),
                        "l2_note": "each shard is %.1f GB (> 126 MB L2); no explicit flush" % (bc_loc * 1e-9), "generate_s": round(t_gen, 1)},
             "effective_GBs": round(bc / (ms_step * 1e-3) * 1e-9, 1),
             "roofline_frac_nominal_8TBs": round(bc / (ms_step * 1e-3) * 1e-9 / (NOMINAL_HBM_GBS * world), 4),
@@ -550,7 +570,7 @@ def run_power(args):
                          "achieved": round(bc_loc / float(kms.item()) * 1e-6, 1), "peak": peak, "unit": "GB/s",
                          "frac": round(bc_loc / float(kms.item()) * 1e-6 / peak, 4), "traffic": None, "peak_source": peak_src,
                          "achieved_def": "rank-0 shard compulsory bytes / slowest rank's kernel-only SpMV time (CUDA events, 5 launches)"},
-            "e2e": {"value": round(2.0 * nnz / te * 1e-9, 2), "unit": "GFLOP/s", "h2d_bytes_per_step": int(8 * n * world),
+            "e2e": {"value": round(2.0 * nnz / te * 1e-9, 2), "unit": "GFLOP/s", "h2d_bytes_per_step": int(8 * (MF.handle.col_range()[1] - MF.handle.col_range()[0]) * world),
                     "d2h_bytes_per_step": int(8 * m), "ms_per_step": round(te * 1e3, 4),
                     "call": "per rank Matrix_Format::spmv(x, y) on its row shard, pinned host x / y, max over ranks"},
             "gpu_launches": int(K * (MF.gpu_launches_per_spmv + 1)), "clocks": clk.summary(), "eigenvalue_estimate": eig, "launch": launch_mode, "nccl_exchange": nccl_cmp, "n1_same_series": n1_same,

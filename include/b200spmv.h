@@ -69,8 +69,9 @@ typedef struct b200spmv_opts {
 	int32_t csr_ext;          /* tail-extension capacity in nnz (multiple of 8); 0 = auto               */
 	int32_t x_hint;           /* 0: L2 evict_last hint on x gathers (default), 1: plain loads           */
 	int32_t sell_sigma_alt;   /* AUTO only: second sort window tried (0 = default 256, -1 = none)       */
-	int32_t sell_variant;     /* SELL kernel shape (k steps in flight x resident warps per SM): 0 = 8 x 32
-	                             (default), 1 = 8 x 48, 2 = 4 x 64, 3 = 16 x 16                          */
+	int32_t sell_variant;     /* SELL kernel shape (k steps in flight x resident warps per SM): 0 = chosen from
+	                             the average slice width (AUTO: timed), 1 = 8 x 32, 2 = 8 x 48, 3 = 4 x 64,
+	                             4 = 16 x 16                                                             */
 	int32_t reserved[7];
 } b200spmv_opts;
 
@@ -78,9 +79,12 @@ typedef struct b200spmv_opts {
 typedef struct b200spmv_launch {
 	const double * scale;     /* optional scalar s: y = s * (A x)        (power iteration, A(s x) = s A x) */
 	double * norm2;           /* optional: receives sum_i y_i^2 of this handle's rows                    */
-	double * y_peer[8];       /* optional extra destinations written like y (peer GPUs' next-x buffers)  */
+	double * y_peer[8];       /* optional extra destinations written like y (peer GPUs' next-x buffers,
+	                             or one NVSwitch multicast address covering all of them)                 */
 	int32_t n_peer;
 	int32_t pad_;
+	int64_t peer_row_lo;      /* only rows [peer_row_lo, peer_row_hi) of this handle are stored to y_peer  */
+	int64_t peer_row_hi;      /* (the rows some rank's columns reference); both 0 = every row             */
 } b200spmv_launch;
 
 void b200spmv_default_opts(b200spmv_opts * opts);
@@ -96,7 +100,8 @@ int b200spmv_create_device(b200spmv_t ** out, const int32_t * d_row_ptr, const i
 
 void b200spmv_destroy(b200spmv_t * h);
 
-/* y = A x with HOST vectors: H2D of x, kernel(s), D2H of y, stream synchronised on return. */
+/* y = A x with HOST vectors: H2D of x (the referenced column band, see b200spmv_col_range), kernel(s), D2H of y,
+ * stream synchronised on return. */
 int b200spmv_spmv_host(b200spmv_t * h, const double * x, double * y);
 int b200spmv_spmv_host_ex(b200spmv_t * h, const double * x, double * y, int32_t flags);
 
@@ -106,6 +111,10 @@ int b200spmv_spmv_device_ex(b200spmv_t * h, const double * dx, double * dy, void
 
 /* The format that runs: B200SPMV_CSR_ADAPTIVE or B200SPMV_SELL_C_SIGMA (what AUTO resolved to). */
 int32_t b200spmv_format(const b200spmv_t * h);
+
+/* Columns referenced by the matrix lie in [*lo, *hi) (found on the GPU at create time).  The products never read x
+ * outside that range, so b200spmv_spmv_host uploads only x[lo..hi) and a multi-GPU exchange only needs those rows. */
+int b200spmv_col_range(const b200spmv_t * h, int64_t * lo, int64_t * hi);
 
 /* Number of kernel launches one b200spmv_spmv_device call issues for this handle (1 or 2). */
 int32_t b200spmv_launches_per_spmv(const b200spmv_t * h);

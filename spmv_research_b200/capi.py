@@ -31,7 +31,8 @@ class Opts(C.Structure):
 
 
 class Launch(C.Structure):
-    _fields_ = [("scale", C.c_void_p), ("norm2", C.c_void_p), ("y_peer", C.c_void_p * 8), ("n_peer", C.c_int32), ("pad_", C.c_int32)]
+    _fields_ = [("scale", C.c_void_p), ("norm2", C.c_void_p), ("y_peer", C.c_void_p * 8), ("n_peer", C.c_int32), ("pad_", C.c_int32),
+                ("peer_row_lo", C.c_int64), ("peer_row_hi", C.c_int64)]
 
 
 _lib = None
@@ -58,6 +59,7 @@ def lib():
         "b200spmv_spmv_device_ex": (C.c_int, [vp, vp, vp, vp, C.POINTER(Launch)]),
         "b200spmv_launches_per_spmv": (i32, [vp]),
         "b200spmv_format": (i32, [vp]),
+        "b200spmv_col_range": (C.c_int, [vp, C.POINTER(i64), C.POINTER(i64)]),
         "b200spmv_stats": (C.c_int, [vp, C.POINTER(C.c_double), i32]),
         "b200spmv_export": (C.c_int, [vp, i32, vp, i64, C.POINTER(i64)]),
         "b200spmv_partition_device": (C.c_int, [vp, i64, i64, i32, vp]),
@@ -136,7 +138,7 @@ class Handle:
         assert x.dtype == np.float64 and y.dtype == np.float64 and x.size >= self.n and y.size >= self.m
         check(lib().b200spmv_spmv_host_ex(self._h, _ptr(x), _ptr(y), flags))
 
-    def spmv_device(self, dx, dy, stream=None, scale=None, norm2=None, peers=()):
+    def spmv_device(self, dx, dy, stream=None, scale=None, norm2=None, peers=(), peer_rows=None):
         if scale is None and norm2 is None and not peers:
             check(lib().b200spmv_spmv_device(self._h, _ptr(dx), _ptr(dy), stream))
             return
@@ -144,6 +146,10 @@ class Handle:
         l.scale = _ptr(scale)
         l.norm2 = _ptr(norm2)
         l.n_peer = len(peers)
+        if peer_rows is not None:
+            l.peer_row_lo, l.peer_row_hi = int(peer_rows[0]), int(peer_rows[1])
+            if l.peer_row_hi <= l.peer_row_lo:
+                l.n_peer = 0                      # nothing of this shard is referenced by anybody
         for i, p in enumerate(peers):
             l.y_peer[i] = _ptr(p)
         check(lib().b200spmv_spmv_device_ex(self._h, _ptr(dx), _ptr(dy), stream, C.byref(l)))
@@ -156,6 +162,12 @@ class Handle:
     def format(self):
         """The format that runs (AUTO handles report what they resolved to)."""
         return int(lib().b200spmv_format(self._h))
+
+    def col_range(self):
+        """[lo, hi) of the column indices the matrix references."""
+        lo, hi = C.c_int64(), C.c_int64()
+        check(lib().b200spmv_col_range(self._h, C.byref(lo), C.byref(hi)))
+        return lo.value, hi.value
 
     def stats(self):
         out = (C.c_double * 10)()

@@ -49,8 +49,8 @@ static int validate_opts(const b200spmv_opts * in, b200spmv_opts * o, int64_t m,
 		B200_FAIL("unknown format %d", o->format);
 	if (o->sell_sigma_alt == 0)
 		o->sell_sigma_alt = 256;
-	if (o->sell_variant < 0 || o->sell_variant > 3)
-		B200_FAIL("sell_variant must be in [0, 3]");
+	if (o->sell_variant < 0 || o->sell_variant > 4)
+		B200_FAIL("sell_variant must be in [0, 4]");
 	if (o->sell_C == 0)
 		o->sell_C = 32;
 	if (o->sell_sigma == 0)
@@ -70,6 +70,48 @@ static int validate_opts(const b200spmv_opts * in, b200spmv_opts * o, int64_t m,
 		o->csr_ext = (o->csr_nnz_per_thread <= 8) ? 256 : 2048;     // shared memory comes out of the L1 the x gathers live in
 	if (o->csr_ext < 64 || o->csr_ext % 64 || o->csr_ext > 8192)
 		B200_FAIL("csr_ext must be a multiple of 64 in [64, 8192]");
+	return 0;
+}
+
+// Smallest / largest column index present: x entries outside [lo, hi] are never read by any product of this matrix.
+__global__ void col_range_kernel(const int32_t * __restrict__ col, int64_t nnz, int * __restrict__ lo_hi)
+{
+	int lo = 0x7fffffff, hi = -1;
+	for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < nnz; i += (int64_t) gridDim.x * blockDim.x) {
+		const int c = col[i];
+		lo = c < lo ? c : lo;
+		hi = c > hi ? c : hi;
+	}
+	for (int o = 16; o > 0; o >>= 1) {
+		const int l2 = __shfl_xor_sync(0xffffffffu, lo, o), h2 = __shfl_xor_sync(0xffffffffu, hi, o);
+		lo = l2 < lo ? l2 : lo;
+		hi = h2 > hi ? h2 : hi;
+	}
+	if ((threadIdx.x & 31) == 0) {
+		atomicMin(&lo_hi[0], lo);
+		atomicMax(&lo_hi[1], hi);
+	}
+}
+
+static int compute_col_range(b200spmv * h)
+{
+	h->col_lo = 0;
+	h->col_hi = 0;
+	if (h->nnz == 0)
+		return 0;
+	int * d = nullptr;
+	int init[2] = { 0x7fffffff, -1 }, got[2];
+	CU(cudaMalloc(&d, 2 * sizeof(int)));
+	CU(cudaMemcpyAsync(d, init, sizeof(init), cudaMemcpyHostToDevice, h->stream));
+	col_range_kernel<<<148 * 8, 256, 0, h->stream>>>(h->d_col, h->nnz, d);
+	CU_LAUNCH();
+	CU(cudaMemcpyAsync(got, d, sizeof(got), cudaMemcpyDeviceToHost, h->stream));
+	CU(cudaStreamSynchronize(h->stream));
+	CU(cudaFree(d));
+	if (got[0] < 0 || got[1] >= h->n)
+		B200_FAIL("col_ind out of range: found [%d, %d], n = %lld", got[0], got[1], (long long) h->n);
+	h->col_lo = got[0];
+	h->col_hi = (int64_t) got[1] + 1;
 	return 0;
 }
 
@@ -110,11 +152,17 @@ static void free_csr_plan(b200spmv * h, bool arrays)
 	}
 }
 
+constexpr size_t TRIAL_FLUSH_BYTES = 192u << 20;
+
 // AUTO trial: median of 5 device-timed products (after 2 untimed) of the format h->format currently names.
 static int trial_ms(b200spmv * h, cudaEvent_t e0, cudaEvent_t e1, float * out)
 {
 	float t[5];
 	for (int i = 0; i < 7; i++) {
+		// a matrix larger than L2 is timed cold (what a sweep over many matrices / a long vector pipeline sees): rewrite a
+		// scratch buffer larger than the 126 MB L2 before every product, outside the event pair
+		if (h->d_trial_flush)
+			CU(cudaMemsetAsync(h->d_trial_flush, i, TRIAL_FLUSH_BYTES, h->stream));
 		if (i >= 2)
 			CU(cudaEventRecord(e0, h->stream));
 		const int rc = (h->format == B200SPMV_CSR_ADAPTIVE) ? launch_csr_spmv(h, h->d_x, h->d_y, h->stream, nullptr)
@@ -145,6 +193,9 @@ static int auto_select(b200spmv * h, const b200spmv_opts & o)
 	CU(cudaEventCreate(&e0));
 	CU(cudaEventCreate(&e1));
 	const int rc = auto_select_impl(h, o, e0, e1);
+	if (h->d_trial_flush)
+		cudaFree(h->d_trial_flush);
+	h->d_trial_flush = nullptr;
 	cudaEventDestroy(e0);
 	cudaEventDestroy(e1);
 	return rc;
@@ -155,6 +206,8 @@ static int auto_select_impl(b200spmv * h, const b200spmv_opts & o, cudaEvent_t e
 	CU(cudaMalloc(&h->d_x, (h->n > 0 ? h->n : 1) * sizeof(double)));
 	CU(cudaMalloc(&h->d_y, (h->m > 0 ? h->m : 1) * sizeof(double)));
 	CU(cudaMemsetAsync(h->d_x, 0, (h->n > 0 ? h->n : 1) * sizeof(double), h->stream));
+	if (12 * h->nnz > (64LL << 20))
+		CU(cudaMalloc(&h->d_trial_flush, TRIAL_FLUSH_BYTES));
 	h->format = B200SPMV_CSR_ADAPTIVE;
 	if (csr_plan_tiles(h))
 		return 1;
@@ -164,6 +217,7 @@ static int auto_select_impl(b200spmv * h, const b200spmv_opts & o, cudaEvent_t e
 		return 1;
 	float best = h->trial_ms[0];
 	int64_t best_sigma = 0;                         // 0 = CSR
+	int best_variant = o.sell_variant;
 	int64_t cand[2] = { o.sell_sigma, o.sell_sigma_alt > 0 ? (int64_t) o.sell_sigma_alt : 0 };
 	if (cand[1] == cand[0] || (cand[1] > 0 && (cand[1] < h->C || cand[1] % h->C)))
 		cand[1] = 0;
@@ -177,11 +231,22 @@ static int auto_select_impl(b200spmv * h, const b200spmv_opts & o, cudaEvent_t e
 		if (rc == 1)
 			return 1;
 		if (rc == 0) {
-			if (trial_ms(h, e0, e1, &h->trial_ms[1 + c]))
-				return 1;
-			if (h->trial_ms[1 + c] < best) {
-				best = h->trial_ms[1 + c];
+			// both kernel shapes that win somewhere (8 k-steps in flight x 32 or 48 resident warps per SM) unless one is forced
+			float tv[2] = { 0.f, 0.f };
+			const int forced = o.sell_variant;
+			for (int v = 0; v < 2; v++) {
+				if (forced != 0 && v > 0)
+					break;
+				h->sell_variant = forced != 0 ? forced : 1 + v;
+				if (trial_ms(h, e0, e1, &tv[v]))
+					return 1;
+			}
+			const int bv = (forced == 0 && tv[1] < tv[0]) ? 1 : 0;
+			h->trial_ms[1 + c] = tv[bv];
+			if (tv[bv] < best) {
+				best = tv[bv];
 				best_sigma = cand[c];
+				best_variant = forced != 0 ? forced : 1 + bv;
 			}
 		}
 		// keep the arrays only when this is the last candidate and it is the winner; otherwise rebuild the winner below
@@ -196,6 +261,7 @@ static int auto_select_impl(b200spmv * h, const b200spmv_opts & o, cudaEvent_t e
 		return 0;
 	}
 	h->sigma = best_sigma;
+	h->sell_variant = best_variant;
 	if (!h->d_scol && sell_convert(h))
 		return 1;
 	free_csr_plan(h, true);
@@ -278,6 +344,7 @@ static int create_common(b200spmv ** out, const int32_t * row_ptr, const int32_t
 			if (cudaMemcpyAsync(h->d_val, values, nnz * sizeof(double), kind, h->stream) != cudaSuccess) break;
 		}
 		if (cudaStreamSynchronize(h->stream) != cudaSuccess) break;
+		if (compute_col_range(h)) goto fail;
 		int64_t norm_slots;
 		if (h->format == B200SPMV_AUTO) {
 			if (auto_select(h, o)) goto fail;           // convert_ms of an AUTO handle includes the trials
@@ -338,6 +405,15 @@ extern "C" void b200spmv_destroy(b200spmv_t * h)
 
 extern "C" int32_t b200spmv_format(const b200spmv_t * h) { return h ? h->format : -1; }
 
+extern "C" int b200spmv_col_range(const b200spmv_t * h, int64_t * lo, int64_t * hi)
+{
+	if (!h || !lo || !hi)
+		B200_FAIL("NULL argument");
+	*lo = h->col_lo;
+	*hi = h->col_hi;
+	return 0;
+}
+
 extern "C" int32_t b200spmv_launches_per_spmv(const b200spmv_t * h)
 {
 	if (!h)
@@ -374,8 +450,9 @@ extern "C" int b200spmv_spmv_host_ex(b200spmv_t * h, const double * x, double * 
 	if (!h->x_uploaded)
 		flags &= ~B200SPMV_SKIP_X_UPLOAD;           // nothing to reuse yet
 	h->x_uploaded = 1;
-	if (!(flags & B200SPMV_SKIP_X_UPLOAD) && h->n > 0)
-		CU(cudaMemcpyAsync(h->d_x, x, h->n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+	// only the columns the matrix references are read by the kernels: upload that band of x, not all n entries
+	if (!(flags & B200SPMV_SKIP_X_UPLOAD) && h->col_hi > h->col_lo)
+		CU(cudaMemcpyAsync(h->d_x + h->col_lo, x + h->col_lo, (h->col_hi - h->col_lo) * sizeof(double), cudaMemcpyHostToDevice, h->stream));
 	if (b200spmv_spmv_device_ex(h, h->d_x, h->d_y, h->stream, nullptr))
 		return 1;
 	if (!(flags & B200SPMV_SKIP_Y_DOWNLOAD) && h->m > 0)

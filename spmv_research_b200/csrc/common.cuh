@@ -121,6 +121,7 @@ struct YOut {
 	double * y;
 	double * peer[8];
 	int n_peer;
+	int64_t peer_lo, peer_hi; // rows stored to the peers: [peer_lo, peer_hi)
 	const double * scale;     // device scalar or nullptr
 	double * norm_partial;    // one slot per CTA or nullptr
 };
@@ -128,9 +129,10 @@ struct YOut {
 __device__ __forceinline__ void y_store(const YOut & o, int64_t row, double v)
 {
 	o.y[row] = v;
+	const bool send = (row >= o.peer_lo) && (row < o.peer_hi);
 	#pragma unroll
 	for (int d = 0; d < 8; d++)          // unrolled + predicated: keeps the parameter struct out of local memory
-		if (d < o.n_peer)
+		if (d < o.n_peer && send)
 			o.peer[d][row] = v;
 }
 
@@ -152,6 +154,7 @@ struct b200spmv {
 	float trial_ms[4];            // AUTO: measured product time of {CSR, SELL sigma, SELL sigma_alt, -}; 0 = not tried
 	int64_t sell_pad_limit;       // AUTO: a SELL candidate padded beyond this many entries is skipped (0 = no limit)
 	int64_t m, n, nnz;
+	int64_t col_lo, col_hi;       // referenced columns lie in [col_lo, col_hi); x outside is never read
 	int x_hint;
 	cudaStream_t stream;
 	float convert_ms;
@@ -175,7 +178,9 @@ struct b200spmv {
 
 	// SELL-C-sigma (device)
 	int C;
-	int sell_variant;         // kernel shape: 0 = 8 steps x 32 warps/SM, 1 = 8 x 48, 2 = 4 x 64, 3 = 16 x 16
+	int sell_variant;         // kernel shape (k steps in flight x resident warps / SM): 0 = by average slice width,
+	                          // 1 = 8 x 32, 2 = 8 x 48, 3 = 4 x 64, 4 = 16 x 16
+	void * d_trial_flush;     // AUTO trial scratch (freed before create returns)
 	int64_t sigma, nslices, padded;
 	int32_t * d_row_order;
 	int32_t * d_slice_width;

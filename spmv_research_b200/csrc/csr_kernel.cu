@@ -286,6 +286,12 @@ int launch_csr_spmv(b200spmv * h, const double * dx, double * dy, cudaStream_t s
 		out.n_peer = l->n_peer;
 		for (int d = 0; d < l->n_peer; d++)
 			out.peer[d] = l->y_peer[d];
+		out.peer_lo = 0;
+		out.peer_hi = h->m;
+		if (l->peer_row_lo != 0 || l->peer_row_hi != 0) {
+			out.peer_lo = l->peer_row_lo;
+			out.peer_hi = l->peer_row_hi;
+		}
 		out.scale = l->scale;
 		out.norm_partial = l->norm2 ? h->d_norm_partial : nullptr;
 	}

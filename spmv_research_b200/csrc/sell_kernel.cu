@@ -139,6 +139,12 @@ int launch_sell_spmv(b200spmv * h, const double * dx, double * dy, cudaStream_t 
 		out.n_peer = l->n_peer;
 		for (int d = 0; d < l->n_peer; d++)
 			out.peer[d] = l->y_peer[d];
+		out.peer_lo = 0;
+		out.peer_hi = h->m;
+		if (l->peer_row_lo != 0 || l->peer_row_hi != 0) {
+			out.peer_lo = l->peer_row_lo;
+			out.peer_hi = l->peer_row_hi;
+		}
 		out.scale = l->scale;
 		out.norm_partial = l->norm2 ? h->d_norm_partial : nullptr;
 	}
@@ -151,10 +157,15 @@ int launch_sell_spmv(b200spmv * h, const double * dx, double * dy, cudaStream_t 
 			sell_kernel<HINT, U, MINB><<<(unsigned) ctas, SELL_THREADS, 0, st>>>(items, h->sell_nitems, h->d_row_order, h->d_scol, \
 			                                                                     h->d_sval, dx, h->d_sell_partial, h->m, h->C, out)
 		const bool hint = (h->x_hint == 0);
-		switch (h->sell_variant) {
-		case 1:  if (hint) SELL_LAUNCH(true, 8, 12); else SELL_LAUNCH(false, 8, 12); break;    // 48 warps / SM, 8 steps in flight
-		case 2:  if (hint) SELL_LAUNCH(true, 4, 16); else SELL_LAUNCH(false, 4, 16); break;    // 64 warps / SM, 4 steps in flight
-		case 3:  if (hint) SELL_LAUNCH(true, 16, 4); else SELL_LAUNCH(false, 16, 4); break;    // 16 warps / SM, 16 steps in flight
+		// shape 0: short slices are latency-bound (more resident warps win), wide ones want registers for loads in flight
+		// (measured, profiles/r01f_sweep.txt: 8 x 48 wins below ~32 columns per slice, 8 x 32 above)
+		int shape = h->sell_variant;
+		if (shape == 0)
+			shape = (h->m > 0 && (double) h->padded / (double) h->m < 32.0) ? 2 : 1;
+		switch (shape) {
+		case 2:  if (hint) SELL_LAUNCH(true, 8, 12); else SELL_LAUNCH(false, 8, 12); break;    // 48 warps / SM, 8 steps in flight
+		case 3:  if (hint) SELL_LAUNCH(true, 4, 16); else SELL_LAUNCH(false, 4, 16); break;    // 64 warps / SM, 4 steps in flight
+		case 4:  if (hint) SELL_LAUNCH(true, 16, 4); else SELL_LAUNCH(false, 16, 4); break;    // 16 warps / SM, 16 steps in flight
 		default: if (hint) SELL_LAUNCH(true, 8, 8); else SELL_LAUNCH(false, 8, 8); break;      // 32 warps / SM, 8 steps in flight
 		}
 		#undef SELL_LAUNCH

@@ -182,6 +182,28 @@ def test_sell_large_sigma_global_sort(S, oracle):
         MF.close()
 
 
+def test_col_range_and_band_upload(S, oracle, golden_matrices):
+    """b200spmv_col_range is the exact min / max column (+1); the host entry point uploads only that band of x, so
+    x entries outside it must not influence y (NaN there stays invisible) while entries inside do."""
+    for (p, rp, col, val) in golden_matrices:
+        for fmt in (S.CSR_ADAPTIVE, S.SELL_C_SIGMA):
+            MF = S.csr_to_format(rp, col, val, p.rows, p.cols, int(rp[-1]), format=fmt)
+            lo, hi = MF.handle.col_range()
+            assert (lo, hi) == (int(col.min()), int(col.max()) + 1)
+            x = M.rand_x(p.cols)
+            xn = x.copy()
+            xn[:lo] = np.nan
+            xn[hi:] = np.nan
+            y = np.full(p.rows, 1.0)
+            MF.spmv(xn, y)
+            _check(oracle, rp, col, val, x, y, "band upload")
+            MF.close()
+    # out-of-range column indices are refused at create time
+    rp = np.array([0, 1], np.int32)
+    with pytest.raises(S.B200Error):
+        S.csr_to_format(rp, np.array([5], np.int32), np.ones(1), 1, 3, 1)
+
+
 # ------------------------------------------------------------------------------------------ AUTO
 def test_auto_format_resolves_and_matches(S, oracle, golden_matrices):
     """B200SPMV_AUTO builds both formats, times them on the device and keeps one: whatever it keeps must pass the
