@@ -446,6 +446,7 @@ extern "C" int b200spmv_spmv_host_ex(b200spmv_t * h, const double * x, double * 
 	if (!h->d_x) {
 		CU(cudaMalloc(&h->d_x, (h->n > 0 ? h->n : 1) * sizeof(double)));
 		CU(cudaMalloc(&h->d_y, (h->m > 0 ? h->m : 1) * sizeof(double)));
+		CU(cudaMemsetAsync(h->d_x, 0, (h->n > 0 ? h->n : 1) * sizeof(double), h->stream));
 	}
 	if (!h->x_uploaded)
 		flags &= ~B200SPMV_SKIP_X_UPLOAD;           // nothing to reuse yet
@@ -453,6 +454,9 @@ extern "C" int b200spmv_spmv_host_ex(b200spmv_t * h, const double * x, double * 
 	// only the columns the matrix references are read by the kernels: upload that band of x, not all n entries
 	if (!(flags & B200SPMV_SKIP_X_UPLOAD) && h->col_hi > h->col_lo)
 		CU(cudaMemcpyAsync(h->d_x + h->col_lo, x + h->col_lo, (h->col_hi - h->col_lo) * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+	// SELL-C-sigma padding entries are (column 0, 0.0) and are multiplied like real ones (sellcs_format.c:150-158): x[0] is read
+	if (!(flags & B200SPMV_SKIP_X_UPLOAD) && h->format == B200SPMV_SELL_C_SIGMA && h->col_lo > 0 && h->n > 0)
+		CU(cudaMemcpyAsync(h->d_x, x, sizeof(double), cudaMemcpyHostToDevice, h->stream));
 	if (b200spmv_spmv_device_ex(h, h->d_x, h->d_y, h->stream, nullptr))
 		return 1;
 	if (!(flags & B200SPMV_SKIP_Y_DOWNLOAD) && h->m > 0)
