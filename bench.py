@@ -142,8 +142,9 @@ def parse_args():
     ap.add_argument("--format", default=None, choices=["auto", "csr", "sell"],
                     help="default: auto at N=1 (both formats built, the faster kept per matrix), csr at N>1")
     ap.add_argument("--rows-per-gpu", type=int, default=4194304)
-    ap.add_argument("--exchange", default="mc", choices=["nccl", "p2p", "mc"],
-                    help="N>1: mc = fused stores to an NVSwitch multicast address (falls back to p2p), p2p = fused unicast peer stores, nccl = all-gather")
+    ap.add_argument("--exchange", default="p2p", choices=["nccl", "p2p", "mc"],
+                    help="N>1: p2p = fused unicast peer stores (default; measured fastest at N=8, profiles/r01g_bench_n8*.json), "
+                         "mc = fused stores to an NVSwitch multicast address (falls back to p2p), nccl = all-gather")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-sell", action="store_true")
     ap.add_argument("--full-exchange", action="store_true", help="N>1: send every y row to the peers, not only the referenced column band")

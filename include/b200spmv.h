@@ -55,7 +55,8 @@ enum {
 	B200SPMV_X_SLICE_PTR   = 3,    /* int64[nslices+1]    sellcs slice_pointers                       */
 	B200SPMV_X_SELL_COL    = 4,    /* int32[padded]       sellcs column_indices                       */
 	B200SPMV_X_SELL_VAL    = 5,    /* double[padded]      sellcs values                               */
-	B200SPMV_X_TILE_ROW    = 6,    /* int32[ntiles+1]     first row owned by each CSR tile            */
+	B200SPMV_X_TILE_ROW    = 6,    /* int32[ntiles+1]     first row owned by each CSR tile (with compressed
+	                                                       rows: first NON-EMPTY row starting in the tile)   */
 	B200SPMV_X_SPLIT_ROW   = 7,    /* int32[nsplit]       rows finished by the fix-up kernel          */
 	B200SPMV_X_SPLIT_TILE  = 8     /* int32[nsplit]       owner tile of each split row                */
 };
@@ -72,7 +73,9 @@ typedef struct b200spmv_opts {
 	int32_t sell_variant;     /* SELL kernel shape (k steps in flight x resident warps per SM): 0 = chosen from
 	                             the average slice width (AUTO: timed), 1 = 8 x 32, 2 = 8 x 48, 3 = 4 x 64,
 	                             4 = 16 x 16                                                             */
-	int32_t reserved[7];
+	int32_t csr_compress_rows; /* CSR: plan and run on the non-empty rows only, zero the empty ones in a separate balanced
+	                             launch: 0 = when a tile would own more than 2 tiles' worth of rows, 1 = never, 2 = always */
+	int32_t reserved[6];
 } b200spmv_opts;
 
 /* extra outputs / inputs of one device-resident product (all pointers are DEVICE pointers) */
@@ -116,12 +119,13 @@ int32_t b200spmv_format(const b200spmv_t * h);
  * outside that range, so b200spmv_spmv_host uploads only x[lo..hi) and a multi-GPU exchange only needs those rows. */
 int b200spmv_col_range(const b200spmv_t * h, int64_t * lo, int64_t * hi);
 
-/* Number of kernel launches one b200spmv_spmv_device call issues for this handle (1 or 2). */
+/* Number of kernel launches one b200spmv_spmv_device call issues for this handle (1 to 3). */
 int32_t b200spmv_launches_per_spmv(const b200spmv_t * h);
 
 /* Format statistics: out[0]=mem_footprint bytes, [1]=ntiles or nslices, [2]=nsplit rows,
  * [3]=padded entries (SELL) or nnz, [4]=tile nnz (CSR) or C (SELL), [5]=ext capacity or sigma, [6]=convert ms,
- * [7..9]=AUTO trial ms per product of CSR, SELL(sell_sigma), SELL(sell_sigma_alt); 0 = not tried. */
+ * [7..9]=AUTO trial ms per product of CSR, SELL(sell_sigma), SELL(sell_sigma_alt); 0 = not tried,
+ * [10]=1 when the CSR plan runs on compressed (non-empty) rows, [11]=number of empty rows zeroed separately. */
 int b200spmv_stats(const b200spmv_t * h, double * out, int32_t n_out);
 
 int b200spmv_export(const b200spmv_t * h, int32_t what, void * dst_host, int64_t capacity_bytes, int64_t * count_out);

@@ -49,6 +49,8 @@ static int validate_opts(const b200spmv_opts * in, b200spmv_opts * o, int64_t m,
 		B200_FAIL("unknown format %d", o->format);
 	if (o->sell_sigma_alt == 0)
 		o->sell_sigma_alt = 256;
+	if (o->csr_compress_rows < 0 || o->csr_compress_rows > 2)
+		B200_FAIL("csr_compress_rows must be 0 (auto), 1 (never) or 2 (always)");
 	if (o->sell_variant < 0 || o->sell_variant > 4)
 		B200_FAIL("sell_variant must be in [0, 4]");
 	if (o->sell_C == 0)
@@ -144,6 +146,15 @@ static void free_csr_plan(b200spmv * h, bool arrays)
 			cudaFree(*p);
 		*p = nullptr;
 	}
+	void ** more[] = { (void **) &h->d_rp_nz, (void **) &h->d_rows_nz, (void **) &h->d_empty_rows };
+	for (void ** p : more) {
+		if (*p)
+			cudaFree(*p);
+		*p = nullptr;
+	}
+	h->d_rp_plan = nullptr;
+	h->compressed = 0;
+	h->n_empty = 0;
 	if (arrays) {
 		if (h->d_col) cudaFree(h->d_col);
 		if (h->d_val) cudaFree(h->d_val);
@@ -275,7 +286,7 @@ static void free_handle(b200spmv * h)
 		return;
 	void * ptrs[] = { h->d_row_ptr, h->d_col, h->d_val, h->d_tile_row, h->d_split_row, h->d_split_tile, h->d_tile_head, h->d_tile_tail,
 	                  h->d_row_order, h->d_slice_width, h->d_slice_ptr, h->d_scol, h->d_sval, h->d_x, h->d_y, h->d_norm_partial,
-	                  h->d_sell_items, h->d_sell_cuts, h->d_sell_partial };
+	                  h->d_sell_items, h->d_sell_cuts, h->d_sell_partial, h->d_rp_nz, h->d_rows_nz, h->d_empty_rows };
 	for (void * p : ptrs)
 		if (p)
 			cudaFree(p);
@@ -314,6 +325,7 @@ static int create_common(b200spmv ** out, const int32_t * row_ptr, const int32_t
 	h->C = o.sell_C;
 	h->sigma = o.sell_sigma;
 	h->sell_variant = o.sell_variant;
+	h->compress_opt = o.csr_compress_rows;
 	int rc = 1;
 	cudaEvent_t e0 = nullptr, e1 = nullptr;
 	do {
@@ -419,7 +431,7 @@ extern "C" int32_t b200spmv_launches_per_spmv(const b200spmv_t * h)
 	if (!h)
 		return 0;
 	if (h->format == B200SPMV_CSR_ADAPTIVE)
-		return h->nsplit > 0 ? 2 : 1;
+		return (h->nsplit > 0 ? 2 : 1) + ((h->compressed && h->n_empty > 0) ? 1 : 0);
 	return h->sell_ncuts > 0 ? 2 : 1;
 }
 
@@ -477,11 +489,14 @@ extern "C" int b200spmv_stats(const b200spmv_t * h, double * out, int32_t n_out)
 {
 	if (!h || !out)
 		B200_FAIL("NULL argument");
-	double v[10];
+	double v[12];
 	for (int i = 0; i < 3; i++)
 		v[7 + i] = (double) h->trial_ms[i];
+	v[10] = (double) h->compressed;
+	v[11] = (double) h->n_empty;
 	if (h->format == B200SPMV_CSR_ADAPTIVE) {
-		v[0] = (double) h->nnz * 12.0 + (double) (h->m + 1) * 4.0 + (double) (h->ntiles + 1) * 8.0 + (double) h->ntiles * 16.0 + (double) h->nsplit * 8.0;
+		v[0] = (double) h->nnz * 12.0 + (double) (h->m + 1) * 4.0 + (double) (h->ntiles + 1) * 8.0 + (double) h->ntiles * 16.0 + (double) h->nsplit * 8.0
+		       + (h->compressed ? (double) (h->m_plan + 1) * 8.0 + (double) h->n_empty * 4.0 : 0.0);
 		v[1] = (double) h->ntiles;
 		v[2] = (double) h->nsplit;
 		v[3] = (double) h->nnz;
@@ -497,8 +512,26 @@ extern "C" int b200spmv_stats(const b200spmv_t * h, double * out, int32_t n_out)
 		v[5] = (double) h->sigma;
 	}
 	v[6] = (double) h->convert_ms;
-	for (int i = 0; i < n_out && i < 10; i++)
+	for (int i = 0; i < n_out && i < 12; i++)
 		out[i] = v[i];
+	return 0;
+}
+
+// Compressed row space: plan row k is original row rows_nz[k] (rows_nz[m_plan] = m).
+static int export_map_rows(const b200spmv * h, int32_t * d, int64_t count)
+{
+	if (!h->compressed)
+		return 0;
+	int32_t * map = (int32_t *) malloc((size_t) (h->m_plan + 1) * sizeof(int32_t));
+	if (!map)
+		B200_FAIL("out of host memory");
+	if (cudaMemcpy(map, h->d_rows_nz, (size_t) (h->m_plan + 1) * sizeof(int32_t), cudaMemcpyDeviceToHost) != cudaSuccess) {
+		free(map);
+		B200_FAIL("export: copy of the row map failed");
+	}
+	for (int64_t i = 0; i < count; i++)
+		d[i] = map[d[i]];
+	free(map);
 	return 0;
 }
 
@@ -534,9 +567,11 @@ extern "C" int b200spmv_export(const b200spmv_t * h, int32_t what, void * dst, i
 		int32_t * d = (int32_t *) dst;
 		for (int64_t i = 0; i < count; i++)
 			d[i] &= 0x7fffffff;
-		return 0;
+		return export_map_rows(h, d, count);
 	}
 	CU(cudaMemcpy(dst, src, (size_t) (count * esize), cudaMemcpyDeviceToHost));
+	if (what == B200SPMV_X_SPLIT_ROW)
+		return export_map_rows(h, (int32_t *) dst, count);
 	return 0;
 }
 

@@ -164,6 +164,17 @@ struct b200spmv {
 	int32_t * d_col;
 	double * d_val;
 
+	// Row compression (matrices with many / long runs of empty rows): the tile plan and the kernels then work on the
+	// non-empty rows only -- rp_plan[k] = row_ptr of the k-th non-empty row, rows_nz[k] = its index -- and the empty rows
+	// are zeroed by a separate, balanced launch.  Without compression rp_plan = d_row_ptr, m_plan = m, rows_nz = nullptr.
+	int compress_opt;         // 0 = auto, 1 = never, 2 = always
+	int compressed;
+	int64_t m_plan, n_empty;
+	int32_t * d_rp_plan;      // alias of d_row_ptr or d_rp_nz
+	int32_t * d_rp_nz;        // [m_plan + 1]
+	int32_t * d_rows_nz;      // [m_plan + 1], sentinel m
+	int32_t * d_empty_rows;   // [n_empty]
+
 	// CSR tile plan
 	int npt;                  // nnz per thread
 	int tile_nnz;             // CSR_THREADS * npt

@@ -146,7 +146,117 @@ __global__ void split_compact_kernel(const int2 * __restrict__ tile_info, const 
 	}
 }
 
+// ---- row compression ---------------------------------------------------------------------------
+__global__ void nonempty_flag_kernel(const int32_t * __restrict__ row_ptr, int64_t m, int64_t * __restrict__ flag)
+{
+	const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (i <= m)
+		flag[i] = (i < m && row_ptr[i + 1] > row_ptr[i]) ? 1 : 0;
+}
+
+__global__ void compress_rows_kernel(const int32_t * __restrict__ row_ptr, const int64_t * __restrict__ pos, int64_t m, int64_t m_nz,
+                                     int32_t * __restrict__ rp_nz, int32_t * __restrict__ rows_nz, int32_t * __restrict__ empty_rows)
+{
+	const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (i > m)
+		return;
+	if (i == m) {
+		rp_nz[m_nz] = row_ptr[m];
+		rows_nz[m_nz] = (int32_t) m;
+		return;
+	}
+	const int64_t k = pos[i];
+	if (row_ptr[i + 1] > row_ptr[i]) {
+		rp_nz[k] = row_ptr[i];
+		rows_nz[k] = (int32_t) i;
+	} else {
+		empty_rows[i - k] = (int32_t) i;
+	}
+}
+
+__global__ void max_owned_rows_kernel(const int2 * __restrict__ tile_info, int64_t ntiles, int * __restrict__ out)
+{
+	const int64_t t = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= ntiles)
+		return;
+	const int own = (tile_info[t + 1].x & 0x7fffffff) - (tile_info[t].x & 0x7fffffff);
+	atomicMax(out, own);
+}
+
+static void free_tile_plan(b200spmv * h)
+{
+	void ** ptrs[] = { (void **) &h->d_tile_row, (void **) &h->d_split_row, (void **) &h->d_split_tile, (void **) &h->d_tile_head,
+	                   (void **) &h->d_tile_tail };
+	for (void ** q : ptrs) {
+		if (*q)
+			cudaFree(*q);
+		*q = nullptr;
+	}
+}
+
+static int build_compressed_rows(b200spmv * h)
+{
+	const int64_t m = h->m;
+	int64_t * d_pos;
+	CU(cudaMalloc(&d_pos, (m + 1) * sizeof(int64_t)));
+	nonempty_flag_kernel<<<(unsigned) ((m + 1 + 255) / 256), 256, 0, h->stream>>>(h->d_row_ptr, m, d_pos);
+	CU_LAUNCH();
+	if (device_exclusive_scan_i64(d_pos, m + 1, h->stream)) {
+		cudaFree(d_pos);
+		return 1;
+	}
+	int64_t m_nz = 0;
+	CU(cudaMemcpyAsync(&m_nz, d_pos + m, sizeof(int64_t), cudaMemcpyDeviceToHost, h->stream));
+	CU(cudaStreamSynchronize(h->stream));
+	h->m_plan = m_nz;
+	h->n_empty = m - m_nz;
+	CU(cudaMalloc(&h->d_rp_nz, (m_nz + 1) * sizeof(int32_t)));
+	CU(cudaMalloc(&h->d_rows_nz, (m_nz + 1) * sizeof(int32_t)));
+	CU(cudaMalloc(&h->d_empty_rows, (h->n_empty > 0 ? h->n_empty : 1) * sizeof(int32_t)));
+	compress_rows_kernel<<<(unsigned) ((m + 1 + 255) / 256), 256, 0, h->stream>>>(h->d_row_ptr, d_pos, m, m_nz, h->d_rp_nz, h->d_rows_nz,
+	                                                                              h->d_empty_rows);
+	CU_LAUNCH();
+	CU(cudaStreamSynchronize(h->stream));
+	CU(cudaFree(d_pos));
+	h->d_rp_plan = h->d_rp_nz;
+	h->compressed = 1;
+	return 0;
+}
+
+static int plan_tiles_on(b200spmv * h);
+
+// Plans the tiles; switches to the compressed row space when empty rows would otherwise pile up on single tiles
+// (a tile owns every row that starts in its window, so a run of 200 000 empty rows is 200 000 rows for ONE CTA:
+// measured 0.70 ms -> see profiles/, the mawi twin of config 3).
 int csr_plan_tiles(b200spmv * h)
+{
+	h->d_rp_plan = h->d_row_ptr;
+	h->m_plan = h->m;
+	h->compressed = 0;
+	h->n_empty = 0;
+	if (h->compress_opt == 2)
+		return build_compressed_rows(h) || plan_tiles_on(h);
+	if (plan_tiles_on(h))
+		return 1;
+	if (h->compress_opt == 1 || h->m == 0)
+		return 0;
+	int * d_max;
+	int maxown = 0;
+	CU(cudaMalloc(&d_max, sizeof(int)));
+	CU(cudaMemsetAsync(d_max, 0, sizeof(int), h->stream));
+	max_owned_rows_kernel<<<(unsigned) ((h->ntiles + 255) / 256), 256, 0, h->stream>>>(reinterpret_cast<const int2 *>(h->d_tile_row), h->ntiles, d_max);
+	CU_LAUNCH();
+	CU(cudaMemcpyAsync(&maxown, d_max, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+	CU(cudaStreamSynchronize(h->stream));
+	CU(cudaFree(d_max));
+	// a window of T non-zeros holds at most T non-empty rows: more owned rows than 2 T means >= T empty ones on one CTA
+	if (maxown <= 2 * h->tile_nnz)
+		return 0;
+	free_tile_plan(h);
+	return build_compressed_rows(h) || plan_tiles_on(h);
+}
+
+static int plan_tiles_on(b200spmv * h)
 {
 	const int T = h->tile_nnz;
 	h->ntiles = (h->nnz + T - 1) / T;
@@ -162,7 +272,7 @@ int csr_plan_tiles(b200spmv * h)
 	int64_t * d_flag;
 	CU(cudaMalloc(&d_flag, h->ntiles * sizeof(int64_t)));
 	const unsigned blocks = (unsigned) ((h->ntiles + 1 + 255) / 256);
-	tile_info_kernel<<<blocks, 256, 0, h->stream>>>(h->d_row_ptr, h->m, h->nnz, h->ntiles, T, h->ext,
+	tile_info_kernel<<<blocks, 256, 0, h->stream>>>(h->d_rp_plan, h->m_plan, h->nnz, h->ntiles, T, h->ext,
 	                                                reinterpret_cast<int2 *>(h->d_tile_row), d_flag);
 	CU_LAUNCH();
 	// number of split rows = last flag + last exclusive-scan value

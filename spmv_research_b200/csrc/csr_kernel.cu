@@ -49,7 +49,7 @@ __global__ void __launch_bounds__(CSR_THREADS, (NPT <= 4) ? 8 : ((NPT <= 8) ? 6 
 csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict__ col, const double * __restrict__ val,
                 const int2 * __restrict__ tile_info, const double * __restrict__ x,
                 double * __restrict__ tile_head, double * __restrict__ tile_tail,
-                int64_t nnz, int ext_cap, YOut out)
+                int64_t nnz, int ext_cap, const int32_t * __restrict__ rowmap, YOut out)
 {
 	constexpr int T = CSR_THREADS * NPT;
 	extern __shared__ __align__(16) double s_prod[];      // T + ext_cap products
@@ -148,7 +148,7 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 			for (; a < b; a++)
 				sum += s_prod[swz(a)];
 			sum *= scale;
-			y_store(out, i, sum);
+			y_store(out, rowmap ? rowmap[i] : i, sum);
 			nrm += sum * sum;
 		}
 	} else if (rows_full > 0) {
@@ -170,7 +170,7 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 				sum += __shfl_xor_sync(0xffffffffu, sum, o);
 			if (r < rows_full && lane == 0) {
 				sum *= scale;
-				y_store(out, R0 + r, sum);
+				y_store(out, rowmap ? rowmap[R0 + r] : R0 + r, sum);
 				nrm += sum * sum;
 			}
 		}
@@ -210,7 +210,8 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 // One warp per split row: y[row] = tail[owner] + head[owner+1] + ... + head[last], fixed order.
 __global__ void csr_fixup_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict__ split_row,
                                  const int32_t * __restrict__ split_tile, const double * __restrict__ tile_head,
-                                 const double * __restrict__ tile_tail, int64_t nsplit, int tile_nnz, int64_t ntiles, YOut out)
+                                 const double * __restrict__ tile_tail, int64_t nsplit, int tile_nnz, int64_t ntiles,
+                                 const int32_t * __restrict__ rowmap, YOut out)
 {
 	const int64_t s = blockIdx.x;
 	if (s >= nsplit)
@@ -227,10 +228,17 @@ __global__ void csr_fixup_kernel(const int32_t * __restrict__ row_ptr, const int
 	if (lane == 0) {
 		const double scale = out.scale ? *out.scale : 1.0;
 		acc *= scale;
-		y_store(out, row, acc);
+		y_store(out, rowmap ? rowmap[row] : row, acc);
 		if (out.norm_partial)
 			out.norm_partial[ntiles + s] = acc * acc;
 	}
+}
+
+// Compressed row space: the empty rows, listed at plan time, are written 0 by a balanced grid-stride pass.
+__global__ void csr_zero_rows_kernel(const int32_t * __restrict__ empty_rows, int64_t n_empty, YOut out)
+{
+	for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n_empty; i += (int64_t) gridDim.x * blockDim.x)
+		y_store(out, empty_rows[i], 0.0);
 }
 
 // Deterministic final reduction of the per-CTA norm partials (single CTA, fixed tree).
@@ -269,8 +277,8 @@ static int launch_tiles(b200spmv * h, const double * dx, cudaStream_t st, const 
 		attr_set = true;
 	}
 	csr_tile_kernel<NPT, HINT><<<(unsigned) h->ntiles, CSR_THREADS, smem, st>>>(
-		h->d_row_ptr, h->d_col, h->d_val, reinterpret_cast<const int2 *>(h->d_tile_row), dx,
-		h->d_tile_head, h->d_tile_tail, h->nnz, h->ext, out);
+		h->d_rp_plan, h->d_col, h->d_val, reinterpret_cast<const int2 *>(h->d_tile_row), dx,
+		h->d_tile_head, h->d_tile_tail, h->nnz, h->ext, h->compressed ? h->d_rows_nz : nullptr, out);
 	CU_LAUNCH();
 	return 0;
 }
@@ -297,6 +305,11 @@ int launch_csr_spmv(b200spmv * h, const double * dx, double * dy, cudaStream_t s
 	}
 	int rc;
 	const bool hint = (h->x_hint == 0);
+	if (h->compressed && h->n_empty > 0) {
+		const int64_t want = (h->n_empty + 255) / 256;
+		csr_zero_rows_kernel<<<(unsigned) (want < 148 * 8 ? want : 148 * 8), 256, 0, st>>>(h->d_empty_rows, h->n_empty, out);
+		CU_LAUNCH();
+	}
 	switch (h->npt) {
 	case 4:  rc = hint ? launch_tiles<4, true>(h, dx, st, out) : launch_tiles<4, false>(h, dx, st, out); break;
 	case 8:  rc = hint ? launch_tiles<8, true>(h, dx, st, out) : launch_tiles<8, false>(h, dx, st, out); break;
@@ -307,8 +320,9 @@ int launch_csr_spmv(b200spmv * h, const double * dx, double * dy, cudaStream_t s
 	if (rc)
 		return rc;
 	if (h->nsplit > 0) {
-		csr_fixup_kernel<<<(unsigned) h->nsplit, 32, 0, st>>>(h->d_row_ptr, h->d_split_row, h->d_split_tile, h->d_tile_head,
-		                                                     h->d_tile_tail, h->nsplit, h->tile_nnz, h->ntiles, out);
+		csr_fixup_kernel<<<(unsigned) h->nsplit, 32, 0, st>>>(h->d_rp_plan, h->d_split_row, h->d_split_tile, h->d_tile_head,
+		                                                     h->d_tile_tail, h->nsplit, h->tile_nnz, h->ntiles,
+		                                                     h->compressed ? h->d_rows_nz : nullptr, out);
 		CU_LAUNCH();
 	}
 	if (l && l->norm2)

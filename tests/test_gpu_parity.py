@@ -76,7 +76,7 @@ def test_csr_split_rows_and_tile_plan(S, oracle):
         m, nnz = len(rp) - 1, int(rp[-1])
         for npt, ext in ((8, 64), (8, 1024), (16, 2048)):
             T = 256 * npt
-            MF = S.csr_to_format(rp, col, val, m, n, nnz, format=S.CSR_ADAPTIVE, csr_nnz_per_thread=npt, csr_ext=ext)
+            MF = S.csr_to_format(rp, col, val, m, n, nnz, format=S.CSR_ADAPTIVE, csr_nnz_per_thread=npt, csr_ext=ext, csr_compress_rows=1)
             ntiles = max(1, -(-nnz // T))
             want = np.minimum(np.searchsorted(rp, np.arange(ntiles) * T, side="left"), m).astype(np.int32)
             want[0] = 0
@@ -93,6 +93,48 @@ def test_csr_split_rows_and_tile_plan(S, oracle):
             assert np.array_equal(MF.handle.export(S.capi.X_SPLIT_TILE), np.array(split_tiles, np.int32))
             assert MF.gpu_launches_per_spmv == (2 if split_rows else 1)
             MF.close()
+
+
+def test_csr_compressed_rows(S, oracle):
+    """Row compression: the plan runs on the non-empty rows, the empty ones are zeroed by their own launch.  Forced on
+    every edge case (same y, plan = the numpy model evaluated on the compressed row_ptr and mapped back), and switched on
+    by itself when one tile would own a long run of empty rows (the mawi twin's shape: 99 % empty rows)."""
+    for name, rp, col, val, n in M.edge_cases():
+        m, nnz = len(rp) - 1, int(rp[-1])
+        x = M.rand_x(n, 5)
+        MF, y = _spmv(S, dict(format=S.CSR_ADAPTIVE, csr_compress_rows=2, csr_ext=64), rp, col, val, n, x)
+        _check(oracle, rp, col, val, x, y, "compressed " + name)
+        lens = np.diff(rp)
+        assert np.all(y[lens == 0] == 0.0), name
+        st = MF.handle.stats()
+        assert st["compressed_rows"] == 1 and st["n_empty"] == int((lens == 0).sum())
+        nz = np.nonzero(lens)[0]
+        rp_nz = np.append(rp[nz], nnz)
+        T, ext = 2048, 64
+        ntiles = max(1, -(-nnz // T))
+        k = np.minimum(np.searchsorted(rp_nz, np.arange(ntiles) * T, side="left"), len(nz))
+        k[0] = 0
+        k = np.append(k, len(nz))
+        rows_nz = np.append(nz, m)
+        assert np.array_equal(MF.handle.export(S.capi.X_TILE_ROW), rows_nz[k].astype(np.int32)), name
+        split = [rows_nz[k[t + 1] - 1] for t in range(ntiles) if k[t + 1] > k[t] and int(rp_nz[k[t + 1]]) - (t + 1) * T > ext]
+        assert np.array_equal(MF.handle.export(S.capi.X_SPLIT_ROW), np.array(split, np.int32)), name
+        assert MF.gpu_launches_per_spmv == (2 if split else 1) + (1 if st["n_empty"] else 0)
+        MF.close()
+    # auto: 60 000 empty rows in one run -> one tile would own them all
+    rng = np.random.default_rng(3)
+    lens = np.concatenate([rng.integers(1, 9, 3000), np.zeros(60000, np.int64), rng.integers(0, 5, 5000), [9000], np.zeros(7000, np.int64)])
+    rp, col, val = M.csr_from_lengths(lens, 20000, 4)
+    x = M.rand_x(20000, 6)
+    MF, y = _spmv(S, dict(format=S.CSR_ADAPTIVE), rp, col, val, 20000, x)
+    assert MF.handle.stats()["compressed_rows"] == 1
+    _check(oracle, rp, col, val, x, y, "auto-compressed")
+    assert np.all(y[lens == 0] == 0.0)
+    MF.close()
+    MF, y2 = _spmv(S, dict(format=S.CSR_ADAPTIVE, csr_compress_rows=1), rp, col, val, 20000, x)
+    assert MF.handle.stats()["compressed_rows"] == 0
+    _check(oracle, rp, col, val, x, y2, "not compressed")
+    MF.close()
 
 
 def test_csr_deterministic_and_repeatable(S, golden_matrices):
