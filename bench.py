@@ -30,6 +30,18 @@ METRIC = "SpMV GFLOP/s (2*nnz/t), fp64; effective HBM GB/s over compulsory bytes
 NOMINAL_HBM_GBS = 8000.0
 
 
+def ncu_traffic(kernel):
+    """DRAM bytes of one launch of `kernel` from the committed ncu --set full capture (profiles/ncu_traffic.json)."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        k = t[kernel]
+        tot = int(k["dram_bytes_read"]) + int(k["dram_bytes_write"])
+        return tot, "one launch on '%s' (compulsory bytes of that matrix: %d, ratio %.3f); %s" % (
+            t["matrix"], t["compulsory_bytes"], tot / t["compulsory_bytes"], t["source"])
+    except Exception:
+        return None, None
+
+
 def measured_peak():
     try:
         pk = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -305,6 +317,8 @@ def run_single(args):
            "d2h_bytes_per_step": int(sum(8 * r["m"] for r in mats)), "ms_per_step": round(te * 1e3, 4),
            "call": "Matrix_Format::spmv(x, y) via b200spmv_spmv_host, pinned host x / y"}
 
+    n_csr = sum(1 for r in mats if r["MF"].format == S.CSR_ADAPTIVE)
+    traffic, traffic_note = ncu_traffic("csr_tile_kernel" if 2 * n_csr >= len(mats) else "sell_kernel")
     out = {
         "metric": METRIC, "value": round(gflops, 2), "unit": "GFLOP/s", "n_gpus": 1, "steps": K, "warmup": W,
         "ms_per_step": round(ms_step, 5), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
@@ -319,7 +333,7 @@ def run_single(args):
         "roofline": {"bound": "hbm", "kernel": {S.AUTO: "csr_tile_kernel / sell_kernel (per matrix, see per_matrix[].format)",
                                                 S.CSR_ADAPTIVE: "csr_tile_kernel", S.SELL_C_SIGMA: "sell_kernel"}[fmt],
                      "achieved": round(tot_bc / kern_ms * 1e-6, 1), "peak": peak, "unit": "GB/s",
-                     "frac": round(tot_bc / kern_ms * 1e-6 / peak, 4), "traffic": None, "peak_source": peak_src,
+                     "frac": round(tot_bc / kern_ms * 1e-6 / peak, 4), "traffic": traffic, "traffic_note": traffic_note, "peak_source": peak_src,
                      "achieved_def": "compulsory bytes B_c = 12 nnz + 12 m + 8 n + 4 per SpMV / CUDA-event time of that SpMV, summed over the sample"},
         "e2e": e2e, "gpu_launches": int(launches), "clocks": clk.summary(), "per_matrix": per, "other_formats": other,
     }
