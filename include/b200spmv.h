@@ -75,7 +75,10 @@ typedef struct b200spmv_opts {
 	                             4 = 16 x 16                                                             */
 	int32_t csr_compress_rows; /* CSR: plan and run on the non-empty rows only, zero the empty ones in a separate balanced
 	                             launch: 0 = when a tile would own more than 2 tiles' worth of rows, 1 = never, 2 = always */
-	int32_t reserved[6];
+	int32_t x_l2_mb;          /* L2 budget for x in MiB (default 56): when the referenced band of x is larger, only
+	                             budget / band of its lines are gathered with the evict_last priority          */
+	int32_t keep_diag;        /* 1: extract diag(A) at create time (square matrices; needed by b200spmv_pcg)            */
+	int32_t reserved[4];
 } b200spmv_opts;
 
 /* extra outputs / inputs of one device-resident product (all pointers are DEVICE pointers) */
@@ -158,6 +161,23 @@ int b200spmv_ipc_close(void * dptr);
  * flush_bytes > 0 a scratch buffer of that size is rewritten before every product (outside the
  * per-product event pair) so that nothing of the matrix survives in L2.  ms_out[iters]. */
 int b200spmv_time_device(b200spmv_t * h, const double * dx, double * dy, int32_t iters, int64_t flush_bytes, float * ms_out);
+
+/* Jacobi-preconditioned CG entirely on the device: the reference harness's preconditioned_cg()
+ * (benchmark_code/BENCH/src/bench_cg.cpp:93-320: x0 = 0, K = diag(A), eps = 1e-15 ||b||, explicit residual / x_best /
+ * restart every 100 iterations) over b200spmv_spmv_device.  b, x: HOST vectors of m entries; the handle must have been
+ * created with keep_diag = 1.  Fails with "bad K, zero in diagonal" like the reference when a diagonal entry is missing. */
+typedef struct b200spmv_pcg_result {
+	int64_t iterations;       /* k at exit (num_loops_out, bench_cg.cpp:318)                            */
+	int64_t products;         /* SpMV products issued                                                   */
+	int64_t restarts;
+	double err;               /* ||r_k|| (recurrence)                                                   */
+	double err_explicit;      /* ||b - A x|| at exit                                                    */
+	double err_best;          /* of the returned x_best                                                 */
+	double eps;               /* 1e-15 ||b||                                                            */
+	int32_t converged;        /* err < eps                                                              */
+	int32_t pad_;
+} b200spmv_pcg_result;
+int b200spmv_pcg(b200spmv_t * h, const double * b_host, double * x_host, int64_t max_iterations, b200spmv_pcg_result * result);
 
 const char * b200spmv_last_error(void);
 const char * b200spmv_version(void);

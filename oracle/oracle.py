@@ -45,6 +45,8 @@ def lib():
         L.oracle_check_accuracy.argtypes = [_i32p, _i32p, _f64p, _f64p, _f64p, C.c_int64, C.c_double, C.c_void_p, _f64p]
         L.oracle_adaptive_rowblocks.argtypes = [_i32p, C.c_int64, C.c_int64, C.c_int64, _i32p]
         L.oracle_adaptive_rowblocks.restype = C.c_int64
+        L.oracle_pcg.argtypes = [_i32p, _i32p, _f64p, C.c_int64, _f64p, _f64p, C.c_int64, _f64p]
+        L.oracle_pcg.restype = C.c_int
         L.oracle_fnv1a64.argtypes = [C.c_void_p, C.c_int64]
         L.oracle_fnv1a64.restype = C.c_uint64
         _lib = L
@@ -143,6 +145,20 @@ def adaptive_rowblocks(row_ptr, block_nnz, multiblock):
     rb = np.zeros(m + multiblock + 2, np.int32)
     cnt = lib().oracle_adaptive_rowblocks(row_ptr, m, block_nnz, multiblock, rb)
     return rb[:cnt]
+
+
+def pcg(row_ptr, col_ind, val, b, max_iterations):
+    """Serial restatement of the reference's preconditioned_cg (bench_cg.cpp:93-320): (x_best, info dict)."""
+    m = len(row_ptr) - 1
+    x = np.zeros(max(m, 1))
+    out = np.zeros(5)
+    rc = lib().oracle_pcg(row_ptr, _pad1(col_ind, np.int32), _pad1(val, np.float64), m, np.ascontiguousarray(b, np.float64), x,
+                          int(max_iterations), out)
+    if rc == 1:
+        raise ValueError("bad K, zero in diagonal")
+    if rc:
+        raise MemoryError("oracle_pcg")
+    return x[:m], dict(iterations=int(out[0]), err=out[1], err_explicit=out[2], err_best=out[3], eps=out[4])
 
 
 def fnv1a64(a):

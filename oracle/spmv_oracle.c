@@ -369,3 +369,114 @@ uint64_t oracle_fnv1a64(const void *data, int64_t nbytes)
 	}
 	return h;
 }
+
+/*
+ * Jacobi-preconditioned CG, serial restatement of preconditioned_cg()
+ * (benchmark_code/BENCH/src/bench_cg.cpp:93-320): x0 = 0, K = diag(A) (first entry with j == i, :121-131),
+ * eps = 1e-15 * ||b||, eps_counter = 1e-7 * ||b|| (:159-175), every restart_k = 100 iterations the explicit residual
+ * b - A x is evaluated, x_best updated, and CG restarted from it when err_explicit / err > 1e3 while err_best >
+ * eps_counter (:186-236), stop when ||r|| < eps (:238) or k == max_iterations; afterwards one more explicit
+ * residual and x_best update, x_best is the answer (:290-320).  out[0..4] = iterations, err, err_explicit, err_best, eps.
+ * Returns 0, or 1 when a diagonal entry is missing / zero ("bad K, zero in diagonal").
+ */
+static double o_dot(const double *a, const double *b, int64_t n)
+{
+	double s = 0;
+	for (int64_t i = 0; i < n; i++)
+		s += a[i] * b[i];
+	return s;
+}
+
+static void o_spmv(const int32_t *rp, const int32_t *ci, const double *v, const double *x, double *y, int64_t m)
+{
+	for (int64_t i = 0; i < m; i++) {
+		double s = 0;
+		for (int64_t j = rp[i]; j < rp[i + 1]; j++)
+			s += v[j] * x[ci[j]];
+		y[i] = s;
+	}
+}
+
+int oracle_pcg(const int32_t *rp, const int32_t *ci, const double *v, int64_t m, const double *b, double *x_out,
+               int64_t max_iterations, double *out)
+{
+	double *mem = (double *)calloc((size_t)(8 * m + 8), sizeof(double));
+	if (!mem)
+		return 2;
+	double *rk = mem, *rke = mem + m, *pk = mem + 2 * m, *zk = mem + 3 * m, *Ap = mem + 4 * m, *K = mem + 5 * m, *x = mem + 6 * m,
+	       *xb = mem + 7 * m;
+	for (int64_t i = 0; i < m; i++) {
+		K[i] = 0;
+		for (int64_t j = rp[i]; j < rp[i + 1]; j++)
+			if (ci[j] == i) {
+				K[i] = v[j];
+				break;
+			}
+		if (K[i] == 0) {
+			free(mem);
+			return 1;
+		}
+	}
+	o_spmv(rp, ci, v, x, Ap, m);
+	for (int64_t i = 0; i < m; i++) {
+		rk[i] = b[i] + -1 * Ap[i];
+		zk[i] = rk[i] / K[i];
+		pk[i] = zk[i];
+	}
+	double err = sqrt(o_dot(rk, rk, m)), bn = sqrt(o_dot(b, b, m));
+	const double eps = 1.0e-15 * bn, eps_counter = 1.0e-7 * bn;
+	double err_explicit = err, err_best = err;
+	int64_t k = 0;
+	const int64_t restart_k = 100;
+	while (k < max_iterations) {
+		const int check = (k > 0) && !(k % restart_k);
+		if (check) {
+			o_spmv(rp, ci, v, x, Ap, m);
+			for (int64_t i = 0; i < m; i++)
+				rke[i] = b[i] + -1 * Ap[i];
+			err_explicit = sqrt(o_dot(rke, rke, m));
+			if (err_explicit < err_best) {
+				memcpy(xb, x, (size_t)m * sizeof(double));
+				err_best = err_explicit;
+			}
+		}
+		err = sqrt(o_dot(rk, rk, m));
+		if (check && (err_best > eps_counter) && (err_explicit / err > 1e3)) {
+			memcpy(rk, rke, (size_t)m * sizeof(double));
+			for (int64_t i = 0; i < m; i++)
+				zk[i] = rk[i] / K[i];
+			memcpy(pk, zk, (size_t)m * sizeof(double));
+		}
+		if (err < eps)
+			break;
+		o_spmv(rp, ci, v, pk, Ap, m);
+		const double old_zr = o_dot(zk, rk, m);
+		const double ak = o_dot(zk, rk, m) / o_dot(pk, Ap, m);
+		for (int64_t i = 0; i < m; i++)
+			x[i] = x[i] + ak * pk[i];
+		for (int64_t i = 0; i < m; i++)
+			rk[i] = rk[i] + -ak * Ap[i];
+		for (int64_t i = 0; i < m; i++)
+			zk[i] = rk[i] / K[i];
+		const double bk = o_dot(zk, rk, m) / old_zr;
+		for (int64_t i = 0; i < m; i++)
+			pk[i] = zk[i] + bk * pk[i];
+		k++;
+	}
+	o_spmv(rp, ci, v, x, Ap, m);
+	for (int64_t i = 0; i < m; i++)
+		rke[i] = b[i] + -1 * Ap[i];
+	err_explicit = sqrt(o_dot(rke, rke, m));
+	if (err_explicit < err_best) {
+		memcpy(xb, x, (size_t)m * sizeof(double));
+		err_best = err_explicit;
+	}
+	memcpy(x_out, xb, (size_t)m * sizeof(double));
+	out[0] = (double)k;
+	out[1] = err;
+	out[2] = err_explicit;
+	out[3] = err_best;
+	out[4] = eps;
+	free(mem);
+	return 0;
+}

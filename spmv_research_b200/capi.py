@@ -27,12 +27,17 @@ class B200Error(RuntimeError):
 
 class Opts(C.Structure):
     _fields_ = [("format", C.c_int32), ("device", C.c_int32), ("sell_C", C.c_int32), ("sell_sigma", C.c_int32),
-                ("csr_nnz_per_thread", C.c_int32), ("csr_ext", C.c_int32), ("x_hint", C.c_int32), ("sell_sigma_alt", C.c_int32), ("sell_variant", C.c_int32), ("csr_compress_rows", C.c_int32), ("reserved", C.c_int32 * 6)]
+                ("csr_nnz_per_thread", C.c_int32), ("csr_ext", C.c_int32), ("x_hint", C.c_int32), ("sell_sigma_alt", C.c_int32), ("sell_variant", C.c_int32), ("csr_compress_rows", C.c_int32), ("x_l2_mb", C.c_int32), ("keep_diag", C.c_int32), ("reserved", C.c_int32 * 4)]
 
 
 class Launch(C.Structure):
     _fields_ = [("scale", C.c_void_p), ("norm2", C.c_void_p), ("y_peer", C.c_void_p * 8), ("n_peer", C.c_int32), ("pad_", C.c_int32),
                 ("peer_row_lo", C.c_int64), ("peer_row_hi", C.c_int64)]
+
+
+class PcgResult(C.Structure):
+    _fields_ = [("iterations", C.c_int64), ("products", C.c_int64), ("restarts", C.c_int64), ("err", C.c_double),
+                ("err_explicit", C.c_double), ("err_best", C.c_double), ("eps", C.c_double), ("converged", C.c_int32), ("pad_", C.c_int32)]
 
 
 _lib = None
@@ -78,6 +83,7 @@ def lib():
         "b200spmv_ipc_import": (C.c_int, [vp, C.POINTER(vp)]),
         "b200spmv_ipc_close": (C.c_int, [vp]),
         "b200spmv_time_device": (C.c_int, [vp, vp, vp, i32, i64, vp]),
+        "b200spmv_pcg": (C.c_int, [vp, vp, vp, i64, C.POINTER(PcgResult)]),
         "b200spmv_last_error": (C.c_char_p, []),
         "b200spmv_version": (C.c_char_p, []),
     }
@@ -187,6 +193,15 @@ class Handle:
         out = np.zeros((W + 1, 2), np.int64)
         check(lib().b200spmv_merge_coords(self._h, W, out.ctypes.data))
         return out
+
+    def pcg(self, b, max_iterations):
+        """Jacobi-preconditioned CG of the reference harness (bench_cg.cpp:93-320) on the device; returns (x, result dict)."""
+        b = np.ascontiguousarray(b, np.float64)
+        assert b.size >= self.m
+        x = np.zeros(self.m)
+        r = PcgResult()
+        check(lib().b200spmv_pcg(self._h, _ptr(b), _ptr(x), int(max_iterations), C.byref(r)))
+        return x, {k: getattr(r, k) for k, _ in PcgResult._fields_ if k != "pad_"}
 
     def time_device(self, dx, dy, iters, flush_bytes=0):
         ms = np.zeros(iters, np.float32)

@@ -114,6 +114,9 @@ static int compute_col_range(b200spmv * h)
 		B200_FAIL("col_ind out of range: found [%d, %d], n = %lld", got[0], got[1], (long long) h->n);
 	h->col_lo = got[0];
 	h->col_hi = (int64_t) got[1] + 1;
+	// L2 budget for x: the 126 MB L2 of a B200 is two 63 MB halves and a line read from both dies is held twice
+	const double band = 8.0 * (double) (h->col_hi - h->col_lo), budget = (double) h->x_l2_mb * 1048576.0;
+	h->x_frac = (band <= budget) ? 1.0f : (float) (budget / band);
 	return 0;
 }
 
@@ -286,7 +289,7 @@ static void free_handle(b200spmv * h)
 		return;
 	void * ptrs[] = { h->d_row_ptr, h->d_col, h->d_val, h->d_tile_row, h->d_split_row, h->d_split_tile, h->d_tile_head, h->d_tile_tail,
 	                  h->d_row_order, h->d_slice_width, h->d_slice_ptr, h->d_scol, h->d_sval, h->d_x, h->d_y, h->d_norm_partial,
-	                  h->d_sell_items, h->d_sell_cuts, h->d_sell_partial, h->d_rp_nz, h->d_rows_nz, h->d_empty_rows };
+	                  h->d_sell_items, h->d_sell_cuts, h->d_sell_partial, h->d_rp_nz, h->d_rows_nz, h->d_empty_rows, h->d_diag };
 	for (void * p : ptrs)
 		if (p)
 			cudaFree(p);
@@ -326,6 +329,8 @@ static int create_common(b200spmv ** out, const int32_t * row_ptr, const int32_t
 	h->sigma = o.sell_sigma;
 	h->sell_variant = o.sell_variant;
 	h->compress_opt = o.csr_compress_rows;
+	h->x_l2_mb = o.x_l2_mb > 0 ? o.x_l2_mb : 56;
+	h->x_frac = 1.0f;
 	int rc = 1;
 	cudaEvent_t e0 = nullptr, e1 = nullptr;
 	do {
@@ -357,6 +362,7 @@ static int create_common(b200spmv ** out, const int32_t * row_ptr, const int32_t
 		}
 		if (cudaStreamSynchronize(h->stream) != cudaSuccess) break;
 		if (compute_col_range(h)) goto fail;
+		if (o.keep_diag && pcg_extract_diag(h)) goto fail;
 		int64_t norm_slots;
 		if (h->format == B200SPMV_AUTO) {
 			if (auto_select(h, o)) goto fail;           // convert_ms of an AUTO handle includes the trials
@@ -433,6 +439,11 @@ extern "C" int32_t b200spmv_launches_per_spmv(const b200spmv_t * h)
 	if (h->format == B200SPMV_CSR_ADAPTIVE)
 		return (h->nsplit > 0 ? 2 : 1) + ((h->compressed && h->n_empty > 0) ? 1 : 0);
 	return h->sell_ncuts > 0 ? 2 : 1;
+}
+
+int launch_spmv_any(b200spmv * h, const double * dx, double * dy, cudaStream_t st)
+{
+	return (h->format == B200SPMV_CSR_ADAPTIVE) ? launch_csr_spmv(h, dx, dy, st, nullptr) : launch_sell_spmv(h, dx, dy, st, nullptr);
 }
 
 extern "C" int b200spmv_spmv_device_ex(b200spmv_t * h, const double * dx, double * dy, void * stream, const b200spmv_launch * launch)

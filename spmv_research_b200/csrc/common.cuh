@@ -105,6 +105,16 @@ __device__ __forceinline__ uint64_t make_policy_evict_last()
 	return pol;
 }
 
+// x gathers when the referenced band of x is larger than the L2 can keep: evict_last on ALL of an over-sized working
+// set thrashes (LRU), so only a fraction of the lines (picked by the hardware from the address, quantised to 1/16) gets
+// evict_last and the rest keeps the default priority -- a stable subset of the band stays resident.
+__device__ __forceinline__ uint64_t make_policy_evict_last_frac(float frac)
+{
+	uint64_t pol;
+	asm volatile("createpolicy.fractional.L2::evict_last.L2::evict_unchanged.b64 %0, %1;" : "=l"(pol) : "f"(frac));
+	return pol;
+}
+
 template <bool HINT>
 __device__ __forceinline__ double ld_x(const double * p, uint64_t pol)
 {
@@ -155,6 +165,8 @@ struct b200spmv {
 	int64_t sell_pad_limit;       // AUTO: a SELL candidate padded beyond this many entries is skipped (0 = no limit)
 	int64_t m, n, nnz;
 	int64_t col_lo, col_hi;       // referenced columns lie in [col_lo, col_hi); x outside is never read
+	int x_l2_mb;                  // L2 budget for the x band, MiB
+	float x_frac;                 // fraction of the x band gathered with L2 evict_last (1 when the band fits the budget)
 	int x_hint;
 	cudaStream_t stream;
 	float convert_ms;
@@ -203,6 +215,10 @@ struct b200spmv {
 	double * d_sell_partial;  // [sell_nslots * 32]
 	int64_t sell_nitems, sell_ncuts, sell_nslots;
 
+	// diag(A) for the Jacobi-preconditioned CG (keep_diag), number of rows without a non-zero diagonal entry
+	double * d_diag;
+	int diag_bad;
+
 	// staging for the host-vector entry point, norm partials
 	double * d_x;
 	double * d_y;
@@ -218,3 +234,5 @@ int device_exclusive_scan_i64(int64_t * d_data, int64_t n, cudaStream_t st);
 int launch_csr_spmv(b200spmv * h, const double * dx, double * dy, cudaStream_t st, const b200spmv_launch * l);
 int launch_sell_spmv(b200spmv * h, const double * dx, double * dy, cudaStream_t st, const b200spmv_launch * l);
 int launch_norm_reduce(b200spmv * h, int64_t slots, double * d_out, cudaStream_t st);
+int launch_spmv_any(b200spmv * h, const double * dx, double * dy, cudaStream_t st);     // capi.cu: dispatch on h->format
+int pcg_extract_diag(b200spmv * h);                                                     // pcg.cu

@@ -60,3 +60,19 @@ def edge_cases():
     cases.append(("rect_wide", *csr_from_lengths(rng.integers(0, 30, 700), 100000, 12), 100000))
     cases.append(("rect_tall", *csr_from_lengths(rng.integers(0, 6, 9000), 17, 13), 17))
     return cases
+
+
+def spd_matrix(n, per_row, seed, dominance=1.05):
+    """Symmetric, strictly diagonally dominant CSR (int32 / f64, sorted columns): S = B + B^T off the diagonal with
+    B random, diag = dominance * sum |off-diagonal| + 0.1 -- what the reference's CG harness expects (an SPD system)."""
+    import scipy.sparse as sp
+    rng = np.random.default_rng(seed)
+    nnz = n * per_row
+    B = sp.coo_matrix((rng.uniform(-1.0, 1.0, nnz), (rng.integers(0, n, nnz), rng.integers(0, n, nnz))), shape=(n, n)).tocsr()
+    B.setdiag(0)
+    S = (B + B.T).tocsr()
+    S.eliminate_zeros()
+    d = dominance * np.asarray(abs(S).sum(axis=1)).ravel() + 0.1
+    S = (S + sp.diags(d)).tocsr()
+    S.sort_indices()
+    return S.indptr.astype(np.int32), S.indices.astype(np.int32), S.data.astype(np.float64)

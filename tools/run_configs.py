@@ -45,6 +45,9 @@ def workloads(names):
         elif nm == "twins":
             for p in H.load_param_file(os.path.join(ROOT, "spmv_research_b200", "params", "validation_twins.txt")):
                 out.append(("config3-twin:" + p.name, p))
+        elif nm == "classes":
+            for p in H.load_param_file(os.path.join(ROOT, "spmv_research_b200", "params", "medium_classes.txt")):
+                out.append(("config2-class:" + p.name, p))
         elif nm == "medium":
             for p in H.medium_sample():
                 out.append(("config2-sample", p))
