@@ -283,10 +283,54 @@ static int auto_select_impl(b200spmv * h, const b200spmv_opts & o, cudaEvent_t e
 	return 0;
 }
 
+// Ranges of the host-vector path (see common.cuh): only when every row is finished by the main kernel alone.
+static int plan_chunks(b200spmv * h)
+{
+	h->nchunks = 0;
+	h->range_count = -1;
+	const int NCH = 4;
+	if (h->m < 262144)
+		return 0;
+	if (h->format == B200SPMV_CSR_ADAPTIVE) {
+		if (h->nsplit > 0 || h->compressed || h->ntiles < 64 * NCH)
+			return 0;
+		for (int c = 0; c <= NCH; c++) {
+			h->chunk_unit[c] = h->ntiles * c / NCH;
+			int2 ti;
+			CU(cudaMemcpy(&ti, reinterpret_cast<const int2 *>(h->d_tile_row) + h->chunk_unit[c], sizeof(int2), cudaMemcpyDeviceToHost));
+			h->chunk_row[c] = ti.x & 0x7fffffff;
+		}
+		h->chunk_row[0] = 0;
+		h->chunk_row[NCH] = h->m;
+	} else {
+		const int64_t spw = h->sigma / h->C, nwin = (h->m + h->sigma - 1) / h->sigma;
+		const int G = h->C >= 32 ? h->C / 32 : 1;
+		if (h->sell_ncuts > 0 || nwin < 2 * NCH || h->sell_nitems != h->nslices * G)
+			return 0;
+		for (int c = 0; c <= NCH; c++) {
+			const int64_t s = (nwin * c / NCH) * spw;
+			h->chunk_unit[c] = s * G;
+			h->chunk_row[c] = s * h->C < h->m ? s * h->C : h->m;
+		}
+		h->chunk_unit[NCH] = h->sell_nitems;
+		h->chunk_row[NCH] = h->m;
+	}
+	CU(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+	for (int c = 0; c < NCH; c++)
+		CU(cudaEventCreateWithFlags(&h->chunk_ev[c], cudaEventDisableTiming));
+	h->nchunks = NCH;
+	return 0;
+}
+
 static void free_handle(b200spmv * h)
 {
 	if (!h)
 		return;
+	if (h->copy_stream)
+		cudaStreamDestroy(h->copy_stream);
+	for (cudaEvent_t e : h->chunk_ev)
+		if (e)
+			cudaEventDestroy(e);
 	void * ptrs[] = { h->d_row_ptr, h->d_col, h->d_val, h->d_tile_row, h->d_split_row, h->d_split_tile, h->d_tile_head, h->d_tile_tail,
 	                  h->d_row_order, h->d_slice_width, h->d_slice_ptr, h->d_scol, h->d_sval, h->d_x, h->d_y, h->d_norm_partial,
 	                  h->d_sell_items, h->d_sell_cuts, h->d_sell_partial, h->d_rp_nz, h->d_rows_nz, h->d_empty_rows, h->d_diag };
@@ -317,6 +361,7 @@ static int create_common(b200spmv ** out, const int32_t * row_ptr, const int32_t
 		B200_FAIL("out of host memory");
 	h->format = o.format;
 	h->requested_format = o.format;
+	h->range_count = -1;
 	CU(cudaGetDevice(&h->device));
 	h->m = m;
 	h->n = n;
@@ -380,6 +425,7 @@ static int create_common(b200spmv ** out, const int32_t * row_ptr, const int32_t
 			h->d_val = nullptr;
 			norm_slots = (h->sell_nitems + 3) / 4 + (h->sell_ncuts + 3) / 4;
 		}
+		if (plan_chunks(h)) goto fail;
 		h->norm_slots = norm_slots > 0 ? norm_slots : 1;
 		if (cudaMalloc(&h->d_norm_partial, h->norm_slots * sizeof(double)) != cudaSuccess) break;
 		cudaEventRecord(e1, h->stream);
@@ -480,6 +526,29 @@ extern "C" int b200spmv_spmv_host_ex(b200spmv_t * h, const double * x, double * 
 	// SELL-C-sigma padding entries are (column 0, 0.0) and are multiplied like real ones (sellcs_format.c:150-158): x[0] is read
 	if (!(flags & B200SPMV_SKIP_X_UPLOAD) && h->format == B200SPMV_SELL_C_SIGMA && h->col_lo > 0 && h->n > 0)
 		CU(cudaMemcpyAsync(h->d_x, x, sizeof(double), cudaMemcpyHostToDevice, h->stream));
+	if (h->nchunks > 1 && !(flags & B200SPMV_SKIP_Y_DOWNLOAD)) {
+		// the rows of a unit range are final when its kernel ends: their D2H copy runs under the next range's kernel
+		int rc = 0;
+		for (int c = 0; c < h->nchunks && !rc; c++) {
+			h->range_first = h->chunk_unit[c];
+			h->range_count = h->chunk_unit[c + 1] - h->chunk_unit[c];
+			rc = launch_spmv_any(h, h->d_x, h->d_y, h->stream);
+			h->range_count = -1;
+			if (rc)
+				break;
+			const int64_t r0 = h->chunk_row[c], r1 = h->chunk_row[c + 1];
+			CU(cudaEventRecord(h->chunk_ev[c], h->stream));
+			CU(cudaStreamWaitEvent(h->copy_stream, h->chunk_ev[c], 0));
+			if (r1 > r0)
+				CU(cudaMemcpyAsync(y + r0, h->d_y + r0, (r1 - r0) * sizeof(double), cudaMemcpyDeviceToHost, h->copy_stream));
+		}
+		h->range_count = -1;
+		if (rc)
+			return rc;
+		CU(cudaStreamSynchronize(h->stream));
+		CU(cudaStreamSynchronize(h->copy_stream));
+		return 0;
+	}
 	if (b200spmv_spmv_device_ex(h, h->d_x, h->d_y, h->stream, nullptr))
 		return 1;
 	if (!(flags & B200SPMV_SKIP_Y_DOWNLOAD) && h->m > 0)

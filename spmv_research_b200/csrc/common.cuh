@@ -219,6 +219,14 @@ struct b200spmv {
 	double * d_diag;
 	int diag_bad;
 
+	// Host-vector entry point: the product is launched in up to 4 unit ranges (tiles / SELL items) whose rows are final
+	// when the range's kernel ends, so the D2H copy of a range overlaps the kernel of the next one.
+	int nchunks;                  // 0 / 1 = one launch
+	int64_t chunk_unit[5], chunk_row[5];
+	int64_t range_first, range_count;      // range_count < 0: whole matrix (set only around the chunked launches)
+	cudaStream_t copy_stream;
+	cudaEvent_t chunk_ev[4];
+
 	// staging for the host-vector entry point, norm partials
 	double * d_x;
 	double * d_y;

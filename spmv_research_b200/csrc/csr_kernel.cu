@@ -49,7 +49,7 @@ __global__ void __launch_bounds__(CSR_THREADS, (NPT <= 4) ? 8 : ((NPT <= 8) ? 6 
 csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict__ col, const double * __restrict__ val,
                 const int2 * __restrict__ tile_info, const double * __restrict__ x,
                 double * __restrict__ tile_head, double * __restrict__ tile_tail,
-                int64_t nnz, int ext_cap, const int32_t * __restrict__ rowmap, float x_frac, YOut out)
+                int64_t nnz, int ext_cap, const int32_t * __restrict__ rowmap, float x_frac, int64_t tile_base, YOut out)
 {
 	constexpr int T = CSR_THREADS * NPT;
 	extern __shared__ __align__(16) double s_prod[];      // T + ext_cap products
@@ -57,7 +57,7 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 	__shared__ int s_rp[CSR_THREADS + 1];                 // window-relative row_ptr of the first 256 owned rows
 
 	const int tid = threadIdx.x;
-	const int64_t tile = blockIdx.x;
+	const int64_t tile = tile_base + blockIdx.x;
 	const int64_t base = tile * (int64_t) T;
 	const uint64_t pol = make_policy_evict_last_frac(x_frac);
 	const uint64_t pol_stream = make_policy_evict_first();
@@ -276,9 +276,13 @@ static int launch_tiles(b200spmv * h, const double * dx, cudaStream_t st, const 
 		CU(cudaFuncSetAttribute(csr_tile_kernel<NPT, HINT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
 		attr_set = true;
 	}
-	csr_tile_kernel<NPT, HINT><<<(unsigned) h->ntiles, CSR_THREADS, smem, st>>>(
+	const int64_t first = h->range_count >= 0 ? h->range_first : 0;
+	const int64_t count = h->range_count >= 0 ? h->range_count : h->ntiles;
+	if (count <= 0)
+		return 0;
+	csr_tile_kernel<NPT, HINT><<<(unsigned) count, CSR_THREADS, smem, st>>>(
 		h->d_rp_plan, h->d_col, h->d_val, reinterpret_cast<const int2 *>(h->d_tile_row), dx,
-		h->d_tile_head, h->d_tile_tail, h->nnz, h->ext, h->compressed ? h->d_rows_nz : nullptr, h->x_frac, out);
+		h->d_tile_head, h->d_tile_tail, h->nnz, h->ext, h->compressed ? h->d_rows_nz : nullptr, h->x_frac, first, out);
 	CU_LAUNCH();
 	return 0;
 }

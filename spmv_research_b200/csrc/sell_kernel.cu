@@ -149,12 +149,14 @@ int launch_sell_spmv(b200spmv * h, const double * dx, double * dy, cudaStream_t 
 		out.norm_partial = l->norm2 ? h->d_norm_partial : nullptr;
 	}
 	constexpr int WPC = SELL_THREADS / 32;
-	const int64_t ctas = (h->sell_nitems + WPC - 1) / WPC;
+	const int64_t first = h->range_count >= 0 ? h->range_first : 0;
+	const int64_t nit = h->range_count >= 0 ? h->range_count : h->sell_nitems;
+	const int64_t ctas = (nit + WPC - 1) / WPC;
 	const int64_t fix_ctas = (h->sell_ncuts + WPC - 1) / WPC;
 	if (ctas > 0) {
-		const int4 * items = reinterpret_cast<const int4 *>(h->d_sell_items);
+		const int4 * items = reinterpret_cast<const int4 *>(h->d_sell_items) + first;
 		#define SELL_LAUNCH(HINT, U, MINB)                                                                                          \
-			sell_kernel<HINT, U, MINB><<<(unsigned) ctas, SELL_THREADS, 0, st>>>(items, h->sell_nitems, h->d_row_order, h->d_scol, \
+			sell_kernel<HINT, U, MINB><<<(unsigned) ctas, SELL_THREADS, 0, st>>>(items, nit, h->d_row_order, h->d_scol, \
 			                                                                     h->d_sval, dx, h->d_sell_partial, h->m, h->C, h->x_frac, out)
 		const bool hint = (h->x_hint == 0);
 		// shape 0: short slices are latency-bound (more resident warps win), wide ones want registers for loads in flight
