@@ -634,26 +634,35 @@ def run_reference(args):
         for p in plist:
             rp, col, val = amg.generate(p)
             items.append((rp, col, val, p.cols))
-        sample = "every matrix of the %s workload, one SpMV each per step" % wl
-    runners, cores, kind = [], 0, "port"
+        sample = "every matrix of the %s workload, one SpMV each per step (timed matrix by matrix, K calls each)" % wl
+    # One matrix at a time: the reference's CSR plugin keeps its per-thread row ranges in file-scope arrays
+    # (K/csr.cpp thread_i_s / thread_i_e), so a second csr_to_format() re-partitions EVERY live object; timing several
+    # objects in turn would run all of them on the last matrix's row ranges (an incomplete, far too fast product).
+    from oracle import oracle as O
+    cores, kind, t, nnzs, verified = 0, "port", 0.0, [], True
     for rp, col, val, n in items:
         run, kind, cores = cpu_csr_runner(rp, col, val, n)
-        runners.append((run, np.ones(n), np.full(len(rp) - 1, 1.0), int(rp[-1])))
-    for _ in range(max(W, 1)):
-        for run, x, y, nnz in runners:
+        x, y = np.ones(n), np.full(len(rp) - 1, 1.0)
+        for _ in range(max(W, 1)):
             run(x, y)
-    t0 = time.perf_counter()
-    for _ in range(K):
-        for run, x, y, nnz in runners:
+        t0 = time.perf_counter()
+        for _ in range(K):
             run(x, y)
-    t = (time.perf_counter() - t0) / K
+        t += (time.perf_counter() - t0) / K
+        nnzs.append(int(rp[-1]))
+        y_ser = O.csr_spmv(rp, col, val, x)
+        verified = verified and bool(np.all(np.abs(y - y_ser) <= 1e-12 * O.row_abs_bound(rp, col, val, x)))
+    if not verified:
+        raise SystemExit("bench.py --impl reference: the CPU kernel's y does not match the serial oracle")
+    runners = [(None, None, None, z) for z in nnzs]
     flops = sum(2.0 * r[3] for r in runners)
     val_ = round(flops / t * 1e-9, 3)
     emit({"impl": "reference", "metric": METRIC, "value": val_, "unit": "GFLOP/s", "n_gpus": world, "steps": K, "warmup": W,
           "ms_per_step": round(t * 1e3, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
           "data": "synthetic (same generator and parameter lines as the b200 arm)",
           "config": {"workload": wl, "format": "Custom_CSR_B (reference OpenMP CSR, K/csr.cpp)"},
-          "cpu_baseline": {"value": val_, "unit": "GFLOP/s", "cores": cores, "kind": kind, "sample": sample},
+          "cpu_baseline": {"value": val_, "unit": "GFLOP/s", "cores": cores, "kind": kind, "sample": sample,
+                           "verified_against_serial_oracle": verified},
           "e2e": {"value": val_, "unit": "GFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
 
 

@@ -187,7 +187,9 @@ def ref(name):
 
 
 class RefCSR:
-    """The reference's CPU CSR plugin (K/csr.cpp) behind its own csr_to_format()/spmv()."""
+    """The reference's CPU CSR plugin (K/csr.cpp) behind its own csr_to_format()/spmv().
+    CAUTION: the plugin keeps its per-thread row ranges in file-scope arrays (thread_i_s / thread_i_e, K/csr.cpp:36-44), so
+    only the MOST RECENTLY created object computes a complete product: create, use, then create the next."""
 
     def __init__(self, row_ptr, col_ind, val, n):
         L = ref("csr")
