@@ -78,7 +78,10 @@ typedef struct b200spmv_opts {
 	int32_t x_l2_mb;          /* L2 budget for x in MiB (default 56): when the referenced band of x is larger, only
 	                             budget / band of its lines are gathered with the evict_last priority          */
 	int32_t keep_diag;        /* 1: extract diag(A) at create time (square matrices; needed by b200spmv_pcg)            */
-	int32_t reserved[4];
+	int32_t pin_host_vectors; /* 1: b200spmv_spmv_host page-locks (cudaHostRegister) each distinct x / y buffer it is handed
+	                             the first time it sees it (the harness's aligned_alloc vectors live for the whole run,
+	                             bench_spmv.cpp:598-606) and unregisters them in b200spmv_destroy                    */
+	int32_t reserved[3];
 } b200spmv_opts;
 
 /* extra outputs / inputs of one device-resident product (all pointers are DEVICE pointers) */

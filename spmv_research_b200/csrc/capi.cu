@@ -326,6 +326,8 @@ static void free_handle(b200spmv * h)
 {
 	if (!h)
 		return;
+	for (int i = 0; i < h->n_pinned; i++)
+		cudaHostUnregister(h->pinned[i]);
 	if (h->copy_stream)
 		cudaStreamDestroy(h->copy_stream);
 	for (cudaEvent_t e : h->chunk_ev)
@@ -374,6 +376,7 @@ static int create_common(b200spmv ** out, const int32_t * row_ptr, const int32_t
 	h->sigma = o.sell_sigma;
 	h->sell_variant = o.sell_variant;
 	h->compress_opt = o.csr_compress_rows;
+	h->pin_host = o.pin_host_vectors;
 	h->x_l2_mb = o.x_l2_mb > 0 ? o.x_l2_mb : 56;
 	h->x_frac = 1.0f;
 	int rc = 1;
@@ -507,11 +510,35 @@ extern "C" int b200spmv_spmv_device(b200spmv_t * h, const double * dx, double * 
 	return b200spmv_spmv_device_ex(h, dx, dy, stream, nullptr);
 }
 
+// Page-locks a caller buffer once (pageable memory moves at a third of the PCIe rate and cannot overlap with kernels).
+static void pin_once(b200spmv * h, const void * p, size_t bytes)
+{
+	if (!h->pin_host || bytes == 0)
+		return;
+	for (int i = 0; i < h->n_pinned; i++)
+		if (h->pinned[i] == p)
+			return;
+	if (h->n_pinned >= 4)
+		return;
+	cudaPointerAttributes a;
+	if (cudaPointerGetAttributes(&a, p) == cudaSuccess && a.type != cudaMemoryTypeUnregistered)
+		return;                                    // already pinned / managed by the caller
+	cudaGetLastError();
+	if (cudaHostRegister(const_cast<void *>(p), bytes, cudaHostRegisterDefault) == cudaSuccess)
+		h->pinned[h->n_pinned++] = const_cast<void *>(p);
+	else
+		cudaGetLastError();                        // not fatal: the copies fall back to the pageable path
+}
+
 extern "C" int b200spmv_spmv_host_ex(b200spmv_t * h, const double * x, double * y, int32_t flags)
 {
 	if (!h || !x || !y)
 		B200_FAIL("NULL argument");
 	CU(cudaSetDevice(h->device));
+	if (!(flags & B200SPMV_SKIP_X_UPLOAD))
+		pin_once(h, x, (size_t) h->n * sizeof(double));
+	if (!(flags & B200SPMV_SKIP_Y_DOWNLOAD))
+		pin_once(h, y, (size_t) h->m * sizeof(double));
 	if (!h->d_x) {
 		CU(cudaMalloc(&h->d_x, (h->n > 0 ? h->n : 1) * sizeof(double)));
 		CU(cudaMalloc(&h->d_y, (h->m > 0 ? h->m : 1) * sizeof(double)));

@@ -227,6 +227,10 @@ struct b200spmv {
 	cudaStream_t copy_stream;
 	cudaEvent_t chunk_ev[4];
 
+	int pin_host;                 // page-lock the caller's x / y on first sight
+	void * pinned[4];             // buffers this handle registered (unregistered at destroy)
+	int n_pinned;
+
 	// staging for the host-vector entry point, norm partials
 	double * d_x;
 	double * d_y;

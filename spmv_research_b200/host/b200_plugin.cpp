@@ -19,6 +19,7 @@
  * Run-time switches (environment, read once in csr_to_format):
  *     B200SPMV_TRANSFER = first | always   x upload / y download on the first spmv call only (the reference's
  *                         GPU-plugin convention, spmv_kernels/GPU_clean/cuda_csr.cu:353-430; default) or on every call
+ *     B200SPMV_PIN      = 1 | 0   page-lock the harness's x / y buffers on first use (default 1)
  *     B200SPMV_DEVICE   = CUDA device ordinal (default: current device)
  *     B200SPMV_SELL_C / B200SPMV_SELL_SIGMA   slice height / sort window (defaults 32 / 16384, sell_c_s.cpp:58-60)
  * Errors follow the reference: message on stderr and exit(1) (lib/debug.h:135); there is no CPU fallback.
@@ -70,7 +71,10 @@ struct B200_Format : Matrix_Format
 			o.format = B200SPMV_CSR_ADAPTIVE;
 			format_name = (char *) "B200_CSR_ADAPTIVE";
 		#endif
+		o.pin_host_vectors = 1;     /* x and y are the harness's aligned_alloc buffers, alive for the whole run (bench_spmv.cpp:598-606) */
 		const char * e;
+		if ((e = getenv("B200SPMV_PIN")) != NULL)
+			o.pin_host_vectors = atoi(e);
 		if ((e = getenv("B200SPMV_DEVICE")) != NULL)
 			o.device = atoi(e);
 		if ((e = getenv("B200SPMV_SELL_C")) != NULL)

@@ -369,6 +369,23 @@ def test_host_flags_reference_convention(S, oracle, golden_matrices):
     assert np.array_equal(y2, 2.0 * y1)
 
 
+def test_pin_host_vectors(S, oracle, golden_matrices):
+    """pin_host_vectors page-locks the caller's pageable x / y on first sight and releases them at destroy: same y, the
+    buffers stay usable by the host and by a second handle afterwards."""
+    p, rp, col, val = golden_matrices[1]
+    x = M.rand_x(p.cols)
+    y = np.full(p.rows + 64, 1.0)
+    for rep in range(2):
+        MF = S.csr_to_format(rp, col, val, p.rows, p.cols, int(rp[-1]), format=S.CSR_ADAPTIVE, pin_host_vectors=1)
+        for _ in range(3):
+            y[:] = 1.0
+            MF.spmv(x, y)
+            _check(oracle, rp, col, val, x, y[:p.rows], "pinned host vectors")
+            assert np.all(y[p.rows:] == 1.0)
+        MF.close()
+        x = x * 1.0 if rep == 0 else x          # a fresh (different) buffer for the second handle
+
+
 def test_bad_options_fail_loudly(S, golden_matrices):
     p, rp, col, val = golden_matrices[0]
     SELL = dict(format=S.SELL_C_SIGMA)
