@@ -81,7 +81,10 @@ typedef struct b200spmv_opts {
 	int32_t pin_host_vectors; /* 1: b200spmv_spmv_host page-locks (cudaHostRegister) each distinct x / y buffer it is handed
 	                             the first time it sees it (the harness's aligned_alloc vectors live for the whole run,
 	                             bench_spmv.cpp:598-606) and unregisters them in b200spmv_destroy                    */
-	int32_t reserved[3];
+	int32_t col_panels;       /* column panels for an x band larger than L2: 0 = auto (band > 64 MB and >= 24 nnz / row:
+	                             ceil(band / 44 MB) panels), 1 = none, 2..8 = that many; each panel is a sub-handle of the
+	                             requested format, launched in ascending column order, y accumulated                  */
+	int32_t reserved[2];
 } b200spmv_opts;
 
 /* extra outputs / inputs of one device-resident product (all pointers are DEVICE pointers) */
@@ -131,7 +134,8 @@ int32_t b200spmv_launches_per_spmv(const b200spmv_t * h);
 /* Format statistics: out[0]=mem_footprint bytes, [1]=ntiles or nslices, [2]=nsplit rows,
  * [3]=padded entries (SELL) or nnz, [4]=tile nnz (CSR) or C (SELL), [5]=ext capacity or sigma, [6]=convert ms,
  * [7..9]=AUTO trial ms per product of CSR, SELL(sell_sigma), SELL(sell_sigma_alt); 0 = not tried,
- * [10]=1 when the CSR plan runs on compressed (non-empty) rows, [11]=number of empty rows zeroed separately. */
+ * [10]=1 when the CSR plan runs on compressed (non-empty) rows, [11]=number of empty rows zeroed separately,
+ * [12]=number of column panels (1 = none; with panels [0] and [6] are totals, the rest describes panel 0). */
 int b200spmv_stats(const b200spmv_t * h, double * out, int32_t n_out);
 
 int b200spmv_export(const b200spmv_t * h, int32_t what, void * dst_host, int64_t capacity_bytes, int64_t * count_out);

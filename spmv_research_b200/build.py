@@ -9,7 +9,7 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "lib")
-CU_SOURCES = ["capi.cu", "csr_kernel.cu", "sell_kernel.cu", "convert.cu", "partition.cu", "pcg.cu"]
+CU_SOURCES = ["capi.cu", "csr_kernel.cu", "sell_kernel.cu", "convert.cu", "partition.cu", "pcg.cu", "panels.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared", "--cudart", "static"]
 

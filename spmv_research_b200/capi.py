@@ -27,7 +27,7 @@ class B200Error(RuntimeError):
 
 class Opts(C.Structure):
     _fields_ = [("format", C.c_int32), ("device", C.c_int32), ("sell_C", C.c_int32), ("sell_sigma", C.c_int32),
-                ("csr_nnz_per_thread", C.c_int32), ("csr_ext", C.c_int32), ("x_hint", C.c_int32), ("sell_sigma_alt", C.c_int32), ("sell_variant", C.c_int32), ("csr_compress_rows", C.c_int32), ("x_l2_mb", C.c_int32), ("keep_diag", C.c_int32), ("pin_host_vectors", C.c_int32), ("reserved", C.c_int32 * 3)]
+                ("csr_nnz_per_thread", C.c_int32), ("csr_ext", C.c_int32), ("x_hint", C.c_int32), ("sell_sigma_alt", C.c_int32), ("sell_variant", C.c_int32), ("csr_compress_rows", C.c_int32), ("x_l2_mb", C.c_int32), ("keep_diag", C.c_int32), ("pin_host_vectors", C.c_int32), ("col_panels", C.c_int32), ("reserved", C.c_int32 * 2)]
 
 
 class Launch(C.Structure):
@@ -176,10 +176,10 @@ class Handle:
         return lo.value, hi.value
 
     def stats(self):
-        out = (C.c_double * 12)()
-        check(lib().b200spmv_stats(self._h, out, 12))
+        out = (C.c_double * 13)()
+        check(lib().b200spmv_stats(self._h, out, 13))
         keys = ("mem_footprint", "units", "nsplit", "entries", "unit_size", "ext_or_sigma", "convert_ms",
-                "trial_ms_csr", "trial_ms_sell", "trial_ms_sell_alt", "compressed_rows", "n_empty")
+                "trial_ms_csr", "trial_ms_sell", "trial_ms_sell_alt", "compressed_rows", "n_empty", "col_panels")
         return dict(zip(keys, list(out)))
 
     def export(self, what):

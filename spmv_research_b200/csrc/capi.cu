@@ -49,6 +49,8 @@ static int validate_opts(const b200spmv_opts * in, b200spmv_opts * o, int64_t m,
 		B200_FAIL("unknown format %d", o->format);
 	if (o->sell_sigma_alt == 0)
 		o->sell_sigma_alt = 256;
+	if (o->col_panels < 0 || o->col_panels > 8)
+		B200_FAIL("col_panels must be in [0, 8]");
 	if (o->csr_compress_rows < 0 || o->csr_compress_rows > 2)
 		B200_FAIL("csr_compress_rows must be 0 (auto), 1 (never) or 2 (always)");
 	if (o->sell_variant < 0 || o->sell_variant > 4)
@@ -289,7 +291,7 @@ static int plan_chunks(b200spmv * h)
 	h->nchunks = 0;
 	h->range_count = -1;
 	const int NCH = 4;
-	if (h->m < 262144)
+	if (h->m < 262144 || h->npanels > 1)
 		return 0;
 	if (h->format == B200SPMV_CSR_ADAPTIVE) {
 		if (h->nsplit > 0 || h->compressed || h->ntiles < 64 * NCH)
@@ -326,6 +328,8 @@ static void free_handle(b200spmv * h)
 {
 	if (!h)
 		return;
+	for (int q = 0; q < h->npanels; q++)
+		free_handle(h->panel[q]);
 	for (int i = 0; i < h->n_pinned; i++)
 		cudaHostUnregister(h->pinned[i]);
 	if (h->copy_stream)
@@ -412,7 +416,27 @@ static int create_common(b200spmv ** out, const int32_t * row_ptr, const int32_t
 		if (compute_col_range(h)) goto fail;
 		if (o.keep_diag && pcg_extract_diag(h)) goto fail;
 		int64_t norm_slots;
-		if (h->format == B200SPMV_AUTO) {
+		const int P = panels_auto_count(h, o.col_panels);
+		if (P > 1) {
+			// column panels: this handle becomes a shell around P sub-handles (panels.cu)
+			b200spmv_opts sub = o;
+			sub.col_panels = 1;
+			sub.csr_compress_rows = 1;          // every panel launch must pass every row through y_finish
+			sub.keep_diag = 0;
+			sub.device = -1;
+			if (panels_split(h, P, &sub)) goto fail;
+			cudaFree(h->d_col);
+			cudaFree(h->d_val);
+			h->d_col = nullptr;
+			h->d_val = nullptr;
+			h->format = B200SPMV_CSR_ADAPTIVE;
+			for (int q = 0; q < h->npanels; q++) {
+				h->panel[q]->acc_mode = (q > 0 ? 1 : 0) | (q + 1 < h->npanels ? 2 : 0);
+				if (h->panel[q]->format == B200SPMV_SELL_C_SIGMA)
+					h->format = B200SPMV_SELL_C_SIGMA;      // "some panel reads x[0] for its padding"
+			}
+			norm_slots = 1;
+		} else if (h->format == B200SPMV_AUTO) {
 			if (auto_select(h, o)) goto fail;           // convert_ms of an AUTO handle includes the trials
 			norm_slots = (h->format == B200SPMV_CSR_ADAPTIVE) ? h->ntiles + h->nsplit
 			                                                   : (h->sell_nitems + 3) / 4 + (h->sell_ncuts + 3) / 4;
@@ -485,14 +509,48 @@ extern "C" int32_t b200spmv_launches_per_spmv(const b200spmv_t * h)
 {
 	if (!h)
 		return 0;
+	if (h->npanels > 1) {
+		int32_t n = 0;
+		for (int q = 0; q < h->npanels; q++)
+			n += b200spmv_launches_per_spmv(h->panel[q]);
+		return n;
+	}
 	if (h->format == B200SPMV_CSR_ADAPTIVE)
 		return (h->nsplit > 0 ? 2 : 1) + ((h->compressed && h->n_empty > 0) ? 1 : 0);
 	return h->sell_ncuts > 0 ? 2 : 1;
 }
 
+// One product: a plain handle launches its kernel(s); a panel shell launches its sub-handles in ascending column order, the
+// last of which receives the caller's epilogue (scale, norm, peer destinations).
+static int launch_product(b200spmv * h, const double * dx, double * dy, cudaStream_t st, const b200spmv_launch * l)
+{
+	if (h->npanels > 1) {
+		for (int q = 0; q < h->npanels; q++) {
+			b200spmv * s = h->panel[q];
+			const b200spmv_launch * lq = (q + 1 == h->npanels) ? l : nullptr;
+			const int rc = (s->format == B200SPMV_CSR_ADAPTIVE) ? launch_csr_spmv(s, dx, dy, st, lq) : launch_sell_spmv(s, dx, dy, st, lq);
+			if (rc)
+				return rc;
+		}
+		return 0;
+	}
+	return (h->format == B200SPMV_CSR_ADAPTIVE) ? launch_csr_spmv(h, dx, dy, st, l) : launch_sell_spmv(h, dx, dy, st, l);
+}
+
 int launch_spmv_any(b200spmv * h, const double * dx, double * dy, cudaStream_t st)
 {
-	return (h->format == B200SPMV_CSR_ADAPTIVE) ? launch_csr_spmv(h, dx, dy, st, nullptr) : launch_sell_spmv(h, dx, dy, st, nullptr);
+	return launch_product(h, dx, dy, st, nullptr);
+}
+
+int create_from_device(b200spmv ** out, const int32_t * d_row_ptr, const int32_t * d_col, const double * d_val, int64_t m, int64_t n,
+                       int64_t nnz, const b200spmv_opts * opts)
+{
+	return b200spmv_create_device(out, d_row_ptr, d_col, d_val, m, n, nnz, opts);
+}
+
+void destroy_handle(b200spmv * h)
+{
+	b200spmv_destroy(h);
 }
 
 extern "C" int b200spmv_spmv_device_ex(b200spmv_t * h, const double * dx, double * dy, void * stream, const b200spmv_launch * launch)
@@ -500,9 +558,7 @@ extern "C" int b200spmv_spmv_device_ex(b200spmv_t * h, const double * dx, double
 	if (!h || !dx || !dy)
 		B200_FAIL("NULL argument");
 	cudaStream_t st = (cudaStream_t) stream;       // NULL is the CUDA legacy default stream (what torch's default stream is)
-	if (h->format == B200SPMV_CSR_ADAPTIVE)
-		return launch_csr_spmv(h, dx, dy, st, launch);
-	return launch_sell_spmv(h, dx, dy, st, launch);
+	return launch_product(h, dx, dy, st, launch);
 }
 
 extern "C" int b200spmv_spmv_device(b200spmv_t * h, const double * dx, double * dy, void * stream)
@@ -596,7 +652,24 @@ extern "C" int b200spmv_stats(const b200spmv_t * h, double * out, int32_t n_out)
 {
 	if (!h || !out)
 		B200_FAIL("NULL argument");
-	double v[12];
+	double v[13];
+	if (h->npanels > 1) {
+		// panel shell: footprints and launches add up, the rest describes panel 0
+		double w[13];
+		if (b200spmv_stats(h->panel[0], v, 13))
+			return 1;
+		for (int q = 1; q < h->npanels; q++) {
+			if (b200spmv_stats(h->panel[q], w, 13))
+				return 1;
+			v[0] += w[0];
+		}
+		v[6] = (double) h->convert_ms;
+		v[12] = (double) h->npanels;
+		for (int i = 0; i < n_out && i < 13; i++)
+			out[i] = v[i];
+		return 0;
+	}
+	v[12] = 1.0;
 	for (int i = 0; i < 3; i++)
 		v[7 + i] = (double) h->trial_ms[i];
 	v[10] = (double) h->compressed;
@@ -619,7 +692,7 @@ extern "C" int b200spmv_stats(const b200spmv_t * h, double * out, int32_t n_out)
 		v[5] = (double) h->sigma;
 	}
 	v[6] = (double) h->convert_ms;
-	for (int i = 0; i < n_out && i < 12; i++)
+	for (int i = 0; i < n_out && i < 13; i++)
 		out[i] = v[i];
 	return 0;
 }
@@ -646,6 +719,8 @@ extern "C" int b200spmv_export(const b200spmv_t * h, int32_t what, void * dst, i
 {
 	if (!h || !count_out)
 		B200_FAIL("NULL argument");
+	if (h->npanels > 1)
+		B200_FAIL("export: the handle is a shell around %d column panels (create with col_panels = 1 to export a layout)", h->npanels);
 	CU(cudaSetDevice(h->device));
 	const void * src = nullptr;
 	int64_t count = 0, esize = 4;

@@ -132,6 +132,8 @@ struct YOut {
 	double * peer[8];
 	int n_peer;
 	int64_t peer_lo, peer_hi; // rows stored to the peers: [peer_lo, peer_hi)
+	int accum;                // column panels: add the partial already in y[row] (earlier panels) to this panel's row sum
+	int partial;              // column panels: not the last panel -> store the raw sum to y only (no scale / peers / norm)
 	const double * scale;     // device scalar or nullptr
 	double * norm_partial;    // one slot per CTA or nullptr
 };
@@ -144,6 +146,20 @@ __device__ __forceinline__ void y_store(const YOut & o, int64_t row, double v)
 	for (int d = 0; d < 8; d++)          // unrolled + predicated: keeps the parameter struct out of local memory
 		if (d < o.n_peer && send)
 			o.peer[d][row] = v;
+}
+
+// Finishes one row: returns the value that entered y (what the norm accumulates), 0 for a partial panel.
+__device__ __forceinline__ double y_finish(const YOut & o, int64_t row, double sum, double scale)
+{
+	if (o.accum)
+		sum += o.y[row];
+	if (o.partial) {
+		o.y[row] = sum;
+		return 0.0;
+	}
+	sum *= scale;
+	y_store(o, row, sum);
+	return sum;
 }
 
 __device__ __forceinline__ double warp_sum(double v)
@@ -227,6 +243,12 @@ struct b200spmv {
 	cudaStream_t copy_stream;
 	cudaEvent_t chunk_ev[4];
 
+	// Column panels (x band larger than L2): this handle is then a shell around npanels sub-handles, one per column
+	// range, launched in turn; sub-handle p > 0 adds to the partial in y, the last one finishes the rows (scale, peers, norm).
+	int npanels;
+	struct b200spmv * panel[8];
+	int acc_mode;                 // bit 0: accumulate into y, bit 1: partial (not the last panel)
+
 	int pin_host;                 // page-lock the caller's x / y on first sight
 	void * pinned[4];             // buffers this handle registered (unregistered at destroy)
 	int n_pinned;
@@ -247,4 +269,11 @@ int launch_csr_spmv(b200spmv * h, const double * dx, double * dy, cudaStream_t s
 int launch_sell_spmv(b200spmv * h, const double * dx, double * dy, cudaStream_t st, const b200spmv_launch * l);
 int launch_norm_reduce(b200spmv * h, int64_t slots, double * d_out, cudaStream_t st);
 int launch_spmv_any(b200spmv * h, const double * dx, double * dy, cudaStream_t st);     // capi.cu: dispatch on h->format
-int pcg_extract_diag(b200spmv * h);                                                     // pcg.cu
+int pcg_extract_diag(b200spmv * h);
+// panels.cu
+int panels_auto_count(const b200spmv * h, int requested);
+int panels_split(b200spmv * h, int P, const b200spmv_opts * sub_opts);
+// capi.cu
+int create_from_device(b200spmv ** out, const int32_t * d_row_ptr, const int32_t * d_col, const double * d_val, int64_t m, int64_t n,
+                       int64_t nnz, const b200spmv_opts * opts);
+void destroy_handle(b200spmv * h);                                                     // pcg.cu

@@ -147,8 +147,7 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 			double sum = 0.0;
 			for (; a < b; a++)
 				sum += s_prod[swz(a)];
-			sum *= scale;
-			y_store(out, rowmap ? rowmap[i] : i, sum);
+			sum = y_finish(out, rowmap ? rowmap[i] : i, sum, scale);
 			nrm += sum * sum;
 		}
 	} else if (rows_full > 0) {
@@ -169,8 +168,7 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 			for (int o = lpr >> 1; o > 0; o >>= 1)
 				sum += __shfl_xor_sync(0xffffffffu, sum, o);
 			if (r < rows_full && lane == 0) {
-				sum *= scale;
-				y_store(out, rowmap ? rowmap[R0 + r] : R0 + r, sum);
+				sum = y_finish(out, rowmap ? rowmap[R0 + r] : R0 + r, sum, scale);
 				nrm += sum * sum;
 			}
 		}
@@ -227,8 +225,7 @@ __global__ void csr_fixup_kernel(const int32_t * __restrict__ row_ptr, const int
 	acc = warp_sum(acc);
 	if (lane == 0) {
 		const double scale = out.scale ? *out.scale : 1.0;
-		acc *= scale;
-		y_store(out, rowmap ? rowmap[row] : row, acc);
+		acc = y_finish(out, rowmap ? rowmap[row] : row, acc, scale);
 		if (out.norm_partial)
 			out.norm_partial[ntiles + s] = acc * acc;
 	}
@@ -238,7 +235,7 @@ __global__ void csr_fixup_kernel(const int32_t * __restrict__ row_ptr, const int
 __global__ void csr_zero_rows_kernel(const int32_t * __restrict__ empty_rows, int64_t n_empty, YOut out)
 {
 	for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n_empty; i += (int64_t) gridDim.x * blockDim.x)
-		y_store(out, empty_rows[i], 0.0);
+		y_finish(out, empty_rows[i], 0.0, 1.0);
 }
 
 // Deterministic final reduction of the per-CTA norm partials (single CTA, fixed tree).
@@ -307,6 +304,8 @@ int launch_csr_spmv(b200spmv * h, const double * dx, double * dy, cudaStream_t s
 		out.scale = l->scale;
 		out.norm_partial = l->norm2 ? h->d_norm_partial : nullptr;
 	}
+	out.accum = h->acc_mode & 1;
+	out.partial = (h->acc_mode >> 1) & 1;
 	int rc;
 	const bool hint = (h->x_hint == 0);
 	if (h->compressed && h->n_empty > 0) {

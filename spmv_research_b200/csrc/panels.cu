@@ -1,0 +1,149 @@
+// panels.cu -- column panels for matrices whose referenced band of x does not fit the L2.
+//
+// Measured (profiles/r01o_ncu_full_c5shard_csr_key_metrics.txt): a config-5 row shard gathers from an 80 MB band of x; the
+// L2 (two 63 MB halves) cannot hold it, the kernel reads 5.5 GB from DRAM for 3.4 GB of compulsory bytes and runs at
+// 1.04 ms, against 0.81 ms for the same shard shape with a 10 MB band.  Splitting the columns into P ranges of <= 44 MB of
+// x each and running one product per range (y += A_p x, ascending p) keeps every range's x resident; the price is one
+// read-modify-write of y per extra panel (16 bytes per row) -- worth it from ~24 non-zeros per row.
+//
+// The split happens once, on the GPU, at create time: per row and panel a count, a scan per panel, a scatter that keeps
+// the order of a row's entries; each panel becomes an ordinary sub-handle (CSR / SELL-C-sigma / AUTO, picked per panel).
+#include "common.cuh"
+
+constexpr int MAX_PANELS = 8;
+
+struct PanelBounds { int32_t c[MAX_PANELS + 1]; };
+
+__device__ __forceinline__ int panel_of(const PanelBounds & b, int P, int col)
+{
+	int p = 0;
+	#pragma unroll
+	for (int q = 1; q < MAX_PANELS; q++)
+		p += (q < P && col >= b.c[q]) ? 1 : 0;
+	return p;
+}
+
+// cnt[p * (m + 1) + i] = entries of row i in panel p (thread per row; one-time cost)
+__global__ void panel_count_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict__ col, int64_t m, int P, PanelBounds b,
+                                   int64_t * __restrict__ cnt)
+{
+	const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (i > m)
+		return;
+	int c[MAX_PANELS] = { 0 };
+	if (i < m)
+		for (int64_t j = row_ptr[i]; j < row_ptr[i + 1]; j++) {
+			const int p = panel_of(b, P, col[j]);
+			#pragma unroll
+			for (int q = 0; q < MAX_PANELS; q++)
+				c[q] += (q == p) ? 1 : 0;
+		}
+	#pragma unroll
+	for (int q = 0; q < MAX_PANELS; q++)
+		if (q < P)
+			cnt[(int64_t) q * (m + 1) + i] = c[q];
+}
+
+// after the per-panel exclusive scans: rp[p][i] = off[p][i]; entries scattered in row order
+__global__ void panel_fill_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict__ col, const double * __restrict__ val,
+                                  int64_t m, int P, PanelBounds b, const int64_t * __restrict__ off, const int64_t * __restrict__ base,
+                                  int32_t * __restrict__ prp, int32_t * __restrict__ pcol, double * __restrict__ pval)
+{
+	const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (i > m)
+		return;
+	int64_t o[MAX_PANELS];
+	#pragma unroll
+	for (int q = 0; q < MAX_PANELS; q++)
+		if (q < P) {
+			o[q] = off[(int64_t) q * (m + 1) + i];
+			prp[(int64_t) q * (m + 1) + i] = (int32_t) o[q];
+			o[q] += base[q];
+		}
+	if (i == m)
+		return;
+	for (int64_t j = row_ptr[i]; j < row_ptr[i + 1]; j++) {
+		const int cj = col[j];
+		const int p = panel_of(b, P, cj);
+		int64_t dst = 0;
+		#pragma unroll
+		for (int q = 0; q < MAX_PANELS; q++)
+			if (q == p)
+				dst = o[q]++;
+		pcol[dst] = cj;
+		pval[dst] = val[j];
+	}
+}
+
+// 0 = auto: panels when the band is larger than 64 MB and rows are long enough to pay for the y read-modify-write
+int panels_auto_count(const b200spmv * h, int requested)
+{
+	if (requested == 1 || h->nnz == 0 || h->m == 0)
+		return 1;
+	if (requested > 1)
+		return requested > MAX_PANELS ? MAX_PANELS : requested;
+	const double band = 8.0 * (double) (h->col_hi - h->col_lo), avg = (double) h->nnz / (double) h->m;
+	if (band <= 64.0 * 1048576.0 || avg < 24.0)
+		return 1;
+	int P = (int) ((band + 44.0 * 1048576.0 - 1.0) / (44.0 * 1048576.0));
+	return P > MAX_PANELS ? MAX_PANELS : (P < 2 ? 2 : P);
+}
+
+// Splits h's CSR arrays (device) into P column panels and creates one sub-handle per panel.
+int panels_split(b200spmv * h, int P, const b200spmv_opts * sub_opts)
+{
+	const int64_t m = h->m;
+	PanelBounds b;
+	const int64_t lo = h->col_lo, span = h->col_hi - h->col_lo;
+	for (int q = 0; q <= MAX_PANELS; q++)
+		b.c[q] = (int32_t) (q >= P ? h->col_hi : lo + span * q / P);
+	int64_t * d_cnt = nullptr, * d_base = nullptr;
+	int32_t * d_prp = nullptr, * d_pcol = nullptr;
+	double * d_pval = nullptr;
+	int rc = 1;
+	int64_t tot[MAX_PANELS], base[MAX_PANELS];
+	const unsigned blocks = (unsigned) ((m + 1 + 255) / 256);
+	do {
+		if (cudaMalloc(&d_cnt, (size_t) P * (m + 1) * sizeof(int64_t)) != cudaSuccess) break;
+		if (cudaMalloc(&d_base, MAX_PANELS * sizeof(int64_t)) != cudaSuccess) break;
+		if (cudaMalloc(&d_prp, (size_t) P * (m + 1) * sizeof(int32_t)) != cudaSuccess) break;
+		if (cudaMalloc(&d_pcol, (size_t) (h->nnz > 0 ? h->nnz : 1) * sizeof(int32_t)) != cudaSuccess) break;
+		if (cudaMalloc(&d_pval, (size_t) (h->nnz > 0 ? h->nnz : 1) * sizeof(double)) != cudaSuccess) break;
+		panel_count_kernel<<<blocks, 256, 0, h->stream>>>(h->d_row_ptr, h->d_col, m, P, b, d_cnt);
+		if (cudaPeekAtLastError() != cudaSuccess) break;
+		bool ok = true;
+		int64_t run = 0;
+		for (int q = 0; q < P && ok; q++) {
+			ok = device_exclusive_scan_i64(d_cnt + (int64_t) q * (m + 1), m + 1, h->stream) == 0 &&
+			     cudaMemcpyAsync(&tot[q], d_cnt + (int64_t) q * (m + 1) + m, sizeof(int64_t), cudaMemcpyDeviceToHost, h->stream) == cudaSuccess &&
+			     cudaStreamSynchronize(h->stream) == cudaSuccess;
+			base[q] = run;
+			run += tot[q];
+		}
+		if (!ok || run != h->nnz) break;
+		if (cudaMemcpyAsync(d_base, base, P * sizeof(int64_t), cudaMemcpyHostToDevice, h->stream) != cudaSuccess) break;
+		panel_fill_kernel<<<blocks, 256, 0, h->stream>>>(h->d_row_ptr, h->d_col, h->d_val, m, P, b, d_cnt, d_base, d_prp, d_pcol, d_pval);
+		if (cudaPeekAtLastError() != cudaSuccess || cudaStreamSynchronize(h->stream) != cudaSuccess) break;
+		rc = 0;
+	} while (0);
+	if (rc)
+		snprintf(g_b200_err, sizeof(g_b200_err), "column panels: CUDA failure: %s", cudaGetErrorString(cudaGetLastError()));
+	for (int q = 0; q < P && !rc; q++) {
+		rc = create_from_device(&h->panel[q], d_prp + (int64_t) q * (m + 1), d_pcol + base[q], d_pval + base[q], m, h->n, tot[q], sub_opts);
+		if (!rc)
+			h->npanels = q + 1;
+	}
+	cudaFree(d_cnt);
+	cudaFree(d_base);
+	cudaFree(d_prp);
+	cudaFree(d_pcol);
+	cudaFree(d_pval);
+	if (rc) {
+		for (int q = 0; q < h->npanels; q++) {
+			destroy_handle(h->panel[q]);
+			h->panel[q] = nullptr;
+		}
+		h->npanels = 0;
+	}
+	return rc;
+}

@@ -71,8 +71,7 @@ sell_kernel(const int4 * __restrict__ items, int64_t nitems, const int32_t * __r
 			partial[(int64_t) item.z * 32 + lane] = acc;
 		} else if (r < m && lane < C) {
 			const double scale = out.scale ? *out.scale : 1.0;
-			acc *= scale;
-			y_store(out, dst_row, acc);
+			acc = y_finish(out, dst_row, acc, scale);
 			nrm = acc * acc;
 		}
 	}
@@ -108,8 +107,7 @@ sell_fixup_kernel(const int4 * __restrict__ cuts, int64_t ncuts, const int32_t *
 		const int64_t r = (int64_t) cut.x * C + cut.w * 32 + lane;
 		if (r < m && lane < C) {
 			const double scale = out.scale ? *out.scale : 1.0;
-			acc *= scale;
-			y_store(out, row_order[r], acc);
+			acc = y_finish(out, row_order[r], acc, scale);
 			nrm = acc * acc;
 		}
 	}
@@ -148,6 +146,8 @@ int launch_sell_spmv(b200spmv * h, const double * dx, double * dy, cudaStream_t 
 		out.scale = l->scale;
 		out.norm_partial = l->norm2 ? h->d_norm_partial : nullptr;
 	}
+	out.accum = h->acc_mode & 1;
+	out.partial = (h->acc_mode >> 1) & 1;
 	constexpr int WPC = SELL_THREADS / 32;
 	const int64_t first = h->range_count >= 0 ? h->range_first : 0;
 	const int64_t nit = h->range_count >= 0 ? h->range_count : h->sell_nitems;

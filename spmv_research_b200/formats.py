@@ -29,6 +29,7 @@ class MatrixFormat:
         self.requested_format = fmt
         self.format = handle.format                     # AUTO resolves to CSR or SELL at create time
         self.format_name = ("B200_AUTO:" if fmt == capi.AUTO else "") + FORMAT_NAMES[self.format]
+        self.col_panels = int(st["col_panels"])
         self.sigma = int(st["ext_or_sigma"]) if self.format == capi.SELL_C_SIGMA else None
         self.trial_ms = {k[9:]: round(st[k], 5) for k in ("trial_ms_csr", "trial_ms_sell", "trial_ms_sell_alt") if st[k] > 0}
         self.convert_ms = st["convert_ms"]

@@ -353,6 +353,62 @@ def test_device_path_scale_norm_peers_shard(S, oracle, golden_matrices):
         MF.close()
 
 
+def test_column_panels(S, oracle, golden_matrices):
+    """Column panels (x band larger than L2): the handle is a shell around P sub-handles launched in ascending column
+    order, y accumulated, the last panel finishing the rows.  Forced here on small matrices: same per-row bound for every
+    format, every panel count, the edge cases (empty rows, giant rows, rectangular), the fused epilogue and PCG."""
+    import torch
+    dev = torch.device("cuda:0")
+    st = torch.cuda.current_stream().cuda_stream
+    cases = [(p.cols, rp, col, val) for (p, rp, col, val) in golden_matrices] + [(n, rp, col, val) for _, rp, col, val, n in M.edge_cases()]
+    for n, rp, col, val in cases:
+        m, nnz = len(rp) - 1, int(rp[-1])
+        x = M.rand_x(n, 11)
+        for fmt in (S.CSR_ADAPTIVE, S.SELL_C_SIGMA, S.AUTO):
+            for P in (2, 5):
+                MF, y = _spmv(S, dict(format=fmt, col_panels=P), rp, col, val, n, x)
+                _check(oracle, rp, col, val, x, y, "panels %d fmt %d" % (P, fmt))
+                st_ = MF.handle.stats()
+                assert st_["col_panels"] == (P if nnz > 0 and m > 0 else 1)
+                if nnz > 0:
+                    with pytest.raises(S.B200Error):
+                        MF.handle.export(S.capi.X_TILE_ROW)
+                MF.close()
+    # fused epilogue through the last panel: y = s A x, norm, peer destinations limited to a row range
+    p, rp, col, val = golden_matrices[1]
+    x = M.rand_x(p.cols)
+    dx = torch.from_numpy(x).to(dev)
+    yr = oracle.csr_spmv(rp, col, val, x)
+    bound = oracle.row_abs_bound(rp, col, val, x)
+    for fmt in (S.CSR_ADAPTIVE, S.SELL_C_SIGMA):
+        MF = S.csr_to_format(rp, col, val, p.rows, p.cols, int(rp[-1]), format=fmt, col_panels=3)
+        dy = torch.full((p.rows,), 1.0, dtype=torch.float64, device=dev)
+        peer = torch.zeros(p.rows, dtype=torch.float64, device=dev)
+        scale = torch.tensor([0.25], dtype=torch.float64, device=dev)
+        norm2 = torch.zeros(1, dtype=torch.float64, device=dev)
+        lo, hi = p.rows // 4, p.rows // 2
+        MF.spmv_device(dx, dy, st, scale=scale, norm2=norm2, peers=[peer], peer_rows=(lo, hi))
+        torch.cuda.synchronize()
+        y = dy.cpu().numpy()
+        assert np.all(np.abs(y - 0.25 * yr) <= REL * bound)
+        pb = peer.cpu().numpy()
+        assert np.array_equal(pb[lo:hi], y[lo:hi]) and np.all(pb[:lo] == 0) and np.all(pb[hi:] == 0)
+        assert abs(norm2.item() - float(np.sum(y * y))) <= 1e-12 * float(np.sum(y * y))
+        MF.close()
+    # auto rule: small bands never split
+    MF = S.csr_to_format(rp, col, val, p.rows, p.cols, int(rp[-1]))
+    assert MF.handle.stats()["col_panels"] == 1
+    MF.close()
+    # PCG over a panel shell
+    rps, cols, vals = M.spd_matrix(20000, 6, 8)
+    b = np.random.default_rng(9).uniform(-1, 1, 20000)
+    x_ref, ref = oracle.pcg(rps, cols, vals, b, 500)
+    MF = S.csr_to_format(rps, cols, vals, 20000, 20000, int(rps[-1]), keep_diag=1, col_panels=2)
+    xs, res = MF.handle.pcg(b, 500)
+    assert res["converged"] == 1 and np.linalg.norm(xs - x_ref) <= 1e-11 * np.linalg.norm(x_ref)
+    MF.close()
+
+
 def test_host_flags_reference_convention(S, oracle, golden_matrices):
     """cache_x=True follows the reference GPU plugins: x is uploaded on the first call only
     (GPU_clean/cuda_csr.cu:353-382), so a changed x at the same address is NOT seen."""

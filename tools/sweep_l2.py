@@ -26,13 +26,14 @@ for ln in LINES:
     dx = torch.ones(n, dtype=torch.float64, device=dev)
     dy = torch.zeros(m, dtype=torch.float64, device=dev)
     for fmt, fname in ((S.CSR_ADAPTIVE, "csr"), (S.SELL_C_SIGMA, "sell")):
-        for mb in (4000, 112, 84, 64, 56, 48, 36, 24):
-            MF = S.csr_to_format(rp, col, val, m, n, nnz, 0, 0, format=fmt, x_l2_mb=mb)
+        for mb in ((56, 1), (56, 2), (56, 3), (56, 4), (56, 0)) if os.environ.get("SWEEP_PANELS") else [(v, 1) for v in (4000, 112, 84, 64, 56, 48, 36, 24)]:
+            mb, panels = mb
+            MF = S.csr_to_format(rp, col, val, m, n, nnz, 0, 0, format=fmt, x_l2_mb=mb, col_panels=panels)
             lo, hi = MF.handle.col_range()
             frac = min(1.0, mb * 2 ** 20 / (8.0 * (hi - lo)))
             MF.handle.time_device(dx, dy, 3, 256 << 20)
             ms = float(np.median(MF.handle.time_device(dx, dy, 9, 256 << 20)))
-            print("%-100s %-5s %7d %6.3f %9.4f %8.0f" % (ln[:100], fname, mb, frac, ms, bc / ms * 1e-6), flush=True)
+            print("%-100s %-5s %7d %6.3f %9.4f %8.0f  panels req %d -> %d" % (ln[:100], fname, mb, frac, ms, bc / ms * 1e-6, panels, MF.col_panels), flush=True)
             MF.close()
     del dx, dy
     torch.cuda.empty_cache()
