@@ -4,7 +4,7 @@
 // L2 (two 63 MB halves) cannot hold it, the kernel reads 5.5 GB from DRAM for 3.4 GB of compulsory bytes and runs at
 // 1.04 ms, against 0.81 ms for the same shard shape with a 10 MB band.  Splitting the columns into P ranges of <= 44 MB of
 // x each and running one product per range (y += A_p x, ascending p) keeps every range's x resident; the price is one
-// read-modify-write of y per extra panel (16 bytes per row) -- worth it from ~24 non-zeros per row.
+// read-modify-write of y per extra panel (16 bytes per row) and one more launch.
 //
 // The split happens once, on the GPU, at create time: per row and panel a count, a scan per panel, a scatter that keeps
 // the order of a row's entries; each panel becomes an ordinary sub-handle (CSR / SELL-C-sigma / AUTO, picked per panel).
@@ -75,17 +75,19 @@ __global__ void panel_fill_kernel(const int32_t * __restrict__ row_ptr, const in
 	}
 }
 
-// 0 = auto: panels when the band is larger than 64 MB and rows are long enough to pay for the y read-modify-write
+// 0 = auto.  Measured (profiles/r01p_sweep_col_panels.txt): two panels win for every band from 80 to 148 MB (-14 % to
+// -21 % at 60 nnz / row, -18 % at 5 nnz / row with CSR, +-0 with SELL) and three or four panels are always slower than two
+// (each extra panel re-reads and re-writes y and relaunches); a 64 MB band gains 4 % with CSR and loses 10 % with SELL.
 int panels_auto_count(const b200spmv * h, int requested)
 {
 	if (requested == 1 || h->nnz == 0 || h->m == 0)
 		return 1;
 	if (requested > 1)
 		return requested > MAX_PANELS ? MAX_PANELS : requested;
-	const double band = 8.0 * (double) (h->col_hi - h->col_lo), avg = (double) h->nnz / (double) h->m;
-	if (band <= 64.0 * 1048576.0 || avg < 24.0)
+	const double band = 8.0 * (double) (h->col_hi - h->col_lo), MB = 1048576.0;
+	if (band <= 72.0 * MB)
 		return 1;
-	int P = (int) ((band + 44.0 * 1048576.0 - 1.0) / (44.0 * 1048576.0));
+	int P = (int) ((band + 88.0 * MB - 1.0) / (88.0 * MB));
 	return P > MAX_PANELS ? MAX_PANELS : (P < 2 ? 2 : P);
 }
 
