@@ -44,7 +44,10 @@ __device__ __forceinline__ double block_sum_range(const double * s_prod, int a, 
 	return tot;
 }
 
-template <int NPT, bool HINT>
+// PLAIN: the product as the harness calls it (y = A x, nothing else): no row map, scale, norm, peer destinations or
+// panel accumulation.  The kernel sits at its 40-register cap (6 CTAs per SM); each of those features measurably slowed
+// the plain product when it was a run-time branch (+5 % in total), so they are compiled out of this instantiation.
+template <int NPT, bool HINT, bool PLAIN>
 __global__ void __launch_bounds__(CSR_THREADS, (NPT <= 4) ? 8 : ((NPT <= 8) ? 6 : ((NPT <= 16) ? 3 : 2)))
 csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict__ col, const double * __restrict__ val,
                 const int2 * __restrict__ tile_info, const double * __restrict__ x,
@@ -84,7 +87,9 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 	const int64_t lim = (base + T < nnz) ? base + T : nnz;
 	const int64_t over = end_own - (base + T);          // > 0: the last owned row leaves the window
 	const bool tail_split = (nrows > 0) && (over > ext_cap);
-	const double scale = out.scale ? *out.scale : 1.0;
+	double scale = 1.0;
+	if constexpr (!PLAIN)
+		scale = out.scale ? *out.scale : 1.0;
 	int rp_pre = 0, rp_pre2 = 0;
 	const int npre = nrows < CSR_THREADS ? nrows : CSR_THREADS;
 	const bool do_ext = (nrows > 0 && over > 0 && !tail_split);
@@ -147,8 +152,12 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 			double sum = 0.0;
 			for (; a < b; a++)
 				sum += s_prod[swz(a)];
-			sum = y_finish(out, rowmap ? rowmap[i] : i, sum, scale);
-			nrm += sum * sum;
+			if constexpr (PLAIN) {
+				out.y[i] = sum;
+			} else {
+				sum = y_finish(out, rowmap ? rowmap[i] : i, sum, scale);
+				nrm += sum * sum;
+			}
 		}
 	} else if (rows_full > 0) {
 		// LPR lanes per row, LPR = largest power of two with rows_full * LPR <= CSR_THREADS (max 32)
@@ -168,8 +177,12 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 			for (int o = lpr >> 1; o > 0; o >>= 1)
 				sum += __shfl_xor_sync(0xffffffffu, sum, o);
 			if (r < rows_full && lane == 0) {
-				sum = y_finish(out, rowmap ? rowmap[R0 + r] : R0 + r, sum, scale);
-				nrm += sum * sum;
+				if constexpr (PLAIN) {
+					out.y[R0 + r] = sum;
+				} else {
+					sum = y_finish(out, rowmap ? rowmap[R0 + r] : R0 + r, sum, scale);
+					nrm += sum * sum;
+				}
 			}
 		}
 	}
@@ -189,6 +202,7 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 	}
 
 	// 7. optional sum of squares of the rows written here (power iteration norm, no atomics)
+	if constexpr (!PLAIN)
 	if (out.norm_partial) {
 		nrm = warp_sum(nrm);
 		__syncthreads();
@@ -264,24 +278,31 @@ int launch_norm_reduce(b200spmv * h, int64_t slots, double * d_out, cudaStream_t
 	return 0;
 }
 
-template <int NPT, bool HINT>
-static int launch_tiles(b200spmv * h, const double * dx, cudaStream_t st, const YOut & out)
+template <int NPT, bool HINT, bool PLAIN>
+static int launch_tiles_impl(b200spmv * h, const double * dx, cudaStream_t st, const YOut & out)
 {
 	const size_t smem = (size_t) (h->tile_nnz + h->ext) * sizeof(double);
 	static bool attr_set = false;
 	if (!attr_set) {
-		CU(cudaFuncSetAttribute(csr_tile_kernel<NPT, HINT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+		CU(cudaFuncSetAttribute(csr_tile_kernel<NPT, HINT, PLAIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
 		attr_set = true;
 	}
 	const int64_t first = h->range_count >= 0 ? h->range_first : 0;
 	const int64_t count = h->range_count >= 0 ? h->range_count : h->ntiles;
 	if (count <= 0)
 		return 0;
-	csr_tile_kernel<NPT, HINT><<<(unsigned) count, CSR_THREADS, smem, st>>>(
+	csr_tile_kernel<NPT, HINT, PLAIN><<<(unsigned) count, CSR_THREADS, smem, st>>>(
 		h->d_rp_plan, h->d_col, h->d_val, reinterpret_cast<const int2 *>(h->d_tile_row), dx,
 		h->d_tile_head, h->d_tile_tail, h->nnz, h->ext, h->compressed ? h->d_rows_nz : nullptr, h->x_frac, first, out);
 	CU_LAUNCH();
 	return 0;
+}
+
+template <int NPT, bool HINT>
+static int launch_tiles(b200spmv * h, const double * dx, cudaStream_t st, const YOut & out)
+{
+	const bool plain = !h->compressed && !out.accum && !out.partial && out.n_peer == 0 && !out.scale && !out.norm_partial;
+	return plain ? launch_tiles_impl<NPT, HINT, true>(h, dx, st, out) : launch_tiles_impl<NPT, HINT, false>(h, dx, st, out);
 }
 
 int launch_csr_spmv(b200spmv * h, const double * dx, double * dy, cudaStream_t st, const b200spmv_launch * l)

@@ -2,8 +2,8 @@
 //
 // Measured (profiles/r01o_ncu_full_c5shard_csr_key_metrics.txt): a config-5 row shard gathers from an 80 MB band of x; the
 // L2 (two 63 MB halves) cannot hold it, the kernel reads 5.5 GB from DRAM for 3.4 GB of compulsory bytes and runs at
-// 1.04 ms, against 0.81 ms for the same shard shape with a 10 MB band.  Splitting the columns into P ranges of <= 44 MB of
-// x each and running one product per range (y += A_p x, ascending p) keeps every range's x resident; the price is one
+// 1.04 ms, against 0.81 ms for the same shard shape with a 10 MB band.  Splitting the columns into P equal ranges
+// and running one product per range (y += A_p x, ascending p) keeps every range's x resident; the price is one
 // read-modify-write of y per extra panel (16 bytes per row) and one more launch.
 //
 // The split happens once, on the GPU, at create time: per row and panel a count, a scan per panel, a scatter that keeps
