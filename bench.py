@@ -152,7 +152,7 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="auto", choices=["auto", "medium_sample", "config1", "g1", "g2", "power"])
     ap.add_argument("--format", default=None, choices=["auto", "csr", "sell"],
-                    help="default: auto at N=1 (both formats built, the faster kept per matrix), csr at N>1")
+                    help="default: auto (both formats built, the faster kept per matrix / per column panel)")
     ap.add_argument("--rows-per-gpu", type=int, default=4194304)
     ap.add_argument("--exchange", default="p2p", choices=["nccl", "p2p", "mc"],
                     help="N>1: p2p = fused unicast peer stores (default; measured fastest at N=8, profiles/r01g_bench_n8*.json), "
@@ -363,7 +363,7 @@ def run_power(args):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
     stream = torch.cuda.current_stream().cuda_stream
-    fmt = {"auto": S.AUTO, "csr": S.CSR_ADAPTIVE, "sell": S.SELL_C_SIGMA}[args.format or "csr"]
+    fmt = {"auto": S.AUTO, "csr": S.CSR_ADAPTIVE, "sell": S.SELL_C_SIGMA}[args.format or "auto"]
     peak, peak_src = measured_peak()
     p = H.config5(world, args.rows_per_gpu)
 
@@ -572,7 +572,8 @@ def run_power(args):
             "metric": METRIC, "value": round(gflops, 2), "unit": "GFLOP/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": round(ms_step, 5), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic (reference artificial-matrix-generator restated bit-exactly, seed 14), power iteration from x = 1",
-            "config": {"workload": "power_iteration config5-series: %s" % p.line(), "format": MF.format_name, "rows_per_gpu": args.rows_per_gpu,
+            "config": {"workload": "power_iteration config5-series: %s" % p.line(), "format": MF.format_name, "col_panels": MF.col_panels,
+                       "rows_per_gpu": args.rows_per_gpu,
                        "total_nnz": int(nnz), "shard_rows": [int(b[1] - b[0]) for b in bounds], "exchange": {"mc": "fused: SpMV epilogue stores each y row once to an NVSwitch multicast address (NVLS) mapped over every rank's next-x buffer + NCCL scalar all-reduce",
                                     "p2p": "fused: SpMV epilogue stores y rows into every peer's next-x buffer over NVLink (CUDA IPC) + NCCL scalar all-reduce",
                                     "nccl": "NCCL in-place all-gather of y slots (one broadcast per owner) + scalar all-reduce"}[exchange],

@@ -81,8 +81,8 @@ typedef struct b200spmv_opts {
 	int32_t pin_host_vectors; /* 1: b200spmv_spmv_host page-locks (cudaHostRegister) each distinct x / y buffer it is handed
 	                             the first time it sees it (the harness's aligned_alloc vectors live for the whole run,
 	                             bench_spmv.cpp:598-606) and unregisters them in b200spmv_destroy                    */
-	int32_t col_panels;       /* column panels for an x band larger than L2: 0 = auto (band > 72 MB: max(2, ceil(band / 88 MB))
-	                             panels), 1 = none, 2..8 = that many; each panel is a sub-handle of the
+	int32_t col_panels;       /* column panels for an x band larger than L2: 0 = auto (band > 72 MB at >= 24 nnz / row, > 112 MB
+	                             otherwise: max(2, ceil(band / 88 MB)) panels), 1 = none, 2..8 = that many; each panel is a sub-handle of the
 	                             requested format, launched in ascending column order, y accumulated                  */
 	int32_t reserved[2];
 } b200spmv_opts;

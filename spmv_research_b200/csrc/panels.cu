@@ -75,17 +75,18 @@ __global__ void panel_fill_kernel(const int32_t * __restrict__ row_ptr, const in
 	}
 }
 
-// 0 = auto.  Measured (profiles/r01p_sweep_col_panels.txt): two panels win for every band from 80 to 148 MB (-14 % to
-// -21 % at 60 nnz / row, -18 % at 5 nnz / row with CSR, +-0 with SELL) and three or four panels are always slower than two
-// (each extra panel re-reads and re-writes y and relaunches); a 64 MB band gains 4 % with CSR and loses 10 % with SELL.
+// 0 = auto.  Measured (profiles/r01p_sweep_col_panels.txt, profiles/r01r_panels_borderline.txt): two panels win by 14-21 % on an
+// 80 MB band at 60 nnz / row and by 18 % (CSR) on a 137 MB band at 5 nnz / row, but LOSE 7-24 % on 67-84 MB bands at 5-10 nnz /
+// row (the second launch re-reads and re-writes y: 16 bytes per row against 60-120 bytes of matrix per row); three or four
+// panels are always slower than two.  Hence: long rows split above 72 MB, short rows only when the band is far beyond L2.
 int panels_auto_count(const b200spmv * h, int requested)
 {
 	if (requested == 1 || h->nnz == 0 || h->m == 0)
 		return 1;
 	if (requested > 1)
 		return requested > MAX_PANELS ? MAX_PANELS : requested;
-	const double band = 8.0 * (double) (h->col_hi - h->col_lo), MB = 1048576.0;
-	if (band <= 72.0 * MB)
+	const double band = 8.0 * (double) (h->col_hi - h->col_lo), MB = 1048576.0, avg = (double) h->nnz / (double) h->m;
+	if (band <= 72.0 * MB || (avg < 24.0 && band <= 112.0 * MB))
 		return 1;
 	int P = (int) ((band + 88.0 * MB - 1.0) / (88.0 * MB));
 	return P > MAX_PANELS ? MAX_PANELS : (P < 2 ? 2 : P);
