@@ -152,7 +152,7 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="auto", choices=["auto", "medium_sample", "config1", "g1", "g2", "power"])
     ap.add_argument("--format", default=None, choices=["auto", "csr", "sell"],
-                    help="default: auto (both formats built, the faster kept per matrix / per column panel)")
+                    help="default: auto at N=1 (both formats built, the faster kept per matrix / per column panel), csr at N>1")
     ap.add_argument("--rows-per-gpu", type=int, default=4194304)
     ap.add_argument("--exchange", default="p2p", choices=["nccl", "p2p", "mc"],
                     help="N>1: p2p = fused unicast peer stores (default; measured fastest at N=8, profiles/r01g_bench_n8*.json), "
@@ -363,7 +363,10 @@ def run_power(args):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
     stream = torch.cuda.current_stream().cuda_stream
-    fmt = {"auto": S.AUTO, "csr": S.CSR_ADAPTIVE, "sell": S.SELL_C_SIGMA}[args.format or "auto"]
+    # CSR for the sharded run: the fused exchange stores y rows to the peers from the epilogue, and only the CSR kernel
+    # writes rows in order (coalesced NVLink stores); SELL-C-sigma scatters them through row_order -- measured at N=8:
+    # 2.61 ms / iteration with AUTO -> SELL against 1.10 ms with CSR (profiles/r01s_bench_n8_auto_sell_panels.json)
+    fmt = {"auto": S.AUTO, "csr": S.CSR_ADAPTIVE, "sell": S.SELL_C_SIGMA}[args.format or "csr"]
     peak, peak_src = measured_peak()
     p = H.config5(world, args.rows_per_gpu)
 
