@@ -381,7 +381,11 @@ def run_power(args):
     t_gen = time.time() - t0
     rp_loc = (rp[i_s:i_e + 1] - rp[i_s]).astype(np.int32)
     nnz_loc = int(rp_loc[-1])
-    MF = S.csr_to_format(rp_loc, col, val, i_e - i_s, n, nnz_loc, 0, 0, format=fmt, device=local)
+    # Column panels are off under the fused exchange: the rows become final (and can be stored to the peers) only in the
+    # LAST panel's launch, which squeezes the NVLink traffic into half of the iteration -- measured at N=8: 1.28 ms / iteration
+    # with 2 panels against 1.10 ms without, although the kernels alone are 10 % faster (profiles/r01s_bench_n8_csr_panels.json).
+    fused = world > 1 and args.exchange in ("p2p", "mc")
+    MF = S.csr_to_format(rp_loc, col, val, i_e - i_s, n, nnz_loc, 0, 0, format=fmt, device=local, col_panels=(1 if fused else 0))
     del col, val
 
     exchange = args.exchange if world > 1 else "nccl"

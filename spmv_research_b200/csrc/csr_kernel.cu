@@ -47,13 +47,16 @@ __device__ __forceinline__ double block_sum_range(const double * s_prod, int a, 
 // PLAIN: the product as the harness calls it (y = A x, nothing else): no row map, scale, norm, peer destinations or
 // panel accumulation.  The kernel sits at its 40-register cap (6 CTAs per SM); each of those features measurably slowed
 // the plain product when it was a run-time branch (+5 % in total), so they are compiled out of this instantiation.
-template <int NPT, bool HINT, bool PLAIN>
+// MODE 0 = PLAIN; 1 = EPILOGUE (scale, norm partials, peer destinations: the power-iteration product);
+// 2 = FULL (adds the compressed-row map and the column-panel accumulate / partial modes).
+template <int NPT, bool HINT, int MODE>
 __global__ void __launch_bounds__(CSR_THREADS, (NPT <= 4) ? 8 : ((NPT <= 8) ? 6 : ((NPT <= 16) ? 3 : 2)))
 csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict__ col, const double * __restrict__ val,
                 const int2 * __restrict__ tile_info, const double * __restrict__ x,
                 double * __restrict__ tile_head, double * __restrict__ tile_tail,
                 int64_t nnz, int ext_cap, const int32_t * __restrict__ rowmap, float x_frac, int64_t tile_base, YOut out)
 {
+	constexpr bool PLAIN = (MODE == 0);
 	constexpr int T = CSR_THREADS * NPT;
 	extern __shared__ __align__(16) double s_prod[];      // T + ext_cap products
 	__shared__ double s_red[CSR_THREADS / 32];
@@ -154,6 +157,10 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 				sum += s_prod[swz(a)];
 			if constexpr (PLAIN) {
 				out.y[i] = sum;
+			} else if constexpr (MODE == 1) {
+				sum *= scale;
+				y_store(out, i, sum);
+				nrm += sum * sum;
 			} else {
 				sum = y_finish(out, rowmap ? rowmap[i] : i, sum, scale);
 				nrm += sum * sum;
@@ -179,6 +186,10 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 			if (r < rows_full && lane == 0) {
 				if constexpr (PLAIN) {
 					out.y[R0 + r] = sum;
+				} else if constexpr (MODE == 1) {
+					sum *= scale;
+					y_store(out, R0 + r, sum);
+					nrm += sum * sum;
 				} else {
 					sum = y_finish(out, rowmap ? rowmap[R0 + r] : R0 + r, sum, scale);
 					nrm += sum * sum;
@@ -278,20 +289,20 @@ int launch_norm_reduce(b200spmv * h, int64_t slots, double * d_out, cudaStream_t
 	return 0;
 }
 
-template <int NPT, bool HINT, bool PLAIN>
+template <int NPT, bool HINT, int MODE>
 static int launch_tiles_impl(b200spmv * h, const double * dx, cudaStream_t st, const YOut & out)
 {
 	const size_t smem = (size_t) (h->tile_nnz + h->ext) * sizeof(double);
 	static bool attr_set = false;
 	if (!attr_set) {
-		CU(cudaFuncSetAttribute(csr_tile_kernel<NPT, HINT, PLAIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+		CU(cudaFuncSetAttribute(csr_tile_kernel<NPT, HINT, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
 		attr_set = true;
 	}
 	const int64_t first = h->range_count >= 0 ? h->range_first : 0;
 	const int64_t count = h->range_count >= 0 ? h->range_count : h->ntiles;
 	if (count <= 0)
 		return 0;
-	csr_tile_kernel<NPT, HINT, PLAIN><<<(unsigned) count, CSR_THREADS, smem, st>>>(
+	csr_tile_kernel<NPT, HINT, MODE><<<(unsigned) count, CSR_THREADS, smem, st>>>(
 		h->d_rp_plan, h->d_col, h->d_val, reinterpret_cast<const int2 *>(h->d_tile_row), dx,
 		h->d_tile_head, h->d_tile_tail, h->nnz, h->ext, h->compressed ? h->d_rows_nz : nullptr, h->x_frac, first, out);
 	CU_LAUNCH();
@@ -301,8 +312,11 @@ static int launch_tiles_impl(b200spmv * h, const double * dx, cudaStream_t st, c
 template <int NPT, bool HINT>
 static int launch_tiles(b200spmv * h, const double * dx, cudaStream_t st, const YOut & out)
 {
-	const bool plain = !h->compressed && !out.accum && !out.partial && out.n_peer == 0 && !out.scale && !out.norm_partial;
-	return plain ? launch_tiles_impl<NPT, HINT, true>(h, dx, st, out) : launch_tiles_impl<NPT, HINT, false>(h, dx, st, out);
+	const bool full = h->compressed || out.accum || out.partial;
+	const bool plain = !full && out.n_peer == 0 && !out.scale && !out.norm_partial;
+	if (plain)
+		return launch_tiles_impl<NPT, HINT, 0>(h, dx, st, out);
+	return full ? launch_tiles_impl<NPT, HINT, 2>(h, dx, st, out) : launch_tiles_impl<NPT, HINT, 1>(h, dx, st, out);
 }
 
 int launch_csr_spmv(b200spmv * h, const double * dx, double * dy, cudaStream_t st, const b200spmv_launch * l)
