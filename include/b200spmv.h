@@ -75,8 +75,8 @@ typedef struct b200spmv_opts {
 	                             4 = 16 x 16                                                             */
 	int32_t csr_compress_rows; /* CSR: plan and run on the non-empty rows only, zero the empty ones in a separate balanced
 	                             launch: 0 = when a tile would own more than 2 tiles' worth of rows, 1 = never, 2 = always */
-	int32_t x_l2_mb;          /* L2 budget for x in MiB (default 56): when the referenced band of x is larger, only
-	                             budget / band of its lines are gathered with the evict_last priority          */
+	int32_t x_l2_mb;          /* unused (a fractional L2 evict_last budget for x was measured, <= 2 %, and removed;
+	                             column panels handle x bands larger than L2)                                    */
 	int32_t keep_diag;        /* 1: extract diag(A) at create time (square matrices; needed by b200spmv_pcg)            */
 	int32_t pin_host_vectors; /* 1: b200spmv_spmv_host page-locks (cudaHostRegister) each distinct x / y buffer it is handed
 	                             the first time it sees it (the harness's aligned_alloc vectors live for the whole run,

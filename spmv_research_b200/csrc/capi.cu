@@ -116,9 +116,6 @@ static int compute_col_range(b200spmv * h)
 		B200_FAIL("col_ind out of range: found [%d, %d], n = %lld", got[0], got[1], (long long) h->n);
 	h->col_lo = got[0];
 	h->col_hi = (int64_t) got[1] + 1;
-	// L2 budget for x: the 126 MB L2 of a B200 is two 63 MB halves and a line read from both dies is held twice
-	const double band = 8.0 * (double) (h->col_hi - h->col_lo), budget = (double) h->x_l2_mb * 1048576.0;
-	h->x_frac = (band <= budget) ? 1.0f : (float) (budget / band);
 	return 0;
 }
 
@@ -381,8 +378,6 @@ static int create_common(b200spmv ** out, const int32_t * row_ptr, const int32_t
 	h->sell_variant = o.sell_variant;
 	h->compress_opt = o.csr_compress_rows;
 	h->pin_host = o.pin_host_vectors;
-	h->x_l2_mb = o.x_l2_mb > 0 ? o.x_l2_mb : 56;
-	h->x_frac = 1.0f;
 	int rc = 1;
 	cudaEvent_t e0 = nullptr, e1 = nullptr;
 	do {

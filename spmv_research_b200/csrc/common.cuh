@@ -105,16 +105,9 @@ __device__ __forceinline__ uint64_t make_policy_evict_last()
 	return pol;
 }
 
-// x gathers when the referenced band of x is larger than the L2 can keep: evict_last on ALL of an over-sized working
-// set thrashes (LRU), so only a fraction of the lines (picked by the hardware from the address, quantised to 1/16) gets
-// evict_last and the rest keeps the default priority -- a stable subset of the band stays resident.
-__device__ __forceinline__ uint64_t make_policy_evict_last_frac(float frac)
-{
-	uint64_t pol;
-	asm volatile("createpolicy.fractional.L2::evict_last.L2::evict_unchanged.b64 %0, %1;" : "=l"(pol) : "f"(frac));
-	return pol;
-}
-
+// (A fractional evict_last policy -- createpolicy.fractional with budget / band -- was measured for x bands larger than
+// L2: <= 2 % at any budget, profiles/r01l_sweep_x_l2_budget.txt, and the run-time policy cost the long-row matrices 2-3 %;
+// removed.  Column panels, panels.cu, are what fixes those bands.)
 template <bool HINT>
 __device__ __forceinline__ double ld_x(const double * p, uint64_t pol)
 {
@@ -181,8 +174,6 @@ struct b200spmv {
 	int64_t sell_pad_limit;       // AUTO: a SELL candidate padded beyond this many entries is skipped (0 = no limit)
 	int64_t m, n, nnz;
 	int64_t col_lo, col_hi;       // referenced columns lie in [col_lo, col_hi); x outside is never read
-	int x_l2_mb;                  // L2 budget for the x band, MiB
-	float x_frac;                 // fraction of the x band gathered with L2 evict_last (1 when the band fits the budget)
 	int x_hint;
 	cudaStream_t stream;
 	float convert_ms;

@@ -48,13 +48,13 @@ __device__ __forceinline__ double block_sum_range(const double * s_prod, int a, 
 // panel accumulation.  The kernel sits at its 40-register cap (6 CTAs per SM); each of those features measurably slowed
 // the plain product when it was a run-time branch (+5 % in total), so they are compiled out of this instantiation.
 // MODE 0 = PLAIN; 1 = EPILOGUE (scale, norm partials, peer destinations: the power-iteration product);
-// 2 = FULL (adds the compressed-row map and the column-panel accumulate / partial modes).
+// 2 = FULL (adds the compressed-row map, the column-panel accumulate / partial modes and unit-range launches).
 template <int NPT, bool HINT, int MODE>
 __global__ void __launch_bounds__(CSR_THREADS, (NPT <= 4) ? 8 : ((NPT <= 8) ? 6 : ((NPT <= 16) ? 3 : 2)))
 csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict__ col, const double * __restrict__ val,
                 const int2 * __restrict__ tile_info, const double * __restrict__ x,
                 double * __restrict__ tile_head, double * __restrict__ tile_tail,
-                int64_t nnz, int ext_cap, const int32_t * __restrict__ rowmap, float x_frac, int64_t tile_base, YOut out)
+                int64_t nnz, int ext_cap, const int32_t * __restrict__ rowmap, int64_t tile_base, YOut out)
 {
 	constexpr bool PLAIN = (MODE == 0);
 	constexpr int T = CSR_THREADS * NPT;
@@ -63,9 +63,9 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 	__shared__ int s_rp[CSR_THREADS + 1];                 // window-relative row_ptr of the first 256 owned rows
 
 	const int tid = threadIdx.x;
-	const int64_t tile = tile_base + blockIdx.x;
+	const int64_t tile = (MODE == 2) ? tile_base + blockIdx.x : (int64_t) blockIdx.x;      // unit ranges run the FULL instantiation
 	const int64_t base = tile * (int64_t) T;
-	const uint64_t pol = make_policy_evict_last_frac(x_frac);
+	const uint64_t pol = make_policy_evict_last();
 	const uint64_t pol_stream = make_policy_evict_first();
 
 	// 1. all streaming loads of the window, issued back to back (lane-consecutive, coalesced)
@@ -304,7 +304,7 @@ static int launch_tiles_impl(b200spmv * h, const double * dx, cudaStream_t st, c
 		return 0;
 	csr_tile_kernel<NPT, HINT, MODE><<<(unsigned) count, CSR_THREADS, smem, st>>>(
 		h->d_rp_plan, h->d_col, h->d_val, reinterpret_cast<const int2 *>(h->d_tile_row), dx,
-		h->d_tile_head, h->d_tile_tail, h->nnz, h->ext, h->compressed ? h->d_rows_nz : nullptr, h->x_frac, first, out);
+		h->d_tile_head, h->d_tile_tail, h->nnz, h->ext, h->compressed ? h->d_rows_nz : nullptr, first, out);
 	CU_LAUNCH();
 	return 0;
 }
@@ -312,7 +312,7 @@ static int launch_tiles_impl(b200spmv * h, const double * dx, cudaStream_t st, c
 template <int NPT, bool HINT>
 static int launch_tiles(b200spmv * h, const double * dx, cudaStream_t st, const YOut & out)
 {
-	const bool full = h->compressed || out.accum || out.partial;
+	const bool full = h->compressed || out.accum || out.partial || h->range_count >= 0;
 	const bool plain = !full && out.n_peer == 0 && !out.scale && !out.norm_partial;
 	if (plain)
 		return launch_tiles_impl<NPT, HINT, 0>(h, dx, st, out);

@@ -19,10 +19,10 @@ template <bool HINT, int U, int MINB>
 __global__ void __launch_bounds__(SELL_THREADS, MINB)
 sell_kernel(const int4 * __restrict__ items, int64_t nitems, const int32_t * __restrict__ row_order,
             const int32_t * __restrict__ scol, const double * __restrict__ sval, const double * __restrict__ x,
-            double * __restrict__ partial, int64_t m, int C, float x_frac, YOut out)
+            double * __restrict__ partial, int64_t m, int C, YOut out)
 {
 	__shared__ double s_red[SELL_THREADS / 32];
-	const uint64_t pol = make_policy_evict_last_frac(x_frac);
+	const uint64_t pol = make_policy_evict_last();
 	const uint64_t pol_stream = make_policy_evict_first();
 	const int lane = threadIdx.x & 31;
 	const int64_t it = (int64_t) blockIdx.x * (SELL_THREADS / 32) + (threadIdx.x >> 5);
@@ -157,7 +157,7 @@ int launch_sell_spmv(b200spmv * h, const double * dx, double * dy, cudaStream_t 
 		const int4 * items = reinterpret_cast<const int4 *>(h->d_sell_items) + first;
 		#define SELL_LAUNCH(HINT, U, MINB)                                                                                          \
 			sell_kernel<HINT, U, MINB><<<(unsigned) ctas, SELL_THREADS, 0, st>>>(items, nit, h->d_row_order, h->d_scol, \
-			                                                                     h->d_sval, dx, h->d_sell_partial, h->m, h->C, h->x_frac, out)
+			                                                                     h->d_sval, dx, h->d_sell_partial, h->m, h->C, out)
 		const bool hint = (h->x_hint == 0);
 		// shape 0: short slices are latency-bound (more resident warps win), wide ones want registers for loads in flight
 		// (measured, profiles/r01f_sweep.txt: 8 x 48 wins below ~32 columns per slice, 8 x 32 above)

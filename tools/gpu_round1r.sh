@@ -15,7 +15,7 @@ for ln in ("14713889 14713889 10 3.3333 normal random 0.6 0 1.9 0.5 14", "184483
     dx = torch.ones(n, dtype=torch.float64, device='cuda'); dy = torch.zeros(m, dtype=torch.float64, device='cuda')
     for fmt, fn in ((S.CSR_ADAPTIVE, 'csr'), (S.SELL_C_SIGMA, 'sell')):
         for mb, pan in ((4000, 1), (56, 1), (56, 2)):
-            MF = S.csr_to_format(rp, col, val, m, n, nnz, format=fmt, x_l2_mb=mb, col_panels=pan)
+            MF = S.csr_to_format(rp, col, val, m, n, nnz, format=fmt, col_panels=pan)
             MF.handle.time_device(dx, dy, 3, 256 << 20)
             ms = float(np.median(MF.handle.time_device(dx, dy, 9, 256 << 20)))
             print(ln[:50], fn, 'x_l2_mb', mb, 'panels', pan, '%.4f ms' % ms, flush=True)

@@ -28,7 +28,7 @@ for ln in LINES:
     for fmt, fname in ((S.CSR_ADAPTIVE, "csr"), (S.SELL_C_SIGMA, "sell")):
         for mb in ((56, 1), (56, 2), (56, 3), (56, 4), (56, 0)) if os.environ.get("SWEEP_PANELS") else [(v, 1) for v in (4000, 112, 84, 64, 56, 48, 36, 24)]:
             mb, panels = mb
-            MF = S.csr_to_format(rp, col, val, m, n, nnz, 0, 0, format=fmt, x_l2_mb=mb, col_panels=panels)
+            MF = S.csr_to_format(rp, col, val, m, n, nnz, 0, 0, format=fmt, col_panels=panels)
             lo, hi = MF.handle.col_range()
             frac = min(1.0, mb * 2 ** 20 / (8.0 * (hi - lo)))
             MF.handle.time_device(dx, dy, 3, 256 << 20)
