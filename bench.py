@@ -383,7 +383,8 @@ def run_power(args):
     nnz_loc = int(rp_loc[-1])
     # Column panels are off under the fused exchange: the rows become final (and can be stored to the peers) only in the
     # LAST panel's launch, which squeezes the NVLink traffic into half of the iteration -- measured at N=8: 1.28 ms / iteration
-    # with 2 panels against 1.10 ms without, although the kernels alone are 10 % faster (profiles/r01s_bench_n8_csr_panels.json).
+    # with 2 panels against 1.10 ms without, although the kernels alone are 10 % faster (profiles/r01s_bench_n8_csr_panels.json;
+    # the two runs were on different boxes with different power caps, see DESIGN.md 7 -- to be re-measured on one box).
     fused = world > 1 and args.exchange in ("p2p", "mc")
     MF = S.csr_to_format(rp_loc, col, val, i_e - i_s, n, nnz_loc, 0, 0, format=fmt, device=local, col_panels=(1 if fused else 0))
     del col, val
