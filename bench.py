@@ -419,11 +419,7 @@ def run_power(args):
     peer_rows = None
     band = (0, n)
     if world > 1 and not args.full_exchange:
-        lo, hi = MF.handle.col_range()
-        t = torch.tensor([-lo, hi], dtype=torch.int64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        band = (int(-t[0].item()), int(t[1].item()))
-        peer_rows = (min(max(band[0] - i_s, 0), i_e - i_s), min(max(band[1] - i_s, 0), i_e - i_s))
+        band, peer_rows = power.exchange_rows(MF.handle.col_range(), bounds, rank)
 
     def local_spmv(cur, slot, scale, norm2, parity):
         peers = ()

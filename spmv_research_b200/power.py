@@ -27,6 +27,26 @@ def shard_bounds(row_ptr, m, nnz, world, partition_fn):
     return b
 
 
+def exchange_rows(col_range, bounds, rank, group=None):
+    """Rows of this rank's shard that some rank reads in the next product: the union over ranks of the shards' referenced
+    column bands [lo, hi) (b200spmv_col_range), intersected with the rows [i_s, i_e) this rank owns, as LOCAL row indices.
+    Returns ((band_lo, band_hi), (local_lo, local_hi)); an empty shard band (lo == hi) does not widen the union."""
+    lo, hi = int(col_range[0]), int(col_range[1])
+    big = 1 << 62
+    t = torch.tensor([-(lo if hi > lo else big), (hi if hi > lo else -big)], dtype=torch.int64)
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dev = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend(group) == "nccl" else torch.device("cpu")
+        t = t.to(dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
+        t = t.cpu()
+    glo, ghi = int(-t[0].item()), int(t[1].item())
+    if ghi <= glo:
+        glo = ghi = 0
+    i_s, i_e = int(bounds[rank][0]), int(bounds[rank][1])
+    rows = i_e - i_s
+    return (glo, ghi), (min(max(glo - i_s, 0), rows), min(max(ghi - i_s, 0), rows))
+
+
 def allgather_rows(vec, bounds, group=None):
     """In-place all-gather with unequal counts: slot p of `vec` is broadcast from rank p."""
     works = []

@@ -34,11 +34,13 @@ def _worker(rank, world, port, q):
         slot.copy_(torch.from_numpy(y))
         norm2.fill_(float(np.sum(y * y)))
 
+    # band-limited exchange: the union of the shards' column bands, as local rows of this rank
+    band, loc = power.exchange_rows((int(col.min()), int(col.max()) + 1) if col.size else (0, 0), bounds, rank)
     it = power.ShardedPowerIteration(p.cols, bounds, rank, world, local_spmv, torch.device("cpu"))
     it.set_start(np.ones(p.cols))
     for _ in range(ITERS):
         it.step()
-    q.put((rank, it.eigenvalue(), it.vector(), bounds.tolist()))
+    q.put((rank, it.eigenvalue(), it.vector(), bounds.tolist(), band, loc))
     dist.destroy_process_group()
 
 
@@ -65,7 +67,11 @@ def test_sharded_power_iteration_matches_serial(world, oracle, native):
         lam = float(np.linalg.norm(y))
         x = y / lam
     want_bounds = oracle.partition(world, rp, p.rows, int(rp[-1])).tolist()
-    for rank, eig, vec, bounds in res:
+    gband = (int(col.min()), int(col.max()) + 1)
+    for rank, eig, vec, bounds, band, loc in res:
         assert bounds == want_bounds
+        i_s, i_e = want_bounds[rank]
+        assert tuple(band) == gband
+        assert tuple(loc) == (min(max(gband[0] - i_s, 0), i_e - i_s), min(max(gband[1] - i_s, 0), i_e - i_s))
         assert abs(eig - lam) <= 1e-9 * lam                 # Rayleigh-type estimate within 1e-9 relative
         assert np.allclose(vec, x, rtol=0, atol=1e-12)
