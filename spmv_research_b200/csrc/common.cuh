@@ -38,7 +38,7 @@ constexpr int SELL_KCH = 128;             // slice columns per work item
 // Blackwell load helpers.
 //  * matrix streams (values / col_ind): read exactly once -> non-coherent loads that do not
 //    allocate in L1 (SASS: LDG.E.NA...CONSTANT) and carry an L2 evict-first policy, so they do
-//    not push x out of the 126 MB L2.  (256-bit variants, LDG.E.NA.EFL2.256, are kept for probes.)
+//    not push x out of the 126 MB L2.
 //  * x gathers: L1-allocating loads with an L2 evict_last cache hint (LDG.E.EL.64.CONSTANT).
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint64_t make_policy_evict_first()
@@ -46,41 +46,6 @@ __device__ __forceinline__ uint64_t make_policy_evict_first()
 	uint64_t pol;
 	asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
 	return pol;
-}
-
-struct i32x8 { int v[8]; };
-struct f64x4 { double v[4]; };
-
-__device__ __forceinline__ i32x8 ld_stream_i32x8(const int32_t * p)
-{
-	i32x8 r;
-	asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-	             : "=r"(r.v[0]), "=r"(r.v[1]), "=r"(r.v[2]), "=r"(r.v[3]), "=r"(r.v[4]), "=r"(r.v[5]), "=r"(r.v[6]), "=r"(r.v[7])
-	             : "l"(p));
-	return r;
-}
-
-__device__ __forceinline__ f64x4 ld_stream_f64x4(const double * p)
-{
-	f64x4 r;
-	asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v4.b64 {%0,%1,%2,%3}, [%4];"
-	             : "=d"(r.v[0]), "=d"(r.v[1]), "=d"(r.v[2]), "=d"(r.v[3])
-	             : "l"(p));
-	return r;
-}
-
-__device__ __forceinline__ double2 ld_stream_f64x2(const double * p, uint64_t pol)
-{
-	double2 r;
-	asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.f64 {%0,%1}, [%2], %3;" : "=d"(r.x), "=d"(r.y) : "l"(p), "l"(pol));
-	return r;
-}
-
-__device__ __forceinline__ int2 ld_stream_i32x2(const int32_t * p, uint64_t pol)
-{
-	int2 r;
-	asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.s32 {%0,%1}, [%2], %3;" : "=r"(r.x), "=r"(r.y) : "l"(p), "l"(pol));
-	return r;
 }
 
 __device__ __forceinline__ double ld_stream_f64(const double * p, uint64_t pol)

@@ -25,13 +25,11 @@
 //    reduction (long rows), whole CTA for split-row partials.
 #include "common.cuh"
 
-__device__ __forceinline__ int swz(int j) { return j; }      // products are stored in nnz order
-
 __device__ __forceinline__ double block_sum_range(const double * s_prod, int a, int b, double * s_red)
 {
 	double acc = 0.0;
 	for (int j = a + (int) threadIdx.x; j < b; j += CSR_THREADS)
-		acc += s_prod[swz(j)];
+		acc += s_prod[j];
 	acc = warp_sum(acc);
 	__syncthreads();
 	if ((threadIdx.x & 31) == 0)
@@ -154,7 +152,7 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 			}
 			double sum = 0.0;
 			for (; a < b; a++)
-				sum += s_prod[swz(a)];
+				sum += s_prod[a];
 			if constexpr (PLAIN) {
 				out.y[i] = sum;
 			} else if constexpr (MODE == 1) {
@@ -179,7 +177,7 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 			if (r < rows_full) {
 				const int a = s_rp[r], b = s_rp[r + 1];
 				for (int j = a + lane; j < b; j += lpr)
-					sum += s_prod[swz(j)];
+					sum += s_prod[j];
 			}
 			for (int o = lpr >> 1; o > 0; o >>= 1)
 				sum += __shfl_xor_sync(0xffffffffu, sum, o);
