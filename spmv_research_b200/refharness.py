@@ -45,6 +45,11 @@ def run(name, args, gpu_kernel, threads=None, extra_env=None, timeout=900):
         env.update(extra_env)
     p = subprocess.run([exe_path(name)] + [str(a) for a in args], env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=timeout)
     out = dict(returncode=p.returncode, stdout=p.stdout, stderr=p.stderr, test_failed=("Test failed" in p.stdout))
+    cg = re.findall(r"k = (\d+)\s+error = (\S+)\s+error_explicit = (\S+)\s+error_best = (\S+)", p.stdout)
+    if cg:
+        out["cg_trace"] = [(int(k), float(e), float(ee), float(eb)) for k, e, ee, eb in cg]
+        mf = re.search(r"^error = (\S+)", p.stdout, re.M)
+        out["cg_final_error"] = float(mf.group(1)) if mf else None
     mt = re.search(r"time iter: min=([0-9.eE+-]+), median=([0-9.eE+-]+), max=([0-9.eE+-]+)", p.stdout)
     if mt:
         out.update(time_min=float(mt.group(1)), time_median=float(mt.group(2)), time_max=float(mt.group(3)))

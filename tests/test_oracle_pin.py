@@ -132,3 +132,32 @@ def test_csr_vs_reference_plugin(oracle):
         yp = np.full(len(rp) - 1, 1.0)
         R.spmv(x, yp)                                      # OpenMP compute_csr, nnz-balanced threads
         assert np.array_equal(yp, yr), name
+
+
+def test_pcg_vs_reference_cg_harness(oracle, tmp_path):
+    """oracle_pcg pinned against the reference's OWN CG harness (bench.cpp + bench_cg.cpp + K/csr.cpp, compiled unmodified
+    into oracle/_ref/cg_csr_d.exe): same eps, same iteration count, the same ||r_k|| at every iteration (the harness prints
+    4 significant digits; its dot products are OpenMP-reduced, so later iterates agree to rounding noise only) and the same
+    explicit residual at exit.  b = ones as in bench_cg.cpp:512-516 when no _b.mtx file exists."""
+    from spmv_research_b200 import refharness as RH
+    if not RH.available("cg_csr_d.exe"):
+        pytest.skip("oracle/_ref/cg_csr_d.exe not built (needs /root/reference at build time)")
+    for n, per_row, seed, cap in ((3000, 6, 1, 500), (800, 10, 2, 500), (3000, 6, 1, 7)):
+        rp, col, val = M.spd_matrix(n, per_row, seed)
+        path = str(tmp_path / ("spd_%d_%d.mtx" % (n, seed)))
+        RH.write_matrix_market(path, rp, col, val, n)
+        r = RH.run("cg_csr_d.exe", [path], gpu_kernel=False, threads=2, extra_env={"CG_MAX_NUM_ITERS": str(cap)})
+        assert r["returncode"] == 0, r["stderr"][-1500:]
+        trace = r["cg_trace"]
+        x, info = oracle.pcg(rp, col, val, np.ones(n), cap)
+        # the harness prints one line per iteration it EXECUTES (k = 0 .. iterations - 1)
+        assert len(trace) == info["iterations"], (len(trace), info)
+        # replay the oracle with growing caps to read its ||r_k|| sequence: `err` is evaluated at the top of an iteration
+        # (bench_cg.cpp:213-218), so a run capped at k + 1 iterations leaves err = ||r_k||, the value the harness printed at k
+        for k, err, _, _ in trace[:12]:
+            if k + 1 > info["iterations"]:
+                break
+            _, ik = oracle.pcg(rp, col, val, np.ones(n), k + 1)
+            assert ik["iterations"] == k + 1
+            assert abs(ik["err"] - err) <= 2e-3 * err + 1e-300, (k, ik["err"], err)
+        assert abs(info["err_explicit"] - r["cg_final_error"]) <= 0.05 * r["cg_final_error"] + 1e-13 * np.sqrt(n)
