@@ -66,3 +66,23 @@ def test_device_pcg_error_paths(native):
     with pytest.raises(S.B200Error, match="zero in diagonal"):
         MF.handle.pcg(np.ones(2), 10)
     MF.close()
+
+
+@pytest.mark.gpu
+def test_reference_cg_harness_drives_the_plugin(native, oracle, tmp_path):
+    """The reference's unmodified CG harness (bench.cpp + bench_cg.cpp) linked with host/b200_plugin.cpp: its
+    preconditioned_cg() calls MF->spmv with a different x every iteration, so the plugin runs with B200SPMV_TRANSFER=always
+    (the reference's own GPU plugins cache x and fail here).  Same iteration count as the oracle (+- 2), converged."""
+    from spmv_research_b200 import refharness as RH
+    if not RH.available("cg_b200_d.exe"):
+        pytest.skip("oracle/_ref/cg_b200_d.exe not built (needs /root/reference at build time)")
+    n = 3000
+    rp, col, val = M.spd_matrix(n, 6, 1)
+    path = str(tmp_path / "spd_3000.mtx")
+    RH.write_matrix_market(path, rp, col, val, n)
+    r = RH.run("cg_b200_d.exe", [path], gpu_kernel=True, threads=2,
+               extra_env={"CG_MAX_NUM_ITERS": "500", "B200SPMV_TRANSFER": "always", "B200SPMV_PIN": "0"})
+    assert r["returncode"] == 0, (r["stdout"][-1500:], r["stderr"][-1500:])
+    _, info = oracle.pcg(rp, col, val, np.ones(n), 500)
+    assert abs(len(r["cg_trace"]) - info["iterations"]) <= 2, (len(r["cg_trace"]), info)
+    assert r["cg_final_error"] is not None and r["cg_final_error"] <= 1e-12 * np.sqrt(n)
