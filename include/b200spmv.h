@@ -186,6 +186,17 @@ typedef struct b200spmv_pcg_result {
 } b200spmv_pcg_result;
 int b200spmv_pcg(b200spmv_t * h, const double * b_host, double * x_host, int64_t max_iterations, b200spmv_pcg_result * result);
 
+/* Jacobi-preconditioned BiCGSTAB entirely on the device: the reference harness's preconditioned_bicgstab()
+ * (benchmark_code/BENCH/src/bench_bicg.cpp:150-456).  Like the reference it has NO stop test (:333-334 are commented out):
+ * exactly max_iterations iterations; the returned x is x_best, the iterate with the smallest explicit residual seen at the
+ * checkpoints (every 100 iterations) and at the end -- so, as in the reference, a cap far beyond convergence can return an
+ * older iterate (or x0) once the recurrence degenerates to 0/0.  Two products per iteration, no host synchronisation
+ * between checkpoints.  trace_host: NULL, or max_iterations + 1 doubles receiving ||r_k|| (recurrence) for k = 0 ..
+ * max_iterations (the harness's "k = .. error = .." line, :343).  result: iterations = max_iterations, restarts = 0,
+ * err = ||r_k|| after the last iteration, converged = (err_best < eps).  Needs keep_diag = 1. */
+int b200spmv_bicgstab(b200spmv_t * h, const double * b_host, double * x_host, int64_t max_iterations, double * trace_host,
+                      b200spmv_pcg_result * result);
+
 const char * b200spmv_last_error(void);
 const char * b200spmv_version(void);
 

@@ -47,6 +47,8 @@ def lib():
         L.oracle_adaptive_rowblocks.restype = C.c_int64
         L.oracle_pcg.argtypes = [_i32p, _i32p, _f64p, C.c_int64, _f64p, _f64p, C.c_int64, _f64p]
         L.oracle_pcg.restype = C.c_int
+        L.oracle_bicgstab.argtypes = [_i32p, _i32p, _f64p, C.c_int64, _f64p, _f64p, C.c_int64, _f64p, _f64p]
+        L.oracle_bicgstab.restype = C.c_int
         L.oracle_fnv1a64.argtypes = [C.c_void_p, C.c_int64]
         L.oracle_fnv1a64.restype = C.c_uint64
         _lib = L
@@ -159,6 +161,23 @@ def pcg(row_ptr, col_ind, val, b, max_iterations):
     if rc:
         raise MemoryError("oracle_pcg")
     return x[:m], dict(iterations=int(out[0]), err=out[1], err_explicit=out[2], err_best=out[3], eps=out[4])
+
+
+def bicgstab(row_ptr, col_ind, val, b, max_iterations):
+    """Serial restatement of the reference's preconditioned_bicgstab (bench_bicg.cpp:150-456): (x_best, info dict).
+    No stop test, like the reference: exactly max_iterations iterations; info["trace"][k] = ||r_k|| at the top of iteration k."""
+    m = len(row_ptr) - 1
+    x = np.zeros(max(m, 1))
+    out = np.zeros(5)
+    trace = np.zeros(max(int(max_iterations), 1))
+    rc = lib().oracle_bicgstab(row_ptr, _pad1(col_ind, np.int32), _pad1(val, np.float64), m, np.ascontiguousarray(b, np.float64), x,
+                               int(max_iterations), trace, out)
+    if rc == 1:
+        raise ValueError("bad K, zero in diagonal")
+    if rc:
+        raise MemoryError("oracle_bicgstab")
+    return x[:m], dict(iterations=int(out[0]), err=out[1], err_explicit=out[2], err_best=out[3], eps=out[4],
+                       trace=trace[:int(max_iterations)])
 
 
 def fnv1a64(a):

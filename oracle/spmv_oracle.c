@@ -480,3 +480,106 @@ int oracle_pcg(const int32_t *rp, const int32_t *ci, const double *v, int64_t m,
 	free(mem);
 	return 0;
 }
+
+/* Jacobi-preconditioned BiCGSTAB, serial restatement of preconditioned_bicgstab()
+ * (benchmark_code/BENCH/src/bench_bicg.cpp:150-456).  Like the reference it has NO stop test (the "if (err < eps) break" is
+ * commented out at :333-334): it runs max_iterations iterations, keeps x_best = the iterate with the smallest explicit
+ * residual seen at the checkpoints (every 100 iterations, :307-331) and at the end (:427-446), and returns x_best.
+ * trace (nullable, max_iterations doubles) receives ||r_k|| at the top of iteration k (the "k = .. error = .." line, :343).
+ * out[0] iterations, out[1] ||r|| at the top of the last iteration, out[2] last explicit residual, out[3] err_best, out[4] eps.
+ * Returns 1 on "bad K, zero in diagonal" (:209-210). */
+int oracle_bicgstab(const int32_t *rp, const int32_t *ci, const double *v, int64_t m, const double *b, double *x_out,
+                    int64_t max_iterations, double *trace, double *out)
+{
+	double *mem = (double *)calloc((size_t)(12 * m + 8), sizeof(double));
+	if (!mem)
+		return 2;
+	double *r0 = mem, *rk = mem + m, *rke = mem + 2 * m, *pk = mem + 3 * m, *z = mem + 4 * m, *h = mem + 5 * m, *s = mem + 6 * m,
+	       *vv = mem + 7 * m, *buf = mem + 8 * m, *K = mem + 9 * m, *xk = mem + 10 * m, *xb = mem + 11 * m;
+	for (int64_t i = 0; i < m; i++) {
+		K[i] = 0;
+		for (int64_t j = rp[i]; j < rp[i + 1]; j++)
+			if (ci[j] == i) {
+				K[i] = v[j];
+				break;
+			}
+		if (K[i] == 0) {
+			free(mem);
+			return 1;
+		}
+	}
+	o_spmv(rp, ci, v, xk, buf, m);                              /* :218-250 */
+	for (int64_t i = 0; i < m; i++) {
+		rk[i] = b[i] + -1 * buf[i];
+		r0[i] = rk[i];
+		pk[i] = rk[i];
+	}
+	double s_pk_p = o_dot(r0, rk, m), s_a = 0;
+	double err = sqrt(o_dot(rk, rk, m));
+	const double bn = sqrt(o_dot(b, b, m));
+	const double eps = 1.0e-15 * bn;
+	double err_explicit = err, err_best = err;
+	int64_t k = 0;
+	const int64_t restart_k = 100;
+	while (k < max_iterations) {
+		if ((k > 0) && !(k % restart_k)) {                      /* :307-331 */
+			o_spmv(rp, ci, v, xk, buf, m);
+			for (int64_t i = 0; i < m; i++)
+				rke[i] = b[i] + -1 * buf[i];
+			err_explicit = sqrt(o_dot(rke, rke, m));
+			if (err_explicit < err_best) {
+				memcpy(xb, xk, (size_t)m * sizeof(double));
+				err_best = err_explicit;
+			}
+		}
+		err = sqrt(o_dot(rk, rk, m));                           /* :333-341 */
+		if (trace)
+			trace[k] = err;
+		double *y = buf;                                        /* y = pk / K, v = A y   (:349-361) */
+		for (int64_t i = 0; i < m; i++)
+			y[i] = pk[i] / K[i];
+		o_spmv(rp, ci, v, y, vv, m);
+		s_a = s_pk_p / o_dot(r0, vv, m);                        /* :368-386 */
+		for (int64_t i = 0; i < m; i++)
+			h[i] = xk[i] + s_a * y[i];
+		for (int64_t i = 0; i < m; i++)
+			s[i] = rk[i] + -s_a * vv[i];
+		for (int64_t i = 0; i < m; i++)
+			z[i] = s[i] / K[i];
+		double *t = buf;                                        /* t = A z   (:389-392) */
+		o_spmv(rp, ci, v, z, t, m);
+		double p1 = 0, p2 = 0;                                  /* :399-416 */
+		for (int64_t i = 0; i < m; i++) {
+			const double v1 = t[i] / K[i], v2 = s[i] / K[i];
+			p1 += v1 * v2;
+			p2 += v1 * v1;
+		}
+		const double s_w = p1 / p2;
+		for (int64_t i = 0; i < m; i++)                         /* :418-422 */
+			rk[i] = s[i] + -s_w * t[i];
+		for (int64_t i = 0; i < m; i++)
+			xk[i] = h[i] + s_w * z[i];
+		const double s_pk = o_dot(r0, rk, m);                   /* :426-437 */
+		const double s_b = (s_pk / s_pk_p) * (s_a / s_w);
+		for (int64_t i = 0; i < m; i++)
+			pk[i] = rk[i] + s_b * (pk[i] - s_w * vv[i]);
+		s_pk_p = s_pk;
+		k++;
+	}
+	o_spmv(rp, ci, v, xk, buf, m);                              /* :427-446 */
+	for (int64_t i = 0; i < m; i++)
+		rke[i] = b[i] + -1 * buf[i];
+	err_explicit = sqrt(o_dot(rke, rke, m));
+	if (err_explicit < err_best) {
+		memcpy(xb, xk, (size_t)m * sizeof(double));
+		err_best = err_explicit;
+	}
+	memcpy(x_out, xb, (size_t)m * sizeof(double));
+	out[0] = (double)k;
+	out[1] = err;
+	out[2] = err_explicit;
+	out[3] = err_best;
+	out[4] = eps;
+	free(mem);
+	return 0;
+}

@@ -84,6 +84,7 @@ def lib():
         "b200spmv_ipc_close": (C.c_int, [vp]),
         "b200spmv_time_device": (C.c_int, [vp, vp, vp, i32, i64, vp]),
         "b200spmv_pcg": (C.c_int, [vp, vp, vp, i64, C.POINTER(PcgResult)]),
+        "b200spmv_bicgstab": (C.c_int, [vp, vp, vp, i64, vp, C.POINTER(PcgResult)]),
         "b200spmv_last_error": (C.c_char_p, []),
         "b200spmv_version": (C.c_char_p, []),
     }
@@ -202,6 +203,20 @@ class Handle:
         r = PcgResult()
         check(lib().b200spmv_pcg(self._h, _ptr(b), _ptr(x), int(max_iterations), C.byref(r)))
         return x, {k: getattr(r, k) for k, _ in PcgResult._fields_ if k != "pad_"}
+
+    def bicgstab(self, b, max_iterations, trace=False):
+        """Jacobi-preconditioned BiCGSTAB of the reference harness (bench_bicg.cpp:150-456) on the device: exactly
+        max_iterations iterations (the reference has no stop test); returns (x_best, result dict [+ "trace": ||r_k||])."""
+        b = np.ascontiguousarray(b, np.float64)
+        assert b.size >= self.m
+        x = np.zeros(self.m)
+        r = PcgResult()
+        tr = np.zeros(int(max_iterations) + 1) if trace else None
+        check(lib().b200spmv_bicgstab(self._h, _ptr(b), _ptr(x), int(max_iterations), _ptr(tr) if trace else None, C.byref(r)))
+        out = {k: getattr(r, k) for k, _ in PcgResult._fields_ if k != "pad_"}
+        if trace:
+            out["trace"] = tr
+        return x, out
 
     def time_device(self, dx, dy, iters, flush_bytes=0):
         ms = np.zeros(iters, np.float32)

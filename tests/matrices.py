@@ -76,3 +76,31 @@ def spd_matrix(n, per_row, seed, dominance=1.05):
     S = (S + sp.diags(d)).tocsr()
     S.sort_indices()
     return S.indptr.astype(np.int32), S.indices.astype(np.int32), S.data.astype(np.float64)
+
+
+def dd_matrix(n, per_row, seed, dominance=1.05):
+    """NONsymmetric, strictly row-diagonally dominant CSR (int32 / f64, sorted columns, every diagonal entry present):
+    the kind of system the reference's BiCGSTAB harness is for."""
+    import scipy.sparse as sp
+    rng = np.random.default_rng(seed)
+    nnz = n * per_row
+    B = sp.coo_matrix((rng.uniform(-1.0, 1.0, nnz), (rng.integers(0, n, nnz), rng.integers(0, n, nnz))), shape=(n, n)).tocsr()
+    B.setdiag(0)
+    B.eliminate_zeros()
+    d = dominance * np.asarray(abs(B).sum(axis=1)).ravel() + 0.1
+    S = (B + sp.diags(d)).tocsr()
+    S.sort_indices()
+    return S.indptr.astype(np.int32), S.indices.astype(np.int32), S.data.astype(np.float64)
+
+
+def convdiff_matrix(nx, c=0.4):
+    """2-D convection-diffusion 5-point stencil on an nx x nx grid (nonsymmetric for c != 0): diag 4, west -1-c, east -1+c,
+    south -1-c, north -1+c.  BiCGSTAB needs a few hundred iterations on it, which exercises the every-100 checkpoints."""
+    import scipy.sparse as sp
+    n = nx * nx
+    T = sp.diags([(-1.0 - c) * np.ones(nx - 1), 4.0 * np.ones(nx), (-1.0 + c) * np.ones(nx - 1)], [-1, 0, 1])
+    E = sp.diags([(-1.0 - c) * np.ones(nx - 1), (-1.0 + c) * np.ones(nx - 1)], [-1, 1])
+    S = (sp.kron(sp.identity(nx), T) + sp.kron(E, sp.identity(nx))).tocsr()
+    S.sort_indices()
+    assert S.shape == (n, n)
+    return S.indptr.astype(np.int32), S.indices.astype(np.int32), S.data.astype(np.float64)

@@ -161,3 +161,30 @@ def test_pcg_vs_reference_cg_harness(oracle, tmp_path):
             assert ik["iterations"] == k + 1
             assert abs(ik["err"] - err) <= 2e-3 * err + 1e-300, (k, ik["err"], err)
         assert abs(info["err_explicit"] - r["cg_final_error"]) <= 0.05 * r["cg_final_error"] + 1e-13 * np.sqrt(n)
+
+
+def test_bicgstab_vs_reference_bicg_harness(oracle, tmp_path):
+    """oracle_bicgstab pinned against the reference's OWN BiCGSTAB harness (bench.cpp + bench_bicg.cpp + K/csr.cpp, compiled
+    unmodified into oracle/_ref/bicg_csr_d.exe): it runs exactly CG_MAX_NUM_ITERS iterations (no stop test), prints ||r_k|| at
+    the top of every iteration (4 significant digits) and the explicit residual of the returned x_best at exit."""
+    from spmv_research_b200 import refharness as RH
+    if not RH.available("bicg_csr_d.exe"):
+        pytest.skip("oracle/_ref/bicg_csr_d.exe not built (needs /root/reference at build time)")
+    cases = (("dd", M.dd_matrix(3000, 6, 1), 3000, 40), ("lap", M.convdiff_matrix(60, 0.0), 3600, 230),
+             ("cd", M.convdiff_matrix(60, 0.05), 3600, 7))
+    for tag, (rp, col, val), n, cap in cases:
+        path = str(tmp_path / ("bicg_%s.mtx" % tag))
+        RH.write_matrix_market(path, rp, col, val, n)
+        r = RH.run("bicg_csr_d.exe", [path], gpu_kernel=False, threads=2, extra_env={"CG_MAX_NUM_ITERS": str(cap)})
+        assert r["returncode"] == 0, r["stderr"][-1500:]
+        trace = r["cg_trace"]
+        x, info = oracle.bicgstab(rp, col, val, np.ones(n), cap)
+        assert len(trace) == cap == info["iterations"]
+        for k, err, _, _ in trace[:25]:
+            assert abs(info["trace"][k] - err) <= 2e-3 * err + 1e-300, (tag, k, info["trace"][k], err)
+        # checkpoints (k = 100, 200): the harness prints error_explicit / error_best from then on
+        if cap > 200:
+            assert trace[-1][3] < trace[0][3]
+            assert abs(np.log10(trace[-1][3] / info["err_best"])) < 1.0 or info["err_best"] <= trace[-1][3]
+        # the harness's closing "error =" is ||b - A x_best||; the oracle's err_best is the same quantity
+        assert abs(info["err_best"] - r["cg_final_error"]) <= 0.25 * r["cg_final_error"] + 1e-13 * np.sqrt(n), (tag, info, r["cg_final_error"])
