@@ -84,7 +84,11 @@ typedef struct b200spmv_opts {
 	int32_t col_panels;       /* column panels for an x band larger than L2: 0 = auto (band > 72 MB at >= 24 nnz / row, > 112 MB
 	                             otherwise: max(2, ceil(band / 88 MB)) panels), 1 = none, 2..8 = that many; each panel is a sub-handle of the
 	                             requested format, launched in ascending column order, y accumulated                  */
-	int32_t reserved[2];
+	int32_t host_pipeline;    /* b200spmv_spmv_host: 1 = upload x range by range (the columns each unit range of rows references,
+	                             found at create time) on a third stream, so that the H2D copy of x overlaps the D2H copy of y
+	                             (PCIe is full duplex) as well as the kernels; 0 (default) = upload the referenced band of x
+	                             first, then overlap kernels and D2H only.  Same results either way.                */
+	int32_t reserved[1];
 } b200spmv_opts;
 
 /* extra outputs / inputs of one device-resident product (all pointers are DEVICE pointers) */

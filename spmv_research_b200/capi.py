@@ -27,7 +27,7 @@ class B200Error(RuntimeError):
 
 class Opts(C.Structure):
     _fields_ = [("format", C.c_int32), ("device", C.c_int32), ("sell_C", C.c_int32), ("sell_sigma", C.c_int32),
-                ("csr_nnz_per_thread", C.c_int32), ("csr_ext", C.c_int32), ("x_hint", C.c_int32), ("sell_sigma_alt", C.c_int32), ("sell_variant", C.c_int32), ("csr_compress_rows", C.c_int32), ("x_l2_mb", C.c_int32), ("keep_diag", C.c_int32), ("pin_host_vectors", C.c_int32), ("col_panels", C.c_int32), ("reserved", C.c_int32 * 2)]
+                ("csr_nnz_per_thread", C.c_int32), ("csr_ext", C.c_int32), ("x_hint", C.c_int32), ("sell_sigma_alt", C.c_int32), ("sell_variant", C.c_int32), ("csr_compress_rows", C.c_int32), ("x_l2_mb", C.c_int32), ("keep_diag", C.c_int32), ("pin_host_vectors", C.c_int32), ("col_panels", C.c_int32), ("host_pipeline", C.c_int32), ("reserved", C.c_int32 * 1)]
 
 
 class Launch(C.Structure):

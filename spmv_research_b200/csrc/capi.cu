@@ -119,6 +119,64 @@ static int compute_col_range(b200spmv * h)
 	return 0;
 }
 
+// host_pipeline: column range of each block of blk_rows consecutive rows (one CTA per block), so that the host entry point
+// knows which part of x a unit range of rows needs.  lo_hi[2 b] = smallest, lo_hi[2 b + 1] = largest column (lo > hi: none).
+__global__ void __launch_bounds__(256)
+block_col_range_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict__ col, int64_t m, int64_t blk_rows, int * __restrict__ lo_hi)
+{
+	__shared__ int s_lo[8], s_hi[8];
+	const int64_t r0 = (int64_t) blockIdx.x * blk_rows, r1 = r0 + blk_rows < m ? r0 + blk_rows : m;
+	int lo = 0x7fffffff, hi = -1;
+	if (r0 < m)
+		for (int64_t j = (int64_t) row_ptr[r0] + threadIdx.x; j < row_ptr[r1]; j += 256) {
+			const int c = col[j];
+			lo = c < lo ? c : lo;
+			hi = c > hi ? c : hi;
+		}
+	for (int o = 16; o > 0; o >>= 1) {
+		const int l2 = __shfl_xor_sync(0xffffffffu, lo, o), h2 = __shfl_xor_sync(0xffffffffu, hi, o);
+		lo = l2 < lo ? l2 : lo;
+		hi = h2 > hi ? h2 : hi;
+	}
+	if ((threadIdx.x & 31) == 0) {
+		s_lo[threadIdx.x >> 5] = lo;
+		s_hi[threadIdx.x >> 5] = hi;
+	}
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		for (int w = 1; w < 8; w++) {
+			lo = s_lo[w] < lo ? s_lo[w] : lo;
+			hi = s_hi[w] > hi ? s_hi[w] : hi;
+		}
+		lo_hi[2 * blockIdx.x] = lo;
+		lo_hi[2 * blockIdx.x + 1] = hi;
+	}
+}
+
+static int compute_block_col_ranges(b200spmv * h)
+{
+	const int NB = 256;
+	h->blk_rows = 0;
+	if (!h->pipeline || h->m < 262144 || h->nnz == 0)
+		return 0;
+	const int64_t blk_rows = (h->m + NB - 1) / NB;
+	const int nb = (int) ((h->m + blk_rows - 1) / blk_rows);
+	int * d = nullptr;
+	int got[2 * NB];
+	CU(cudaMalloc(&d, 2 * NB * sizeof(int)));
+	block_col_range_kernel<<<nb, 256, 0, h->stream>>>(h->d_row_ptr, h->d_col, h->m, blk_rows, d);
+	CU_LAUNCH();
+	CU(cudaMemcpyAsync(got, d, 2 * nb * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+	CU(cudaStreamSynchronize(h->stream));
+	CU(cudaFree(d));
+	for (int b = 0; b < NB; b++) {
+		h->blk_lo[b] = b < nb ? got[2 * b] : 0x7fffffff;
+		h->blk_hi[b] = b < nb ? got[2 * b + 1] : -1;
+	}
+	h->blk_rows = blk_rows;
+	return 0;
+}
+
 __global__ void rebase_row_ptr_kernel(const int32_t * __restrict__ in, int32_t * __restrict__ out, int64_t m1)
 {
 	const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
@@ -318,6 +376,26 @@ static int plan_chunks(b200spmv * h)
 	for (int c = 0; c < NCH; c++)
 		CU(cudaEventCreateWithFlags(&h->chunk_ev[c], cudaEventDisableTiming));
 	h->nchunks = NCH;
+	if (h->pipeline && h->blk_rows > 0) {
+		// columns referenced by the rows of each unit range (SELL ranges end on sort-window boundaries, so a range
+		// holds the same set of rows before and after sorting): union of the row blocks it touches
+		for (int c = 0; c < NCH; c++) {
+			int lo = 0x7fffffff, hi = -1;
+			const int64_t r0 = h->chunk_row[c], r1 = h->chunk_row[c + 1];
+			if (r1 > r0)
+				for (int64_t b = r0 / h->blk_rows; b <= (r1 - 1) / h->blk_rows && b < 256; b++) {
+					lo = h->blk_lo[b] < lo ? h->blk_lo[b] : lo;
+					hi = h->blk_hi[b] > hi ? h->blk_hi[b] : hi;
+				}
+			h->chunk_col_lo[c] = lo <= hi ? lo : 0;
+			h->chunk_col_hi[c] = lo <= hi ? (int64_t) hi + 1 : 0;
+		}
+		CU(cudaStreamCreateWithFlags(&h->up_stream, cudaStreamNonBlocking));
+		for (int c = 0; c < NCH; c++)
+			CU(cudaEventCreateWithFlags(&h->up_ev[c], cudaEventDisableTiming));
+	} else {
+		h->pipeline = 0;
+	}
 	return 0;
 }
 
@@ -331,7 +409,12 @@ static void free_handle(b200spmv * h)
 		cudaHostUnregister(h->pinned[i]);
 	if (h->copy_stream)
 		cudaStreamDestroy(h->copy_stream);
+	if (h->up_stream)
+		cudaStreamDestroy(h->up_stream);
 	for (cudaEvent_t e : h->chunk_ev)
+		if (e)
+			cudaEventDestroy(e);
+	for (cudaEvent_t e : h->up_ev)
 		if (e)
 			cudaEventDestroy(e);
 	void * ptrs[] = { h->d_row_ptr, h->d_col, h->d_val, h->d_tile_row, h->d_split_row, h->d_split_tile, h->d_tile_head, h->d_tile_tail,
@@ -378,6 +461,7 @@ static int create_common(b200spmv ** out, const int32_t * row_ptr, const int32_t
 	h->sell_variant = o.sell_variant;
 	h->compress_opt = o.csr_compress_rows;
 	h->pin_host = o.pin_host_vectors;
+	h->pipeline = o.host_pipeline ? 1 : 0;
 	int rc = 1;
 	cudaEvent_t e0 = nullptr, e1 = nullptr;
 	do {
@@ -409,6 +493,7 @@ static int create_common(b200spmv ** out, const int32_t * row_ptr, const int32_t
 		}
 		if (cudaStreamSynchronize(h->stream) != cudaSuccess) break;
 		if (compute_col_range(h)) goto fail;
+		if (compute_block_col_ranges(h)) goto fail;
 		if (o.keep_diag && pcg_extract_diag(h)) goto fail;
 		int64_t norm_slots;
 		const int P = panels_auto_count(h, o.col_panels);
@@ -418,6 +503,7 @@ static int create_common(b200spmv ** out, const int32_t * row_ptr, const int32_t
 			sub.col_panels = 1;
 			sub.csr_compress_rows = 1;          // every panel launch must pass every row through y_finish
 			sub.keep_diag = 0;
+			sub.host_pipeline = 0;              // the shell's host entry point uploads the band once
 			sub.device = -1;
 			if (panels_split(h, P, &sub)) goto fail;
 			cudaFree(h->d_col);
@@ -594,20 +680,48 @@ extern "C" int b200spmv_spmv_host_ex(b200spmv_t * h, const double * x, double * 
 		CU(cudaMalloc(&h->d_x, (h->n > 0 ? h->n : 1) * sizeof(double)));
 		CU(cudaMalloc(&h->d_y, (h->m > 0 ? h->m : 1) * sizeof(double)));
 		CU(cudaMemsetAsync(h->d_x, 0, (h->n > 0 ? h->n : 1) * sizeof(double), h->stream));
+		if (h->up_stream)
+			CU(cudaStreamSynchronize(h->stream));   // the range-by-range uploads run on another stream
 	}
 	if (!h->x_uploaded)
 		flags &= ~B200SPMV_SKIP_X_UPLOAD;           // nothing to reuse yet
 	h->x_uploaded = 1;
+	// host_pipeline: x is uploaded range by range inside the chunk loop below
+	const bool pipe = h->pipeline && h->up_stream && h->nchunks > 1 && !(flags & (B200SPMV_SKIP_X_UPLOAD | B200SPMV_SKIP_Y_DOWNLOAD));
 	// only the columns the matrix references are read by the kernels: upload that band of x, not all n entries
-	if (!(flags & B200SPMV_SKIP_X_UPLOAD) && h->col_hi > h->col_lo)
+	if (!pipe && !(flags & B200SPMV_SKIP_X_UPLOAD) && h->col_hi > h->col_lo)
 		CU(cudaMemcpyAsync(h->d_x + h->col_lo, x + h->col_lo, (h->col_hi - h->col_lo) * sizeof(double), cudaMemcpyHostToDevice, h->stream));
 	// SELL-C-sigma padding entries are (column 0, 0.0) and are multiplied like real ones (sellcs_format.c:150-158): x[0] is read
-	if (!(flags & B200SPMV_SKIP_X_UPLOAD) && h->format == B200SPMV_SELL_C_SIGMA && h->col_lo > 0 && h->n > 0)
+	// (host_pipeline: always first -- the range that brings column 0 may come after a range whose padding already reads it)
+	if (!(flags & B200SPMV_SKIP_X_UPLOAD) && h->format == B200SPMV_SELL_C_SIGMA && (h->col_lo > 0 || pipe) && h->n > 0)
 		CU(cudaMemcpyAsync(h->d_x, x, sizeof(double), cudaMemcpyHostToDevice, h->stream));
 	if (h->nchunks > 1 && !(flags & B200SPMV_SKIP_Y_DOWNLOAD)) {
 		// the rows of a unit range are final when its kernel ends: their D2H copy runs under the next range's kernel
 		int rc = 0;
+		int64_t up_lo = 0, up_hi = 0;                // columns of x on the device so far (one interval; empty at first)
 		for (int c = 0; c < h->nchunks && !rc; c++) {
+			if (pipe) {
+				// what range c reads and is not there yet; the interval stays contiguous, inside [col_lo, col_hi)
+				const int64_t lo = h->chunk_col_lo[c], hi = h->chunk_col_hi[c];
+				if (hi > lo) {
+					if (up_hi == up_lo) {
+						CU(cudaMemcpyAsync(h->d_x + lo, x + lo, (hi - lo) * sizeof(double), cudaMemcpyHostToDevice, h->up_stream));
+						up_lo = lo;
+						up_hi = hi;
+					} else {
+						if (lo < up_lo) {
+							CU(cudaMemcpyAsync(h->d_x + lo, x + lo, (up_lo - lo) * sizeof(double), cudaMemcpyHostToDevice, h->up_stream));
+							up_lo = lo;
+						}
+						if (hi > up_hi) {
+							CU(cudaMemcpyAsync(h->d_x + up_hi, x + up_hi, (hi - up_hi) * sizeof(double), cudaMemcpyHostToDevice, h->up_stream));
+							up_hi = hi;
+						}
+					}
+				}
+				CU(cudaEventRecord(h->up_ev[c], h->up_stream));
+				CU(cudaStreamWaitEvent(h->stream, h->up_ev[c], 0));
+			}
 			h->range_first = h->chunk_unit[c];
 			h->range_count = h->chunk_unit[c + 1] - h->chunk_unit[c];
 			rc = launch_spmv_any(h, h->d_x, h->d_y, h->stream);

@@ -198,6 +198,13 @@ struct b200spmv {
 	int64_t range_first, range_count;      // range_count < 0: whole matrix (set only around the chunked launches)
 	cudaStream_t copy_stream;
 	cudaEvent_t chunk_ev[4];
+	// host_pipeline: x travels range by range on up_stream (columns [chunk_col_lo, chunk_col_hi) are what range c reads)
+	int pipeline;
+	int64_t blk_rows;             // rows per entry of the column-range table built at create time (0 = no table)
+	int blk_lo[256], blk_hi[256]; // smallest / largest column of each block of blk_rows rows (lo > hi: no entries)
+	int64_t chunk_col_lo[4], chunk_col_hi[4];
+	cudaStream_t up_stream;
+	cudaEvent_t up_ev[4];
 
 	// Column panels (x band larger than L2): this handle is then a shell around npanels sub-handles, one per column
 	// range, launched in turn; sub-handle p > 0 adds to the partial in y, the last one finishes the rows (scale, peers, norm).
