@@ -163,6 +163,8 @@ def parse_args():
     ap.add_argument("--no-nccl-leg", action="store_true", help="N>1: skip the plain-NCCL comparison leg")
     ap.add_argument("--no-graph", action="store_true", help="N>1: time an eager step loop instead of CUDA-graph replays")
     ap.add_argument("--x", default="ones", choices=["ones", "random"])
+    ap.add_argument("--host-pipeline", action="store_true",
+                    help="N=1 e2e leg: opts.host_pipeline = 1 (x uploaded range by range so H2D overlaps D2H; off by default until verified on a B200)")
     ap.add_argument("--line", default=None, help="one generator parameter line to use as the N=1 workload (profiling)")
     return ap.parse_args()
 
@@ -211,7 +213,7 @@ def run_single(args):
         rp, col, val = amg.generate(p)
         t_gen += time.time() - t0
         m, n, nnz = p.rows, p.cols, int(rp[-1])
-        MF = S.csr_to_format(rp, col, val, m, n, nnz, 0, 0, format=fmt)
+        MF = S.csr_to_format(rp, col, val, m, n, nnz, 0, 0, format=fmt, host_pipeline=(1 if args.host_pipeline else 0))
         MFo = [S.csr_to_format(rp, col, val, m, n, nnz, 0, 0, format=f) for f in others]
         x_h = np.ones(n) if args.x == "ones" else np.random.default_rng(14).uniform(-1, 1, n)
         dx = torch.from_numpy(x_h).to(dev)
@@ -315,7 +317,7 @@ def run_single(args):
     e2e = {"value": round(2.0 * tot_nnz / te * 1e-9, 2), "unit": "GFLOP/s", "h2d_bytes_per_step": int(sum(8 * (r["MF"].handle.col_range()[1] - r["MF"].handle.col_range()[0]) for r in mats)),
            "h2d_note": "x is uploaded for the referenced column band [col_lo, col_hi) only (8 n = %d bytes would be the full vectors)" % int(sum(8 * r["n"] for r in mats)),
            "d2h_bytes_per_step": int(sum(8 * r["m"] for r in mats)), "ms_per_step": round(te * 1e3, 4),
-           "call": "Matrix_Format::spmv(x, y) via b200spmv_spmv_host, pinned host x / y"}
+           "call": "Matrix_Format::spmv(x, y) via b200spmv_spmv_host, pinned host x / y" + (", host_pipeline = 1" if args.host_pipeline else "")}
 
     n_csr = sum(1 for r in mats if r["MF"].format == S.CSR_ADAPTIVE)
     traffic, traffic_note = ncu_traffic("csr_tile_kernel" if 2 * n_csr >= len(mats) else "sell_kernel")
