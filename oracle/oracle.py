@@ -49,6 +49,9 @@ def lib():
         L.oracle_pcg.restype = C.c_int
         L.oracle_bicgstab.argtypes = [_i32p, _i32p, _f64p, C.c_int64, _f64p, _f64p, C.c_int64, _f64p, _f64p]
         L.oracle_bicgstab.restype = C.c_int
+        L.oracle_sell_plain_convert.argtypes = [_i32p, _i32p, _f64p, C.c_int64, C.c_int64, C.c_int64, _i32p, C.c_void_p, C.c_void_p]
+        L.oracle_sell_plain_convert.restype = C.c_int64
+        L.oracle_sell_plain_spmv.argtypes = [C.c_int64, C.c_int64, _i32p, _i32p, _f64p, _f64p, _f64p]
         L.oracle_fnv1a64.argtypes = [C.c_void_p, C.c_int64]
         L.oracle_fnv1a64.restype = C.c_uint64
         _lib = L
@@ -180,6 +183,34 @@ def bicgstab(row_ptr, col_ind, val, b, max_iterations):
                        trace=trace[:int(max_iterations)])
 
 
+def sell_plain_convert(row_ptr, col_ind, val, VL, nthreads):
+    """The reference's plain SELL layout (K/sell.cpp:98-192): dict(row_cluster_ptr, ja, a, VL, m).
+    The layout depends on nthreads (padding entries carry the last real column the converting thread saw)."""
+    m = len(row_ptr) - 1
+    S = (m + VL - 1) // VL
+    rcp = np.zeros(S + 1, np.int32)
+    ci, v = _pad1(col_ind, np.int32), _pad1(val, np.float64)
+    total = lib().oracle_sell_plain_convert(row_ptr, ci, v, m, VL, nthreads, rcp, None, None)
+    ja = np.zeros(max(total, 1), np.int32)
+    a = np.zeros(max(total, 1), np.float64)
+    lib().oracle_sell_plain_convert(row_ptr, ci, v, m, VL, nthreads, rcp, ja.ctypes.data, a.ctypes.data)
+    return dict(row_cluster_ptr=rcp, ja=ja[:total], a=a[:total], VL=VL, m=m)
+
+
+def sell_plain_spmv(layout, x):
+    """y of the plain SELL product (fused multiply-adds in ascending k, K/sell.cpp:232-273); S * VL entries, the first m are y."""
+    m, VL = layout["m"], layout["VL"]
+    y = np.zeros(((m + VL - 1) // VL) * VL + 1)
+    lib().oracle_sell_plain_spmv(m, VL, layout["row_cluster_ptr"], _pad1(layout["ja"], np.int32), _pad1(layout["a"], np.float64),
+                                 np.ascontiguousarray(x, np.float64), y)
+    return y[:-1]
+
+
+def set_threads(k):
+    """omp_set_num_threads for every OpenMP library of this process (the oracle and oracle/_ref share libgomp)."""
+    C.CDLL("libgomp.so.1").omp_set_num_threads(int(k))
+
+
 def fnv1a64(a):
     a = np.ascontiguousarray(a)
     return int(lib().oracle_fnv1a64(a.ctypes.data, a.nbytes))
@@ -231,6 +262,40 @@ class RefCSR:
     @property
     def format_name(self):
         return self.L.ref_csr_format_name(self.h).decode()
+
+
+class RefSELL:
+    """The reference's plain SELL plugin (K/sell.cpp) behind its own csr_to_format()/spmv(), plus its layout arrays.
+    Like RefCSR it keeps per-thread state in a file-scope array (tds): one live object at a time."""
+
+    def __init__(self, row_ptr, col_ind, val, n):
+        L = ref("sell")
+        L.ref_sell_create.restype = C.c_void_p
+        L.ref_sell_create.argtypes = [_i32p, _i32p, _f64p, C.c_long, C.c_long, C.c_long]
+        L.ref_sell_spmv.argtypes = [C.c_void_p, _f64p, _f64p]
+        L.ref_sell_vec_len.restype = C.c_long
+        for f in ("ref_sell_num_row_clusters", "ref_sell_nnz_ext"):
+            getattr(L, f).restype = C.c_long
+            getattr(L, f).argtypes = [C.c_void_p]
+        self.L = L
+        self.m = len(row_ptr) - 1
+        self.VL = int(L.ref_sell_vec_len())
+        self.h = L.ref_sell_create(row_ptr, _pad1(col_ind, np.int32), _pad1(val, np.float64), self.m, n, int(row_ptr[-1]))
+        S, total = L.ref_sell_num_row_clusters(self.h), L.ref_sell_nnz_ext(self.h)
+
+        def grab(fn, count, ctype):
+            f = getattr(L, fn)
+            f.restype = C.POINTER(ctype)
+            f.argtypes = [C.c_void_p]
+            return np.ctypeslib.as_array(f(self.h), shape=(max(count, 1),))[:count].copy()
+
+        self.row_cluster_ptr = grab("ref_sell_row_cluster_ptr", S + 1, C.c_int32)
+        self.ja = grab("ref_sell_ja", total, C.c_int32)
+        self.a = grab("ref_sell_a", total, C.c_double)
+
+    def spmv(self, x, y):
+        """y needs ceil(m / VL) * VL entries (whole vectors are stored)."""
+        self.L.ref_sell_spmv(self.h, x, y)
 
 
 def ref_partition(num_workers, sums, N, total):

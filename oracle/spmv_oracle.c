@@ -583,3 +583,69 @@ int oracle_bicgstab(const int32_t *rp, const int32_t *ci, const double *v, int64
 	free(mem);
 	return 0;
 }
+
+/* Plain SELL of the reference (benchmark_code/BENCH/src/spmv_kernels/sell.cpp:98-192): slices
+ * ("row clusters") of VL consecutive rows in their original order (VL = vec_len_default_f64: 4 with AVX2, 8 with AVX-512),
+ * each padded to its longest row and stored column-major (entry k of the slice's rows side by side).  What is peculiar:
+ *   - row_cluster_ptr is already multiplied by VL (:137-143);
+ *   - a padding entry has value 0 and the LAST REAL COLUMN the converting thread has seen (0 at the start of the thread's
+ *     range, :158-185), so the layout depends on the number of threads: the slices are dealt to `nthreads` workers with
+ *     loop_partitioner_balance_prefix_sums over row_cluster_ptr (:155);
+ *   - the product accumulates with fused multiply-adds in ascending k and stores all VL lanes of the last slice, i.e.
+ *     y[m .. S*VL) is written too (:232-273; the harness allocates m + 64).
+ * Pass 1 (ja == NULL): fills rcp[S + 1] and returns nnz_ext.  Pass 2: fills ja / a. */
+int64_t oracle_sell_plain_convert(const int32_t *rp, const int32_t *ci, const double *v, int64_t m, int64_t VL, int64_t nthreads,
+                                  int32_t *rcp, int32_t *ja, double *a)
+{
+	const int64_t S = (m + VL - 1) / VL;
+	int64_t run = 0;
+	for (int64_t s = 0; s < S; s++) {
+		int64_t width = 0;
+		const int64_t k_e = (s + 1) * VL < m ? (s + 1) * VL : m;
+		for (int64_t k = s * VL; k < k_e; k++)
+			if (rp[k + 1] - rp[k] > width)
+				width = rp[k + 1] - rp[k];
+		rcp[s] = (int32_t)run;
+		run += VL * width;
+	}
+	rcp[S] = (int32_t)run;
+	if (!ja)
+		return run;
+	for (int64_t t = 0; t < nthreads; t++) {
+		int64_t ii_s, ii_e;
+		oracle_partition_prefix_sums(nthreads, t, rcp, S, run, &ii_s, &ii_e);
+		int64_t col = 0;
+		for (int64_t ii = ii_s; ii < ii_e; ii++) {
+			const int64_t width = (rcp[ii + 1] - rcp[ii]) / VL;
+			const int64_t i_s = VL * ii;
+			for (int64_t lane = 0; lane < VL; lane++) {
+				const int64_t i = i_s + lane;
+				int64_t k = 0;
+				if (i < m)
+					for (int64_t j = rp[i]; j < rp[i + 1]; j++, k++) {
+						col = ci[j];
+						a[rcp[ii] + k * VL + lane] = v[j];
+						ja[rcp[ii] + k * VL + lane] = (int32_t)col;
+					}
+				for (; k < width; k++) {        /* padding of shorter rows, and of the rows missing in the last slice */
+					a[rcp[ii] + k * VL + lane] = 0;
+					ja[rcp[ii] + k * VL + lane] = (int32_t)col;
+				}
+			}
+		}
+	}
+	return run;
+}
+
+/* y must hold S * VL entries (sell.cpp:266 stores whole vectors). */
+void oracle_sell_plain_spmv(int64_t m, int64_t VL, const int32_t *rcp, const int32_t *ja, const double *a, const double *x, double *y)
+{
+	const int64_t S = (m + VL - 1) / VL;
+	for (int64_t ii = 0; ii < S; ii++)
+		for (int64_t lane = 0; lane < VL; lane++) {
+			double sum = 0;
+			for (int64_t jj = rcp[ii]; jj < rcp[ii + 1]; jj += VL)
+				sum = fma(a[jj + lane], x[ja[jj + lane]], sum);
+			y[VL * ii + lane] = sum;
+		}
+}

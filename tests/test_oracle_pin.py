@@ -188,3 +188,38 @@ def test_bicgstab_vs_reference_bicg_harness(oracle, tmp_path):
             assert abs(np.log10(trace[-1][3] / info["err_best"])) < 1.0 or info["err_best"] <= trace[-1][3]
         # the harness's closing "error =" is ||b - A x_best||; the oracle's err_best is the same quantity
         assert abs(info["err_best"] - r["cg_final_error"]) <= 0.25 * r["cg_final_error"] + 1e-13 * np.sqrt(n), (tag, info, r["cg_final_error"])
+
+
+def test_plain_sell_vs_reference(oracle):
+    """the oracle's restatement of the reference's plain SELL (K/sell.cpp) pinned against that file compiled
+    unmodified (oracle/_ref/libref_sell.so): row_cluster_ptr / ja / a bit for bit -- including the padding entries, which carry
+    the last real column the converting THREAD saw and therefore change with the thread count -- and the fused-multiply-add
+    product bit for bit, tail lanes of the last slice included."""
+    import os
+    if not os.path.exists(os.path.join(os.path.dirname(oracle.__file__), "_ref", "libref_sell.so")):
+        pytest.skip("oracle/_ref/libref_sell.so not built (needs /root/reference at build time)")
+    rng = np.random.default_rng(5)
+    cases = [M.csr_from_lengths(rng.integers(0, 9, 1003), 500, 1),                          # ragged last slice, empty rows
+             M.csr_from_lengths(np.r_[np.zeros(9, np.int64), rng.integers(0, 40, 500)], 2000, 2),   # a thread range starting on empty rows
+             M.csr_from_lengths(np.r_[rng.integers(1, 4, 300), [700], rng.integers(1, 4, 200)], 900, 3),   # one long row
+             M.csr_from_lengths([3], 10, 4)]                                                   # a single row
+    t0 = oracle.max_threads()
+    try:
+        for nt in (1, 2, 3, 5):
+            oracle.set_threads(nt)
+            for rp, col, val in cases:
+                m, n = len(rp) - 1, int(col.max()) + 1 if len(col) else 1
+                R = oracle.RefSELL(rp, col, val, n)
+                O = oracle.sell_plain_convert(rp, col, val, R.VL, nt)
+                assert np.array_equal(O["row_cluster_ptr"], R.row_cluster_ptr)
+                assert np.array_equal(O["ja"], R.ja), (nt, m)
+                assert np.array_equal(O["a"], R.a)
+                x = M.rand_x(n, 7)
+                y_ref = np.full(((m + R.VL - 1) // R.VL) * R.VL + 64, 3.0)
+                R.spmv(x, y_ref)
+                y = oracle.sell_plain_spmv(O, x)
+                assert np.array_equal(y, y_ref[:len(y)]) and np.all(y_ref[len(y):] == 3.0)
+                # against the scalar CSR oracle: same sums up to the fused multiply-add (north-star bound)
+                assert oracle.within_bound(y[:m], oracle.csr_spmv(rp, col, val, x), oracle.row_abs_bound(rp, col, val, x))
+    finally:
+        oracle.set_threads(t0)
