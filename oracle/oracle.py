@@ -51,6 +51,8 @@ def lib():
         L.oracle_bicgstab.restype = C.c_int
         L.oracle_sell_plain_convert.argtypes = [_i32p, _i32p, _f64p, C.c_int64, C.c_int64, C.c_int64, _i32p, C.c_void_p, C.c_void_p]
         L.oracle_sell_plain_convert.restype = C.c_int64
+        L.oracle_sell_sorted_convert.argtypes = [_i32p, _i32p, _f64p, C.c_int64, C.c_int64, C.c_int64, _i32p, _i32p, _i32p, C.c_void_p, C.c_void_p]
+        L.oracle_sell_sorted_convert.restype = C.c_int64
         L.oracle_sell_plain_spmv.argtypes = [C.c_int64, C.c_int64, _i32p, _i32p, _f64p, _f64p, _f64p]
         L.oracle_fnv1a64.argtypes = [C.c_void_p, C.c_int64]
         L.oracle_fnv1a64.restype = C.c_uint64
@@ -197,6 +199,30 @@ def sell_plain_convert(row_ptr, col_ind, val, VL, nthreads):
     return dict(row_cluster_ptr=rcp, ja=ja[:total], a=a[:total], VL=VL, m=m)
 
 
+def sell_sorted_convert(row_ptr, col_ind, val, VL, nthreads):
+    """The reference's per-thread-sorted SELL layout (K/sell_sorted.cpp:125-298): the plain SELL dict plus permutation /
+    rev_permutation (rows sorted by ascending length inside each converting thread's range)."""
+    m = len(row_ptr) - 1
+    S = (m + VL - 1) // VL
+    rcp = np.zeros(S + 1, np.int32)
+    perm, rev = np.zeros(max(m, 1), np.int32), np.zeros(max(m, 1), np.int32)
+    ci, v = _pad1(col_ind, np.int32), _pad1(val, np.float64)
+    total = lib().oracle_sell_sorted_convert(row_ptr, ci, v, m, VL, nthreads, perm, rev, rcp, None, None)
+    ja = np.zeros(max(total, 1), np.int32)
+    a = np.zeros(max(total, 1), np.float64)
+    lib().oracle_sell_sorted_convert(row_ptr, ci, v, m, VL, nthreads, perm, rev, rcp, ja.ctypes.data, a.ctypes.data)
+    return dict(row_cluster_ptr=rcp, ja=ja[:total], a=a[:total], VL=VL, m=m, permutation=perm[:m], rev_permutation=rev[:m])
+
+
+def sell_sorted_spmv(layout, x):
+    """y[rev_permutation[i]] = lane i of the plain product over the reordered layout (K/sell_sorted.cpp:338-419)."""
+    m = layout["m"]
+    ys = sell_plain_spmv(layout, x)
+    y = np.zeros(m)
+    y[layout["rev_permutation"]] = ys[:m]
+    return y
+
+
 def sell_plain_spmv(layout, x):
     """y of the plain SELL product (fused multiply-adds in ascending k, K/sell.cpp:232-273); S * VL entries, the first m are y."""
     m, VL = layout["m"], layout["VL"]
@@ -268,8 +294,13 @@ class RefSELL:
     """The reference's plain SELL plugin (K/sell.cpp) behind its own csr_to_format()/spmv(), plus its layout arrays.
     Like RefCSR it keeps per-thread state in a file-scope array (tds): one live object at a time."""
 
+    LIB, PFX = "sell", "ref_sell_"
+
     def __init__(self, row_ptr, col_ind, val, n):
-        L = ref("sell")
+        L = ref(self.LIB)
+        if self.PFX != "ref_sell_":
+            for f in ("create", "spmv", "vec_len", "num_row_clusters", "nnz_ext", "row_cluster_ptr", "ja", "a"):
+                setattr(L, "ref_sell_" + f, getattr(L, self.PFX + f))
         L.ref_sell_create.restype = C.c_void_p
         L.ref_sell_create.argtypes = [_i32p, _i32p, _f64p, C.c_long, C.c_long, C.c_long]
         L.ref_sell_spmv.argtypes = [C.c_void_p, _f64p, _f64p]
@@ -296,6 +327,19 @@ class RefSELL:
     def spmv(self, x, y):
         """y needs ceil(m / VL) * VL entries (whole vectors are stored)."""
         self.L.ref_sell_spmv(self.h, x, y)
+
+
+class RefSELLSorted(RefSELL):
+    """The reference's per-thread-sorted SELL plugin (K/sell_sorted.cpp); spmv needs a y of m entries."""
+    LIB, PFX = "sell_sorted", "ref_sells_"
+
+    def __init__(self, row_ptr, col_ind, val, n):
+        super().__init__(row_ptr, col_ind, val, n)
+        for fn in ("permutation", "rev_permutation"):
+            f = getattr(self.L, "ref_sells_" + fn)
+            f.restype = C.POINTER(C.c_int)
+            f.argtypes = [C.c_void_p]
+            setattr(self, fn, np.ctypeslib.as_array(f(self.h), shape=(max(self.m, 1),))[:self.m].copy())
 
 
 def ref_partition(num_workers, sums, N, total):

@@ -594,8 +594,7 @@ int oracle_bicgstab(const int32_t *rp, const int32_t *ci, const double *v, int64
  *   - the product accumulates with fused multiply-adds in ascending k and stores all VL lanes of the last slice, i.e.
  *     y[m .. S*VL) is written too (:232-273; the harness allocates m + 64).
  * Pass 1 (ja == NULL): fills rcp[S + 1] and returns nnz_ext.  Pass 2: fills ja / a. */
-int64_t oracle_sell_plain_convert(const int32_t *rp, const int32_t *ci, const double *v, int64_t m, int64_t VL, int64_t nthreads,
-                                  int32_t *rcp, int32_t *ja, double *a)
+static int64_t sell_plain_widths(const int32_t *rp, int64_t m, int64_t VL, int32_t *rcp)
 {
 	const int64_t S = (m + VL - 1) / VL;
 	int64_t run = 0;
@@ -609,31 +608,106 @@ int64_t oracle_sell_plain_convert(const int32_t *rp, const int32_t *ci, const do
 		run += VL * width;
 	}
 	rcp[S] = (int32_t)run;
+	return run;
+}
+
+/* one converting thread's slices [ii_s, ii_e): sell.cpp:158-188 / sell_sorted.cpp:262-290 */
+static void sell_plain_fill(const int32_t *rp, const int32_t *ci, const double *v, int64_t m, int64_t VL, const int32_t *rcp,
+                            int64_t ii_s, int64_t ii_e, int32_t *ja, double *a)
+{
+	int64_t col = 0;
+	for (int64_t ii = ii_s; ii < ii_e; ii++) {
+		const int64_t width = (rcp[ii + 1] - rcp[ii]) / VL;
+		const int64_t i_s = VL * ii;
+		for (int64_t lane = 0; lane < VL; lane++) {
+			const int64_t i = i_s + lane;
+			int64_t k = 0;
+			if (i < m)
+				for (int64_t j = rp[i]; j < rp[i + 1]; j++, k++) {
+					col = ci[j];
+					a[rcp[ii] + k * VL + lane] = v[j];
+					ja[rcp[ii] + k * VL + lane] = (int32_t)col;
+				}
+			for (; k < width; k++) {        /* padding of shorter rows, and of the rows missing in the last slice */
+				a[rcp[ii] + k * VL + lane] = 0;
+				ja[rcp[ii] + k * VL + lane] = (int32_t)col;
+			}
+		}
+	}
+}
+
+int64_t oracle_sell_plain_convert(const int32_t *rp, const int32_t *ci, const double *v, int64_t m, int64_t VL, int64_t nthreads,
+                                  int32_t *rcp, int32_t *ja, double *a)
+{
+	const int64_t S = (m + VL - 1) / VL;
+	const int64_t run = sell_plain_widths(rp, m, VL, rcp);
 	if (!ja)
 		return run;
 	for (int64_t t = 0; t < nthreads; t++) {
 		int64_t ii_s, ii_e;
 		oracle_partition_prefix_sums(nthreads, t, rcp, S, run, &ii_s, &ii_e);
-		int64_t col = 0;
-		for (int64_t ii = ii_s; ii < ii_e; ii++) {
-			const int64_t width = (rcp[ii + 1] - rcp[ii]) / VL;
-			const int64_t i_s = VL * ii;
-			for (int64_t lane = 0; lane < VL; lane++) {
-				const int64_t i = i_s + lane;
-				int64_t k = 0;
-				if (i < m)
-					for (int64_t j = rp[i]; j < rp[i + 1]; j++, k++) {
-						col = ci[j];
-						a[rcp[ii] + k * VL + lane] = v[j];
-						ja[rcp[ii] + k * VL + lane] = (int32_t)col;
-					}
-				for (; k < width; k++) {        /* padding of shorter rows, and of the rows missing in the last slice */
-					a[rcp[ii] + k * VL + lane] = 0;
-					ja[rcp[ii] + k * VL + lane] = (int32_t)col;
-				}
-			}
+		sell_plain_fill(rp, ci, v, m, VL, rcp, ii_s, ii_e, ja, a);
+	}
+	return run;
+}
+
+/* Per-thread-sorted SELL of the reference (K/sell_sorted.cpp:125-298): the slices are dealt to the threads by nnz on the
+ * ORIGINAL row_ptr (:158-175), each thread sorts the rows of its range by ASCENDING length with a stable bucket sort
+ * (:186-191; permutation[i] = new position of row i, rev_permutation its inverse), the matrix is rewritten in that order and
+ * then stored exactly like the plain SELL, with the same thread ranges (:262-290).  The product writes
+ * y[rev_permutation[i]] (:392-395), so per row it is the plain SELL's chain of fused multiply-adds.
+ * Pass 1 (ja == NULL): permutation / rev_permutation / rcp, returns nnz_ext.  Pass 2: ja / a as well. */
+int64_t oracle_sell_sorted_convert(const int32_t *rp, const int32_t *ci, const double *v, int64_t m, int64_t VL, int64_t nthreads,
+                                   int32_t *permutation, int32_t *rev_permutation, int32_t *rcp, int32_t *ja, double *a)
+{
+	const int64_t S = (m + VL - 1) / VL, nnz = rp[m];
+	int32_t *rcp0 = (int32_t *)malloc((size_t)(S + 1) * sizeof(int32_t));
+	int32_t *rp2 = (int32_t *)malloc((size_t)(m + 1) * sizeof(int32_t));
+	int32_t *ci2 = (int32_t *)malloc((size_t)(nnz > 0 ? nnz : 1) * sizeof(int32_t));
+	double *v2 = (double *)malloc((size_t)(nnz > 0 ? nnz : 1) * sizeof(double));
+	int64_t *bounds = (int64_t *)malloc((size_t)(2 * nthreads) * sizeof(int64_t));
+	for (int64_t s = 0; s < S; s++)
+		rcp0[s] = rp[s * VL];
+	rcp0[S] = rp[m];
+	for (int64_t t = 0; t < nthreads; t++) {
+		int64_t ii_s, ii_e;
+		oracle_partition_prefix_sums(nthreads, t, rcp0, S, nnz, &ii_s, &ii_e);
+		bounds[2 * t] = ii_s;
+		bounds[2 * t + 1] = ii_e;
+		const int64_t i_s = ii_s * VL, i_e = (t == nthreads - 1) ? m : ii_e * VL;
+		int64_t dmax = 0;
+		for (int64_t i = i_s; i < i_e; i++)
+			if (rp[i + 1] - rp[i] > dmax)
+				dmax = rp[i + 1] - rp[i];
+		int64_t *off = (int64_t *)calloc((size_t)(dmax + 2), sizeof(int64_t));   /* stable counting sort, ascending length */
+		for (int64_t i = i_s; i < i_e; i++)
+			off[rp[i + 1] - rp[i] + 1]++;
+		for (int64_t d = 0; d <= dmax; d++)
+			off[d + 1] += off[d];
+		for (int64_t i = i_s; i < i_e; i++) {
+			permutation[i] = (int32_t)(i_s + off[rp[i + 1] - rp[i]]++);
+			rev_permutation[permutation[i]] = (int32_t)i;
+		}
+		free(off);
+	}
+	rp2[0] = 0;
+	for (int64_t i = 0; i < m; i++) {
+		const int64_t r = rev_permutation[i];
+		rp2[i + 1] = rp2[i] + (rp[r + 1] - rp[r]);
+		for (int64_t j = rp[r], k = rp2[i]; j < rp[r + 1]; j++, k++) {
+			ci2[k] = ci[j];
+			v2[k] = v[j];
 		}
 	}
+	const int64_t run = sell_plain_widths(rp2, m, VL, rcp);
+	if (ja)
+		for (int64_t t = 0; t < nthreads; t++)
+			sell_plain_fill(rp2, ci2, v2, m, VL, rcp, bounds[2 * t], bounds[2 * t + 1], ja, a);
+	free(rcp0);
+	free(rp2);
+	free(ci2);
+	free(v2);
+	free(bounds);
 	return run;
 }
 

@@ -223,3 +223,40 @@ def test_plain_sell_vs_reference(oracle):
                 assert oracle.within_bound(y[:m], oracle.csr_spmv(rp, col, val, x), oracle.row_abs_bound(rp, col, val, x))
     finally:
         oracle.set_threads(t0)
+
+
+def test_sorted_sell_vs_reference(oracle):
+    """SURVEY 8a row a8, second half: the per-thread-sorted SELL (K/sell_sorted.cpp) restated and pinned against that file
+    compiled unmodified (oracle/_ref/libref_sell_sorted.so): permutation / rev_permutation (stable ascending sort inside each
+    converting thread's row range), row_cluster_ptr / ja / a bit for bit, and the product (y written through rev_permutation)
+    bit-equal to the plain SELL oracle's.  Sizes keep every thread at >= VEC_LEN slices: with fewer the reference's
+    `ii_e_last -= VEC_LEN` (:356-358) walks out of its range."""
+    import os
+    if not os.path.exists(os.path.join(os.path.dirname(oracle.__file__), "_ref", "libref_sell_sorted.so")):
+        pytest.skip("oracle/_ref/libref_sell_sorted.so not built (needs /root/reference at build time)")
+    rng = np.random.default_rng(6)
+    cases = [M.csr_from_lengths(rng.integers(0, 9, 1003), 500, 1),
+             M.csr_from_lengths(np.r_[np.zeros(9, np.int64), rng.integers(0, 40, 500)], 2000, 2),
+             M.csr_from_lengths(np.r_[rng.integers(1, 4, 300), [700], rng.integers(1, 4, 201)], 900, 3)]
+    t0 = oracle.max_threads()
+    try:
+        for nt in (1, 2, 3, 5):
+            oracle.set_threads(nt)
+            for rp, col, val in cases:
+                m, n = len(rp) - 1, int(col.max()) + 1
+                R = oracle.RefSELLSorted(rp, col, val, n)
+                O = oracle.sell_sorted_convert(rp, col, val, R.VL, nt)
+                assert np.array_equal(O["permutation"], R.permutation), (nt, m)
+                assert np.array_equal(O["rev_permutation"], R.rev_permutation)
+                assert np.array_equal(O["row_cluster_ptr"], R.row_cluster_ptr)
+                assert np.array_equal(O["ja"], R.ja), (nt, m)
+                assert np.array_equal(O["a"], R.a)
+                x = M.rand_x(n, 7)
+                y_ref = np.full(m + 64, 3.0)
+                R.spmv(x, y_ref)
+                y = oracle.sell_sorted_spmv(O, x)
+                assert np.array_equal(y, y_ref[:m]) and np.all(y_ref[m:] == 3.0)
+                P = oracle.sell_plain_convert(rp, col, val, R.VL, nt)
+                assert np.array_equal(y, oracle.sell_plain_spmv(P, x)[:m])
+    finally:
+        oracle.set_threads(t0)
