@@ -53,6 +53,8 @@ def lib():
         L.oracle_sell_plain_convert.restype = C.c_int64
         L.oracle_sell_sorted_convert.argtypes = [_i32p, _i32p, _f64p, C.c_int64, C.c_int64, C.c_int64, _i32p, _i32p, _i32p, C.c_void_p, C.c_void_p]
         L.oracle_sell_sorted_convert.restype = C.c_int64
+        L.oracle_coo_to_csr.argtypes = [_i32p, _i32p, _f64p, C.c_int64, C.c_int64, C.c_int64, _i32p, _i32p, _f64p]
+        L.oracle_coo_to_csr.restype = C.c_int64
         L.oracle_sell_plain_spmv.argtypes = [C.c_int64, C.c_int64, _i32p, _i32p, _f64p, _f64p, _f64p]
         L.oracle_fnv1a64.argtypes = [C.c_void_p, C.c_int64]
         L.oracle_fnv1a64.restype = C.c_uint64
@@ -230,6 +232,44 @@ def sell_plain_spmv(layout, x):
     lib().oracle_sell_plain_spmv(m, VL, layout["row_cluster_ptr"], _pad1(layout["ja"], np.int32), _pad1(layout["a"], np.float64),
                                  np.ascontiguousarray(x, np.float64), y)
     return y[:-1]
+
+
+def coo_to_csr(row, col, val, m, n):
+    """COO -> CSR as the reference's import_file() (bench.cpp:208-229, csr_gen.c:178-213): (row_ptr, col, val, n_duplicates)."""
+    nnz = len(row)
+    rp = np.zeros(m + 1, np.int32)
+    co, vo = np.zeros(max(nnz, 1), np.int32), np.zeros(max(nnz, 1), np.float64)
+    d = lib().oracle_coo_to_csr(_pad1(np.ascontiguousarray(row, np.int32), np.int32), _pad1(np.ascontiguousarray(col, np.int32), np.int32),
+                                _pad1(np.ascontiguousarray(val, np.float64), np.float64), m, n, nnz, rp, co, vo)
+    if d < 0:
+        raise ValueError("COO index out of range")
+    return rp, co[:nnz], vo[:nnz], int(d)
+
+
+def ref_mtx_to_csr(path, threads=2):
+    """The reference's own ingest (mtx_read + mtx_values_convert_to_real + coo_to_csr) through oracle/_ref/ref_mtx_dump.exe:
+    dict(m, n, nnz, symmetric, nnz_diag, nnz_non_diag, row_ptr, col, val), or None when the tool is not built."""
+    import subprocess
+    import tempfile
+    exe = os.path.join(HERE, "_ref", "ref_mtx_dump.exe")
+    if not os.path.exists(exe):
+        return None
+    with tempfile.TemporaryDirectory() as td:
+        out = os.path.join(td, "csr.bin")
+        env = dict(os.environ, OMP_NUM_THREADS=str(threads))
+        p = subprocess.run([exe, path, out], capture_output=True, text=True, env=env)
+        if p.returncode != 0:
+            raise RuntimeError("ref_mtx_dump failed: %s %s" % (p.stdout[-500:], p.stderr[-500:]))
+        b = open(out, "rb").read()
+    h = np.frombuffer(b[:48], np.int64)
+    m, n, nnz = int(h[0]), int(h[1]), int(h[2])
+    o = 48
+    rp = np.frombuffer(b[o:o + 4 * (m + 1)], np.int32).copy()
+    o += 4 * (m + 1)
+    ci = np.frombuffer(b[o:o + 4 * nnz], np.int32).copy()
+    o += 4 * nnz
+    va = np.frombuffer(b[o:o + 8 * nnz], np.float64).copy()
+    return dict(m=m, n=n, nnz=nnz, symmetric=int(h[3]), nnz_diag=int(h[4]), nnz_non_diag=int(h[5]), row_ptr=rp, col=ci, val=va)
 
 
 def set_threads(k):

@@ -723,3 +723,52 @@ void oracle_sell_plain_spmv(int64_t m, int64_t VL, const int32_t *rcp, const int
 			y[VL * ii + lane] = sum;
 		}
 }
+
+/* COO -> CSR as the reference's import_file() does it (bench.cpp:208-229 -> coo_to_csr, lib/storage_formats/csr/csr_gen.c:
+ * 178-213): a stable bucket sort of the entries by row (row_ptr = the bucket offsets), then the columns of each row
+ * sorted ascending (csr_sort_columns).  For a matrix without duplicate (row, col) pairs the result is simply the entries
+ * in (row, col) order.  The reference orders duplicates with an unstable quicksort; here they keep their input order
+ * (stable), and the return value says how many there are so that callers can refuse them.
+ * row_ptr[m + 1], col_out[nnz], val_out[nnz].  Returns the number of duplicate pairs, or -1 on an index out of range. */
+int64_t oracle_coo_to_csr(const int32_t *R, const int32_t *Cc, const double *V, int64_t m, int64_t n, int64_t nnz,
+                          int32_t *row_ptr, int32_t *col_out, double *val_out)
+{
+	int64_t *cnt = (int64_t *)calloc((size_t)(m + 1), sizeof(int64_t));
+	int64_t *perm = (int64_t *)malloc((size_t)(nnz > 0 ? nnz : 1) * sizeof(int64_t));
+	for (int64_t e = 0; e < nnz; e++) {
+		if (R[e] < 0 || R[e] >= m || Cc[e] < 0 || Cc[e] >= n) {
+			free(cnt);
+			free(perm);
+			return -1;
+		}
+		cnt[R[e] + 1]++;
+	}
+	for (int64_t i = 0; i < m; i++)
+		cnt[i + 1] += cnt[i];
+	for (int64_t i = 0; i <= m; i++)
+		row_ptr[i] = (int32_t)cnt[i];
+	for (int64_t e = 0; e < nnz; e++)
+		perm[cnt[R[e]]++] = e;                      /* stable: entries of a row in input order */
+	int64_t dups = 0;
+	for (int64_t i = 0; i < m; i++) {
+		const int64_t a = row_ptr[i], b = row_ptr[i + 1];
+		for (int64_t j = a + 1; j < b; j++) {       /* stable insertion sort by column (rows are short in tests) */
+			const int64_t p = perm[j];
+			int64_t k = j;
+			while (k > a && Cc[perm[k - 1]] > Cc[p]) {
+				perm[k] = perm[k - 1];
+				k--;
+			}
+			perm[k] = p;
+		}
+		for (int64_t j = a; j < b; j++) {
+			col_out[j] = Cc[perm[j]];
+			val_out[j] = V[perm[j]];
+			if (j > a && col_out[j] == col_out[j - 1])
+				dups++;
+		}
+	}
+	free(cnt);
+	free(perm);
+	return dups;
+}

@@ -2,6 +2,7 @@
 
   lib/libb200spmv.so : CUDA kernels + C-ABI, nvcc, sm_100a only
   lib/libb200amg.so  : host-side synthetic matrix source, gcc
+  lib/libb200mtx.so  : host-side Matrix Market reader, gcc
 """
 import os
 import subprocess
@@ -38,8 +39,13 @@ def build_amg(force=False):
     return amg.build(force)
 
 
+def build_mtx(force=False):
+    from . import mtx
+    return mtx.build(force)
+
+
 def build_all(force=False, verbose=False):
-    return build_spmv(force, verbose), build_amg(force)
+    return build_spmv(force, verbose), build_amg(force), build_mtx(force)
 
 
 if __name__ == "__main__":

@@ -66,3 +66,12 @@ def test_symmetric_unexpanded_rejected(native):
     import spmv_research_b200 as S
     with pytest.raises(S.B200Error, match="symmetric matrices have to be expanded"):
         S.csr_to_format(np.array([0, 1], np.int32), np.zeros(1, np.int32), np.ones(1), 1, 1, 1, symmetric=1, symmetry_expanded=0)
+
+
+def test_b200mtx_exports_all_declared_symbols(native):
+    from spmv_research_b200 import mtx
+    L = ctypes.CDLL(mtx._SO)
+    names = _declared("b200mtx.h", "b200mtx_")
+    assert set(names) >= {"b200mtx_read", "b200mtx_free", "b200mtx_last_error"}
+    for n in names:
+        assert hasattr(L, n), n
