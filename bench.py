@@ -165,6 +165,9 @@ def parse_args():
     ap.add_argument("--x", default="ones", choices=["ones", "random"])
     ap.add_argument("--host-pipeline", action="store_true",
                     help="N=1 e2e leg: opts.host_pipeline = 1 (x uploaded range by range so H2D overlaps D2H; off by default until verified on a B200)")
+    ap.add_argument("--device-generator", action="store_true",
+                    help="power workload: generate each rank's non-zeros on the GPU (b200spmv_amg_fill_device; bit-identical, "
+                         "not yet verified on a B200 -> off by default)")
     ap.add_argument("--line", default=None, help="one generator parameter line to use as the N=1 workload (profiling)")
     return ap.parse_args()
 
@@ -379,16 +382,29 @@ def run_power(args):
     capi.check(capi.lib().b200spmv_set_device(local))
     bounds = power.shard_bounds(rp, m, nnz, world, capi.partition)        # reference partitioner, on the GPU
     i_s, i_e = int(bounds[rank, 0]), int(bounds[rank, 1])
-    col, val = amg.fill(p, rp, bw, i_s, i_e)
-    t_gen = time.time() - t0
     rp_loc = (rp[i_s:i_e + 1] - rp[i_s]).astype(np.int32)
     nnz_loc = int(rp_loc[-1])
+    if args.device_generator:
+        # pass 2 on the GPU: the shard's non-zeros never exist on the host
+        d_rp = torch.from_numpy(rp).to(dev)
+        col = torch.empty(nnz_loc, dtype=torch.int32, device=dev)
+        val = torch.empty(nnz_loc, dtype=torch.float64, device=dev)
+        amg.fill_device(p, d_rp, bw, i_s, i_e, col, val, stream)
+        del d_rp
+    else:
+        col, val = amg.fill(p, rp, bw, i_s, i_e)
+    t_gen = time.time() - t0
     # Column panels are off under the fused exchange: the rows become final (and can be stored to the peers) only in the
     # LAST panel's launch, which squeezes the NVLink traffic into half of the iteration -- measured at N=8: 1.28 ms / iteration
     # with 2 panels against 1.10 ms without, although the kernels alone are 10 % faster (profiles/r01s_bench_n8_csr_panels.json;
     # the two runs were on different boxes with different power caps, see DESIGN.md 7 -- to be re-measured on one box).
     fused = world > 1 and args.exchange in ("p2p", "mc")
-    MF = S.csr_to_format(rp_loc, col, val, i_e - i_s, n, nnz_loc, 0, 0, format=fmt, device=local, col_panels=(1 if fused else 0))
+    if args.device_generator:
+        from spmv_research_b200 import formats
+        MF = formats.csr_to_format_device(torch.from_numpy(rp_loc).to(dev), col, val, i_e - i_s, n, nnz_loc, format=fmt, device=local,
+                                          col_panels=(1 if fused else 0))
+    else:
+        MF = S.csr_to_format(rp_loc, col, val, i_e - i_s, n, nnz_loc, 0, 0, format=fmt, device=local, col_panels=(1 if fused else 0))
     del col, val
 
     exchange = args.exchange if world > 1 else "nccl"
@@ -585,7 +601,8 @@ def run_power(args):
                                     "nccl": "NCCL in-place all-gather of y slots (one broadcast per owner) + scalar all-reduce"}[exchange],
                        "exchange_note": mc_note,
                        "exchange_rows": "rows [%d, %d) of %d (the union of the shards' referenced column bands)" % (band[0], band[1], n),
-                       "l2_note": "each shard is %.1f GB (> 126 MB L2); no explicit flush" % (bc_loc * 1e-9), "generate_s": round(t_gen, 1)},
+                       "l2_note": "each shard is %.1f GB (> 126 MB L2); no explicit flush" % (bc_loc * 1e-9), "generate_s": round(t_gen, 1),
+                       "generator": "device pass 2" if args.device_generator else "host"},
             "effective_GBs": round(bc / (ms_step * 1e-3) * 1e-9, 1),
             "roofline_frac_nominal_8TBs": round(bc / (ms_step * 1e-3) * 1e-9 / (NOMINAL_HBM_GBS * world), 4),
             "roofline": {"bound": "hbm", "kernel": "csr_tile_kernel" if MF.format == S.CSR_ADAPTIVE else "sell_kernel",

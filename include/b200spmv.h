@@ -28,6 +28,7 @@
 #define B200SPMV_H
 
 #include <stdint.h>
+#include "b200amg.h"      /* b200amg_params (the generator's 11 parameters) */
 
 #ifdef __cplusplus
 extern "C" {
@@ -200,6 +201,17 @@ int b200spmv_pcg(b200spmv_t * h, const double * b_host, double * x_host, int64_t
  * err = ||r_k|| after the last iteration, converged = (err_best < eps).  Needs keep_diag = 1. */
 int b200spmv_bicgstab(b200spmv_t * h, const double * b_host, double * x_host, int64_t max_iterations, double * trace_host,
                       b200spmv_pcg_result * result);
+
+/* Pass 2 of the synthetic matrix source on the GPU: the device counterpart of b200amg_fill() (include/b200amg.h), i.e. of
+ * the non-zero placement half of the reference's artificial_matrix_generation()
+ * (artificial-matrix-generator/artificial_matrix_generation.c:366-523; called from benchmark_code/BENCH/src/bench.cpp:250).
+ * d_row_ptr: the WHOLE matrix's row_ptr (nr_rows + 1 entries, from b200amg_row_ptr -- pass 1 stays on the host because it
+ * is the only part that depends on glibc's libm) in device memory; bw_corrected: pass 1's second output.  Writes the
+ * non-zeros of rows [i_s, i_e) to d_col_ind / d_values (DEVICE pointers; entry j of the whole matrix lands at
+ * j - row_ptr[i_s]), bit-identical to the reference generator, ready for b200spmv_create_device().  One warp per anchor
+ * segment (<= ~4100 independent random streams); synchronises `stream` before returning. */
+int b200spmv_amg_fill_device(const b200amg_params * p, const int32_t * d_row_ptr, double bw_corrected, int64_t i_s, int64_t i_e,
+                             int32_t * d_col_ind, double * d_values, void * stream);
 
 const char * b200spmv_last_error(void);
 const char * b200spmv_version(void);

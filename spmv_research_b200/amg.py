@@ -110,6 +110,32 @@ def fill(p, rp, bw_corrected, i_s, i_e, col_out=None, val_out=None):
     return col[:cnt], val[:cnt]
 
 
+def fill_device(p, d_row_ptr, bw_corrected, i_s, i_e, d_col, d_val, stream=None):
+    """Pass 2 on the GPU (libb200spmv.so: b200spmv_amg_fill_device, csrc/amg_device.cu): the non-zeros of rows [i_s, i_e)
+    written straight into HBM, bit-identical to fill().  d_row_ptr: the WHOLE row_ptr in device memory; d_col / d_val:
+    device buffers of row_ptr[i_e] - row_ptr[i_s] entries (torch tensors or raw addresses).  No CPU fallback."""
+    from . import capi
+    cp = p._c()
+    capi.check(capi.lib().b200spmv_amg_fill_device(C.cast(C.pointer(cp), C.c_void_p), capi._ptr(d_row_ptr), bw_corrected,
+                                                   int(i_s), int(i_e), capi._ptr(d_col), capi._ptr(d_val), stream))
+
+
+def generate_device(p, i_s=0, i_e=None, device="cuda:0"):
+    """Rows [i_s, i_e) generated into HBM: pass 1 on the host (the libm-dependent row lengths), pass 2 on the GPU.
+    Returns (row_ptr numpy int32[m+1] of the whole matrix, d_row_ptr, d_col, d_val) -- the last three torch tensors on
+    `device`, d_row_ptr whole, ready for capi.Handle(d_row_ptr[i_s:i_e+1], d_col, d_val, ..., device_arrays=True)."""
+    import torch
+    i_e = p.rows if i_e is None else i_e
+    rp, bw = row_ptr(p)
+    cnt = int(rp[i_e]) - int(rp[i_s])
+    with torch.cuda.device(device):
+        d_rp = torch.from_numpy(rp).to(device)
+        d_col = torch.empty(cnt, dtype=torch.int32, device=device)
+        d_val = torch.empty(cnt, dtype=torch.float64, device=device)
+        fill_device(p, d_rp, bw, i_s, i_e, d_col, d_val, torch.cuda.current_stream().cuda_stream)
+    return rp, d_rp, d_col, d_val
+
+
 def generate(p):
     """Whole matrix: (row_ptr, col_ind, values) exactly as the reference generator returns them."""
     rp, bw = row_ptr(p)

@@ -85,6 +85,7 @@ def lib():
         "b200spmv_time_device": (C.c_int, [vp, vp, vp, i32, i64, vp]),
         "b200spmv_pcg": (C.c_int, [vp, vp, vp, i64, C.POINTER(PcgResult)]),
         "b200spmv_bicgstab": (C.c_int, [vp, vp, vp, i64, vp, C.POINTER(PcgResult)]),
+        "b200spmv_amg_fill_device": (C.c_int, [vp, vp, C.c_double, i64, i64, vp, vp, vp]),
         "b200spmv_last_error": (C.c_char_p, []),
         "b200spmv_version": (C.c_char_p, []),
     }
