@@ -202,6 +202,20 @@ int b200spmv_pcg(b200spmv_t * h, const double * b_host, double * x_host, int64_t
 int b200spmv_bicgstab(b200spmv_t * h, const double * b_host, double * x_host, int64_t max_iterations, double * trace_host,
                       b200spmv_pcg_result * result);
 
+/* COO -> CSR on the GPU: the reference's coo_to_csr() (lib/storage_formats/csr/csr_gen.c:178-213, called by import_file(),
+ * benchmark_code/BENCH/src/bench.cpp:208-229) -- entries bucketed by row, columns ascending inside every row, equal
+ * (row, col) pairs kept in input order.  All pointers are DEVICE pointers; indices base 0; d_row_ptr has m + 1 entries,
+ * d_col_out / d_val_out nnz.  *duplicates_out (HOST, optional) = number of adjacent equal (row, col) pairs in the result.
+ * Fails on an index outside [0, m) x [0, n).  Synchronises `stream` before returning. */
+int b200spmv_coo_to_csr(const int32_t * d_row, const int32_t * d_col, const double * d_val, int64_t m, int64_t n, int64_t nnz,
+                        int32_t * d_row_ptr, int32_t * d_col_out, double * d_val_out, int64_t * duplicates_out, void * stream);
+
+/* import_file() + csr_to_format() for a matrix that arrives as COO (HOST arrays, e.g. from b200mtx_read() with the symmetry
+ * expanded, include/b200mtx.h): upload, COO -> CSR on the GPU, format built from the device arrays.  Duplicate (row, col)
+ * entries are refused (the reference leaves their order to an unstable sort; there is nothing bit-exact to reproduce). */
+int b200spmv_create_coo(b200spmv_t ** out, const int32_t * row, const int32_t * col, const double * val, int64_t m, int64_t n,
+                        int64_t nnz, const b200spmv_opts * opts);
+
 /* Pass 2 of the synthetic matrix source on the GPU: the device counterpart of b200amg_fill() (include/b200amg.h), i.e. of
  * the non-zero placement half of the reference's artificial_matrix_generation()
  * (artificial-matrix-generator/artificial_matrix_generation.c:366-523; called from benchmark_code/BENCH/src/bench.cpp:250).

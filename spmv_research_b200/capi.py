@@ -85,6 +85,8 @@ def lib():
         "b200spmv_time_device": (C.c_int, [vp, vp, vp, i32, i64, vp]),
         "b200spmv_pcg": (C.c_int, [vp, vp, vp, i64, C.POINTER(PcgResult)]),
         "b200spmv_bicgstab": (C.c_int, [vp, vp, vp, i64, vp, C.POINTER(PcgResult)]),
+        "b200spmv_coo_to_csr": (C.c_int, [vp, vp, vp, i64, i64, i64, vp, vp, vp, C.POINTER(i64), vp]),
+        "b200spmv_create_coo": (C.c_int, [C.POINTER(vp), vp, vp, vp, i64, i64, i64, C.POINTER(Opts)]),
         "b200spmv_amg_fill_device": (C.c_int, [vp, vp, C.c_double, i64, i64, vp, vp, vp]),
         "b200spmv_last_error": (C.c_char_p, []),
         "b200spmv_version": (C.c_char_p, []),
@@ -128,11 +130,12 @@ def default_opts(**kw):
 class Handle:
     """Owns one b200spmv_t*."""
 
-    def __init__(self, row_ptr, col_ind, values, m, n, nnz, opts=None, device_arrays=False):
+    def __init__(self, row_ptr, col_ind, values, m, n, nnz, opts=None, device_arrays=False, coo=False):
+        """CSR arrays on the host (default) or in HBM (device_arrays); coo=True: row_ptr is the COO row index array (host)."""
         self._h = C.c_void_p()
         self.m, self.n, self.nnz = int(m), int(n), int(nnz)
         self._opts = opts if opts is not None else default_opts()
-        fn = lib().b200spmv_create_device if device_arrays else lib().b200spmv_create
+        fn = lib().b200spmv_create_coo if coo else (lib().b200spmv_create_device if device_arrays else lib().b200spmv_create)
         check(fn(C.byref(self._h), _ptr(row_ptr), _ptr(col_ind), _ptr(values), self.m, self.n, self.nnz, C.byref(self._opts)))
 
     def close(self):
@@ -231,6 +234,14 @@ def partition(sums, N, total, W, device=False):
     fn = lib().b200spmv_partition_device if device else lib().b200spmv_partition
     check(fn(_ptr(sums), int(N), int(total), int(W), out.ctypes.data))
     return out
+
+
+def coo_to_csr_device(d_row, d_col, d_val, m, n, nnz, d_row_ptr, d_col_out, d_val_out, stream=None):
+    """b200spmv_coo_to_csr on device buffers (torch tensors or raw addresses); returns the number of duplicate pairs."""
+    d = C.c_int64()
+    check(lib().b200spmv_coo_to_csr(_ptr(d_row), _ptr(d_col), _ptr(d_val), int(m), int(n), int(nnz), _ptr(d_row_ptr), _ptr(d_col_out),
+                                    _ptr(d_val_out), C.byref(d), stream))
+    return d.value
 
 
 def device_count():

@@ -98,3 +98,18 @@ def csr_to_format_device(d_row_ptr, d_col_ind, d_values, m, n, nnz, *, format=ca
     o = capi.default_opts(format=format, **opts)
     h = capi.Handle(d_row_ptr, d_col_ind, d_values, m, n, nnz, o, device_arrays=True)
     return MatrixFormat(h, format)
+
+
+def coo_to_format(row, col, val, m, n, *, format=capi.CSR_ADAPTIVE, cache_x=False, **opts):
+    """The reference's import_file() tail + csr_to_format() for COO input (base-0 host arrays in the reference's entry
+    order, symmetry already expanded -- what mtx.read_mtx returns): COO -> CSR on the GPU (b200spmv_create_coo,
+    csrc/coo.cu; reference coo_to_csr, lib/storage_formats/csr/csr_gen.c:178-213), then the format."""
+    row = np.ascontiguousarray(row, np.int32)
+    col = np.ascontiguousarray(col, np.int32)
+    val = np.ascontiguousarray(val, np.float64)
+    nnz = int(row.size)
+    if col.size != nnz or val.size != nnz:
+        raise capi.B200Error("COO array sizes differ")
+    o = capi.default_opts(format=format, **opts)
+    h = capi.Handle(row if nnz else None, col if nnz else None, val if nnz else None, m, n, nnz, o, coo=True)
+    return MatrixFormat(h, format, cache_x=cache_x)
