@@ -39,6 +39,10 @@ typedef struct b200amg_params {
 /* pass 1: fills row_ptr[0..nr_rows]; returns nnz or -1.  *bw_corrected feeds b200amg_fill. */
 int64_t b200amg_row_ptr(const b200amg_params * p, int32_t * row_ptr, double * bw_corrected);
 
+/* bw_corrected alone, given pass 1's nnz: pass 1 does not depend on bw / neighbours / similarity, so a sweep over those
+ * computes row_ptr once per (rows, avg, std, distribution, skew, seed) and this per line. */
+double b200amg_bw_corrected(const b200amg_params * p, int64_t nnz);
+
 /* pass 2 for rows [i_s, i_e): entry j of the full matrix is written at j - row_ptr[i_s]. */
 int b200amg_fill(const b200amg_params * p, const int32_t * row_ptr, double bw_corrected,
                  int64_t i_s, int64_t i_e, int32_t * col_ind, double * values);

@@ -44,6 +44,8 @@ def _L():
         i32p = np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS")
         L.b200amg_row_ptr.restype = C.c_int64
         L.b200amg_row_ptr.argtypes = [C.POINTER(_Params), i32p, C.POINTER(C.c_double)]
+        L.b200amg_bw_corrected.restype = C.c_double
+        L.b200amg_bw_corrected.argtypes = [C.POINTER(_Params), C.c_int64]
         L.b200amg_fill.restype = C.c_int
         L.b200amg_fill.argtypes = [C.POINTER(_Params), i32p, C.c_double, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p]
         L.b200amg_fnv1a64.restype = C.c_uint64
@@ -95,6 +97,13 @@ def row_ptr(p):
     if nnz < 0:
         raise RuntimeError(_L().b200amg_last_error().decode())
     return rp, bw.value
+
+
+def bw_corrected(p, nnz):
+    """The corrected band width of a line whose pass 1 (shared by every line with the same rows / avg / std / distribution /
+    skew / seed) gave nnz non-zeros."""
+    cp = p._c()
+    return float(_L().b200amg_bw_corrected(C.byref(cp), int(nnz)))
 
 
 def fill(p, rp, bw_corrected, i_s, i_e, col_out=None, val_out=None):

@@ -261,13 +261,20 @@ int64_t b200amg_row_ptr(const b200amg_params *p, int32_t *row_ptr, double *bw_co
 		}
 		row_ptr[i + 1] = (int32_t)tot;
 	}
-	if (bw_corrected_out) {
-		double p_right = p->avg_num_neighbours / 2;
-		double cluster = 1 / (1 - p_right);
-		double avg_real = ((double)tot) / m;
-		*bw_corrected_out = corrected_bw(p->bw_scaled > 1 ? (double)p->nr_cols : p->bw_scaled * p->nr_cols, avg_real / cluster);
-	}
+	if (bw_corrected_out)
+		*bw_corrected_out = b200amg_bw_corrected(p, tot);
 	return tot;
+}
+
+/* The corrected band width alone (:340-348), for a matrix whose pass 1 gave nnz non-zeros.  Pass 1 depends on
+ * (rows, avg, std, distribution, skew, seed) only, so a parameter sweep over bw / neighbours / similarity computes
+ * row_ptr once and this per line. */
+double b200amg_bw_corrected(const b200amg_params *p, int64_t nnz)
+{
+	double p_right = p->avg_num_neighbours / 2;
+	double cluster = 1 / (1 - p_right);
+	double avg_real = ((double)nnz) / p->nr_rows;
+	return corrected_bw(p->bw_scaled > 1 ? (double)p->nr_cols : p->bw_scaled * p->nr_cols, avg_real / cluster);
 }
 
 /* ---- per-thread column set: open addressing with generation stamps ---- */

@@ -28,6 +28,47 @@ def medium_sample():
     return load_param_file(os.path.join(_HERE, "params", "medium_sample.txt"))
 
 
+# synthetic_matrices_medium_dataset.txt (BASELINE config 2) is a grid: 15 row counts per avg-nnz class x bw x skew x
+# neighbours x similarity (std = avg / 3 to 4 decimals, normal, random, seed 14), minus 10 lines the reference's file does
+# not contain.  Stored as the grid, not as 16 190 lines; tests/test_amg.py checks it against the reference's file as a set
+# when /root/reference is present.
+_MEDIUM_ROWS = {
+    5: [65535, 147455, 229375, 311295, 393215, 524287, 2097151, 3670015, 5242879, 6815743, 8388607, 13418495, 18448383, 23478271, 28508159],
+    10: [33825, 76106, 118387, 160668, 202950, 270600, 1082401, 1894201, 2706002, 3517803, 4329604, 6925675, 9521746, 12117817, 14713889],
+    20: [17189, 38676, 60164, 81651, 103138, 137518, 550072, 962627, 1375181, 1787736, 2200290, 3519605, 4838920, 6158235, 7477550],
+    50: [6944, 15624, 24304, 32985, 41665, 55553, 222214, 388875, 555536, 722198, 888859, 1421827, 1954795, 2487763, 3020732],
+    100: [3483, 7838, 12192, 16547, 20901, 27869, 111476, 195083, 278691, 362298, 445906, 713275, 980644, 1248014, 1515383],
+    500: [698, 1571, 2445, 3318, 4191, 5588, 22354, 39120, 55886, 72652, 89418, 143035, 196651, 250268, 303884],
+}
+_MEDIUM_STD = {5: 1.6667, 10: 3.3333, 20: 6.6667, 50: 16.6667, 100: 33.3333, 500: 166.6667}
+_MEDIUM_BW, _MEDIUM_SKEW = (0.05, 0.3, 0.6), (0, 100, 1000, 10000)
+_MEDIUM_NEIGH, _MEDIUM_CRS = (0.05, 0.5, 0.95, 1.4, 1.9), (0.05, 0.5, 0.95)
+_MEDIUM_ABSENT = {(4191, 1.9, 0.05), (4191, 1.9, 0.5), (4191, 1.9, 0.95), (72652, 1.9, 0.05), (72652, 1.9, 0.5), (72652, 1.9, 0.95),
+                  (303884, 1.4, 0.95), (303884, 1.9, 0.05), (303884, 1.9, 0.5), (303884, 1.9, 0.95)}      # all at avg 500, bw 0.6, skew 10000
+
+
+def medium_dataset():
+    """All 16 190 parameter lines of the reference's synthetic_matrices_medium_dataset.txt, grouped so that lines sharing
+    pass 1 of the generator (same rows / avg / skew) are adjacent."""
+    out = []
+    for avg, rows_list in _MEDIUM_ROWS.items():
+        for rows in rows_list:
+            for skew in _MEDIUM_SKEW:
+                for bw in _MEDIUM_BW:
+                    for neigh in _MEDIUM_NEIGH:
+                        for crs in _MEDIUM_CRS:
+                            if avg == 500 and bw == 0.6 and skew == 10000 and (rows, neigh, crs) in _MEDIUM_ABSENT:
+                                continue
+                            out.append(amg.MatrixParams(rows, rows, avg, _MEDIUM_STD[avg], "normal", "random", bw, skew, neigh, crs, 14))
+    return out
+
+
+def footprint_class(p):
+    """CSR footprint class of SURVEY 8d from the nominal nnz = rows x avg."""
+    mb = (12 * p.rows * p.avg + 4 * (p.rows + 1)) / 2 ** 20
+    return "<32MB" if mb < 32 else "32-128MB" if mb < 128 else "128-512MB" if mb < 512 else ">=512MB"
+
+
 CONFIG1 = amg.MatrixParams.parse("1000000 1000000 10 5 normal random 0.3 0 0.5 0.5 14")
 CONFIG4_G1 = amg.MatrixParams.parse("8388607 8388607 50 150 gamma random 0.6 0 0.05 0.05 14")
 CONFIG4_G2 = amg.MatrixParams.parse("8388607 8388607 50 16.6667 gamma random 0.6 10000 0.05 0.05 14")

@@ -58,3 +58,28 @@ def test_errors_and_parsing(native):
         amg.MatrixParams.parse("1 2 3")
     p = amg.MatrixParams.parse("17099 17099 5.6 4.39 normal random 0.29 61.9 0.8 0.63 14 scircuit")
     assert p.name == "scircuit" and p.seed == 14 and amg.MatrixParams.parse(p.line()).rows == 17099
+
+
+def test_bw_corrected_alone_equals_pass1(native):
+    """b200amg_bw_corrected(p, nnz) is pass 1's second output (a sweep shares row_ptr between lines that differ in bw /
+    neighbours / similarity only)."""
+    for line in M.GOLDEN_LINES[:4]:
+        p = amg.MatrixParams.parse(line)
+        rp, bw = amg.row_ptr(p)
+        assert amg.bw_corrected(p, int(rp[-1])) == bw
+
+
+def test_medium_dataset_grid_is_the_reference_file():
+    """harness.medium_dataset() (a grid description) is, as a set, the reference's synthetic_matrices_medium_dataset.txt."""
+    import collections
+    import os
+    from spmv_research_b200 import harness as H
+    ds = H.medium_dataset()
+    assert len(ds) == 16190 and len(set(p.line() for p in ds)) == 16190
+    cls = collections.Counter(H.footprint_class(p) for p in ds)
+    assert (cls["<32MB"], cls["32-128MB"], cls["128-512MB"], cls[">=512MB"]) == (6477, 900, 4497, 4316)      # SURVEY 8d
+    ref = "/root/reference/matrix_generation_parameters/synthetic_matrices_medium_dataset.txt"
+    if not os.path.exists(ref):
+        pytest.skip("reference not mounted (authoring container only)")
+    want = set(amg.MatrixParams.parse(l).line() for l in open(ref) if l.strip())
+    assert want == set(p.line() for p in ds)
