@@ -227,6 +227,18 @@ int b200spmv_create_coo(b200spmv_t ** out, const int32_t * row, const int32_t * 
 int b200spmv_amg_fill_device(const b200amg_params * p, const int32_t * d_row_ptr, double bw_corrected, int64_t i_s, int64_t i_e,
                              int32_t * d_col_ind, double * d_values, void * stream);
 
+/* ---- fp32: the reference's `_f` build axis (benchmark_code/BENCH/src/make.sh:215-216: ValueType = float,
+ * ValueTypeReference = double).  csr_to_format still receives DOUBLE values and narrows them (K/csr.cpp:58-167; here on
+ * the GPU, round to nearest even like the C cast); Matrix_Format::spmv(ValueType * x, ValueType * y) takes float vectors
+ * and accumulates in float (K/csr.cpp:334-350).  CSR only; a separate handle type, the fp64 path is untouched. */
+typedef struct b200spmv_f32 b200spmv_f32_t;
+int b200spmv_f32_create(b200spmv_f32_t ** out, const int32_t * row_ptr, const int32_t * col_ind, const double * values, int64_t m,
+                        int64_t n, int64_t nnz, int32_t device /* -1 = current */);
+int b200spmv_f32_spmv_host(b200spmv_f32_t * h, const float * x, float * y);                       /* host vectors, synchronised */
+int b200spmv_f32_spmv_device(b200spmv_f32_t * h, const float * dx, float * dy, void * stream);    /* device vectors, asynchronous */
+int b200spmv_f32_time_device(b200spmv_f32_t * h, const float * dx, float * dy, int32_t iters, int64_t flush_bytes, float * ms_out);
+void b200spmv_f32_destroy(b200spmv_f32_t * h);
+
 const char * b200spmv_last_error(void);
 const char * b200spmv_version(void);
 

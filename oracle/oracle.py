@@ -13,6 +13,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 _i32p = np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS")
 _i64p = np.ctypeslib.ndpointer(np.int64, flags="C_CONTIGUOUS")
 _f64p = np.ctypeslib.ndpointer(np.float64, flags="C_CONTIGUOUS")
+_f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
 
 
 def build(force=False):
@@ -34,6 +35,8 @@ def lib():
         L = C.CDLL(build())
         L.oracle_csr_spmv_scalar.argtypes = [_i32p, _i32p, _f64p, _f64p, _f64p, C.c_int64, C.c_int64]
         L.oracle_row_abs_bound.argtypes = [_i32p, _i32p, _f64p, _f64p, _f64p, C.c_int64]
+        L.oracle_csr_spmv_scalar_f32.argtypes = [_i32p, _i32p, _f32p, _f32p, _f32p, C.c_int64, C.c_int64]
+        L.oracle_row_abs_bound_f32.argtypes = [_i32p, _i32p, _f32p, _f32p, _f64p, C.c_int64]
         L.oracle_partition_prefix_sums.argtypes = [C.c_int64, C.c_int64, _i32p, C.c_int64, C.c_int64, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
         L.oracle_csr_spmv_omp.argtypes = [_i32p, _i32p, _f64p, _f64p, _f64p, C.c_int64, C.c_int64, _i64p, C.c_int]
         L.oracle_max_threads.restype = C.c_int
@@ -67,6 +70,27 @@ def _pad1(a, dtype):
     """ctypes ndpointer rejects zero-size views of None; keep at least one element."""
     a = np.ascontiguousarray(a, dtype=dtype)
     return a if a.size else np.zeros(1, dtype)
+
+
+def csr_spmv_f32(row_ptr, col_ind, val, x, y_prefill=1.0):
+    """The reference's `_f` build of the serial CSR kernel: val (double, narrowed here with the C cast the plugin's constructor
+    applies) and x as float32, float accumulation in ascending j.  Returns float32 y."""
+    m = len(row_ptr) - 1
+    y = np.full(m, y_prefill, np.float32)
+    if m:
+        lib().oracle_csr_spmv_scalar_f32(row_ptr, _pad1(col_ind, np.int32), _pad1(np.asarray(val).astype(np.float32), np.float32),
+                                         np.ascontiguousarray(x, np.float32), y, 0, m)
+    return y
+
+
+def row_abs_bound_f32(row_ptr, col_ind, val, x):
+    """sum_j |a_ij x_j| per row, in double, from the float32-narrowed operands."""
+    m = len(row_ptr) - 1
+    b = np.zeros(m, np.float64)
+    if m:
+        lib().oracle_row_abs_bound_f32(row_ptr, _pad1(col_ind, np.int32), _pad1(np.asarray(val).astype(np.float32), np.float32),
+                                       np.ascontiguousarray(x, np.float32), b, m)
+    return b
 
 
 def csr_spmv(row_ptr, col_ind, val, x, y_prefill=1.0):
@@ -328,6 +352,22 @@ class RefCSR:
     @property
     def format_name(self):
         return self.L.ref_csr_format_name(self.h).decode()
+
+
+class RefCSRf32(RefCSR):
+    """The `_f` build of the same plugin (oracle/_ref/libref_csr_f.so): double matrix in, float x / y."""
+
+    def __init__(self, row_ptr, col_ind, val, n):
+        L = ref("csr_f")
+        L.ref_csr_create.restype = C.c_void_p
+        L.ref_csr_create.argtypes = [_i32p, _i32p, _f64p, C.c_long, C.c_long, C.c_long]
+        L.ref_csr_spmv.argtypes = [C.c_void_p, _f32p, _f32p]
+        L.ref_csr_spmv_serial.argtypes = [C.c_void_p, _f32p, _f32p]
+        L.ref_csr_format_name.restype = C.c_char_p
+        L.ref_csr_format_name.argtypes = [C.c_void_p]
+        self.L = L
+        self.m = len(row_ptr) - 1
+        self.h = L.ref_csr_create(row_ptr, _pad1(col_ind, np.int32), _pad1(val, np.float64), self.m, n, int(row_ptr[-1]))
 
 
 class RefSELL:

@@ -2,6 +2,8 @@
  * ref_csr_shim.cpp -- builds the REFERENCE's own CPU CSR plugin (K/csr.cpp) and its
  * nnz-balanced partitioner macro (lib/parallel_util.h:156-184) into oracle/_ref/libref_csr.so.
  * The reference sources are #included from where they lie under $(REF); nothing is copied.
+ * Built twice: ValueType = double (libref_csr.so, the `_d` build) and ValueType = float (libref_csr_f.so, the `_f` build,
+ * make.sh:215-216: the matrix still arrives as double and is narrowed by the plugin's constructor).
  * TEST INFRASTRUCTURE ONLY (see oracle/spmv_oracle.c header).
  */
 #include <stdlib.h>
@@ -19,7 +21,7 @@ void * ref_csr_create(int32_t * row_ptr, int32_t * col_ind, double * values, lon
 	return (void *) csr_to_format(row_ptr, col_ind, values, m, n, nnz, 0, 0);
 }
 
-void ref_csr_spmv(void * h, double * x, double * y)
+void ref_csr_spmv(void * h, ValueType * x, ValueType * y)
 {
 	((struct Matrix_Format *) h)->spmv(x, y);
 }
@@ -30,7 +32,7 @@ const char * ref_csr_format_name(void * h)
 }
 
 /* the serial oracle: subkernel_csr_scalar over all rows (K/csr.cpp:334-350) */
-void ref_csr_spmv_serial(void * h, double * x, double * y)
+void ref_csr_spmv_serial(void * h, ValueType * x, ValueType * y)
 {
 	CSRArrays * csr = (CSRArrays *) h;
 	subkernel_csr_scalar(csr, x, y, 0, csr->m);

@@ -38,6 +38,34 @@ void oracle_csr_spmv_scalar(const int32_t *row_ptr, const int32_t *col_ind, cons
 	}
 }
 
+/* The same kernel in the reference's `_f` build (make.sh:215-216: ValueType = float; the plugin's constructor narrows the
+ * double matrix values with a C cast, K/csr.cpp:58-167): float products, one float accumulator, ascending j. */
+void oracle_csr_spmv_scalar_f32(const int32_t *row_ptr, const int32_t *col_ind, const float *val,
+                                const float *x, float *y, int64_t i_s, int64_t i_e)
+{
+	int64_t j = row_ptr[i_s];
+	for (int64_t i = i_s; i < i_e; i++) {
+		int64_t j_e = row_ptr[i + 1];
+		float sum = 0;
+		for (; j < j_e; j++)
+			sum += val[j] * x[col_ind[j]];
+		y[i] = sum;
+	}
+}
+
+/* fp32 parity bound, per row: bound[i] = sum_j |a_ij * x_j| evaluated in double from the float operands. */
+void oracle_row_abs_bound_f32(const int32_t *row_ptr, const int32_t *col_ind, const float *val,
+                              const float *x, double *bound, int64_t m)
+{
+	#pragma omp parallel for schedule(static)
+	for (int64_t i = 0; i < m; i++) {
+		double s = 0;
+		for (int64_t j = row_ptr[i]; j < row_ptr[i + 1]; j++)
+			s += fabs((double)val[j] * (double)x[col_ind[j]]);
+		bound[i] = s;
+	}
+}
+
 /* The north-star per-row parity bound: bound[i] = sum_j |a_ij * x_j|  (BASELINE.md section 2). */
 void oracle_row_abs_bound(const int32_t *row_ptr, const int32_t *col_ind, const double *val,
                           const double *x, double *bound, int64_t m)

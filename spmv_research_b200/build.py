@@ -10,7 +10,7 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "lib")
-CU_SOURCES = ["capi.cu", "csr_kernel.cu", "sell_kernel.cu", "convert.cu", "partition.cu", "pcg.cu", "panels.cu", "amg_device.cu", "coo.cu"]
+CU_SOURCES = ["capi.cu", "csr_kernel.cu", "sell_kernel.cu", "convert.cu", "partition.cu", "pcg.cu", "panels.cu", "amg_device.cu", "coo.cu", "f32.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared", "--cudart", "static"]
 
@@ -26,7 +26,7 @@ def build_spmv(force=False, verbose=False):
     os.makedirs(LIB, exist_ok=True)
     so = os.path.join(LIB, "libb200spmv.so")
     srcs = [os.path.join(CSRC, f) for f in CU_SOURCES]
-    deps = srcs + [os.path.join(CSRC, f) for f in ("common.cuh", "amg_fill.h", "amg_fill_plan.h", "coo_sort.h")] + \
+    deps = srcs + [os.path.join(CSRC, f) for f in ("common.cuh", "amg_fill.h", "amg_fill_plan.h", "coo_sort.h", "f32_tile.h")] + \
            [os.path.join(HERE, "..", "include", f) for f in ("b200spmv.h", "b200amg.h")]
     if force or _stale(so, deps):
         nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")

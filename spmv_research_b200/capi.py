@@ -87,6 +87,11 @@ def lib():
         "b200spmv_bicgstab": (C.c_int, [vp, vp, vp, i64, vp, C.POINTER(PcgResult)]),
         "b200spmv_coo_to_csr": (C.c_int, [vp, vp, vp, i64, i64, i64, vp, vp, vp, C.POINTER(i64), vp]),
         "b200spmv_create_coo": (C.c_int, [C.POINTER(vp), vp, vp, vp, i64, i64, i64, C.POINTER(Opts)]),
+        "b200spmv_f32_create": (C.c_int, [C.POINTER(vp), vp, vp, vp, i64, i64, i64, i32]),
+        "b200spmv_f32_spmv_host": (C.c_int, [vp, vp, vp]),
+        "b200spmv_f32_spmv_device": (C.c_int, [vp, vp, vp, vp]),
+        "b200spmv_f32_time_device": (C.c_int, [vp, vp, vp, i32, i64, vp]),
+        "b200spmv_f32_destroy": (None, [vp]),
         "b200spmv_amg_fill_device": (C.c_int, [vp, vp, C.c_double, i64, i64, vp, vp, vp]),
         "b200spmv_last_error": (C.c_char_p, []),
         "b200spmv_version": (C.c_char_p, []),
@@ -234,6 +239,37 @@ def partition(sums, N, total, W, device=False):
     fn = lib().b200spmv_partition_device if device else lib().b200spmv_partition
     check(fn(_ptr(sums), int(N), int(total), int(W), out.ctypes.data))
     return out
+
+
+class HandleF32:
+    """Owns one b200spmv_f32_t* (the `_f` build of the CSR format: double matrix in, float vectors)."""
+
+    def __init__(self, row_ptr, col_ind, values, m, n, nnz, device=-1):
+        self._h = C.c_void_p()
+        self.m, self.n, self.nnz = int(m), int(n), int(nnz)
+        check(lib().b200spmv_f32_create(C.byref(self._h), _ptr(row_ptr), _ptr(col_ind), _ptr(values), self.m, self.n, self.nnz, device))
+
+    def close(self):
+        if self._h:
+            lib().b200spmv_f32_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def spmv_host(self, x, y):
+        check(lib().b200spmv_f32_spmv_host(self._h, _ptr(x), _ptr(y)))
+
+    def spmv_device(self, dx, dy, stream=None):
+        check(lib().b200spmv_f32_spmv_device(self._h, _ptr(dx), _ptr(dy), stream))
+
+    def time_device(self, dx, dy, iters, flush_bytes=0):
+        ms = (C.c_float * iters)()
+        check(lib().b200spmv_f32_time_device(self._h, _ptr(dx), _ptr(dy), iters, int(flush_bytes), ms))
+        return [float(v) for v in ms]
 
 
 def coo_to_csr_device(d_row, d_col, d_val, m, n, nnz, d_row_ptr, d_col_out, d_val_out, stream=None):

@@ -113,3 +113,55 @@ def coo_to_format(row, col, val, m, n, *, format=capi.CSR_ADAPTIVE, cache_x=Fals
     o = capi.default_opts(format=format, **opts)
     h = capi.Handle(row if nnz else None, col if nnz else None, val if nnz else None, m, n, nnz, o, coo=True)
     return MatrixFormat(h, format, cache_x=cache_x)
+
+
+class MatrixFormatF32:
+    """`struct Matrix_Format` of the reference's `_f` build (make.sh:215-216: ValueType = float): spmv(x, y) takes float32
+    vectors; the matrix was handed to csr_to_format_f32 as double (ValueTypeReference) and narrowed on the GPU."""
+
+    def __init__(self, handle):
+        self._h = handle
+        self.m, self.n, self.nnz = handle.m, handle.n, handle.nnz
+        self.format_name = "B200_CSR_F32"
+        self.mem_footprint = self.nnz * (4 + 4) + (self.m + 1) * 4          # K/csr.cpp:229 with sizeof(ValueType) = 4
+        self.csr_mem_footprint = self.nnz * (4 + 4) + (self.m + 1) * 4
+        self.gpu_launches_per_spmv = 2
+        self.num_loops = 0
+
+    def spmv(self, x, y):
+        if x.dtype != np.float32 or y.dtype != np.float32:
+            raise capi.B200Error("the _f build takes float32 vectors (ValueType = float)")
+        self._h.spmv_host(x, y)
+        self.num_loops += 1
+
+    def spmv_device(self, dx, dy, stream=None):
+        self._h.spmv_device(dx, dy, stream)
+
+    def statistics_start(self):
+        self.num_loops = 0
+
+    def statistics_print_data(self):
+        return ""
+
+    @property
+    def handle(self):
+        return self._h
+
+    def compulsory_bytes(self):
+        """fp32 compulsory bytes: 4 nnz (values) + 4 nnz (col_ind) + 4 (m+1) (row_ptr) + 4 n (x once) + 4 m (y)."""
+        return 8 * self.nnz + 4 * (self.m + 1) + 4 * self.n + 4 * self.m
+
+    def close(self):
+        self._h.close()
+
+
+def csr_to_format_f32(row_ptr, col_ind, values, m, n, nnz, symmetric=0, symmetry_expanded=0, *, device=-1):
+    """csr_to_format of the `_f` build: same arguments (values are DOUBLE, ValueTypeReference), CSR only."""
+    if symmetric and not symmetry_expanded:
+        raise capi.B200Error("symmetric matrices have to be expanded to be supported by this format")
+    row_ptr = np.ascontiguousarray(row_ptr, np.int32)
+    col_ind = np.ascontiguousarray(col_ind, np.int32)
+    values = np.ascontiguousarray(values, np.float64)
+    if row_ptr.size != m + 1 or col_ind.size < nnz or values.size < nnz:
+        raise capi.B200Error("CSR array sizes do not match m / nnz")
+    return MatrixFormatF32(capi.HandleF32(row_ptr, col_ind if nnz else None, values if nnz else None, m, n, nnz, device))

@@ -1,6 +1,8 @@
 """Pins the CPU oracle (oracle/spmv_oracle.c): against the committed golden fixture made from the
 reference's own code (tests/golden/make_golden.py) and, when oracle/_ref is present, against that
 code directly on random cases with empty rows, duplicate prefix sums and ragged tails."""
+import os
+
 import numpy as np
 import pytest
 
@@ -260,3 +262,29 @@ def test_sorted_sell_vs_reference(oracle):
                 assert np.array_equal(y, oracle.sell_plain_spmv(P, x)[:m])
     finally:
         oracle.set_threads(t0)
+
+
+def test_fp32_serial_csr_vs_reference_f_build(oracle):
+    """oracle_csr_spmv_scalar_f32 against the reference's `_f` build of K/csr.cpp (ValueType = float,
+    make.sh:215-216) compiled unmodified into oracle/_ref/libref_csr_f.so -- the serial kernel bit for bit (float products,
+    one float accumulator, ascending j, double values narrowed by the constructor's cast), and the OpenMP product, which is
+    the same kernel per thread range."""
+    if not oracle.ref_available() or not os.path.exists(os.path.join(os.path.dirname(oracle.__file__), "_ref", "libref_csr_f.so")):
+        pytest.skip("oracle/_ref/libref_csr_f.so not built")
+    rng = np.random.default_rng(11)
+    for m, n, per in [(1, 1, 1), (300, 500, 7), (5000, 4000, 40), (64, 100000, 3000)]:
+        lens = rng.integers(0, 2 * per + 1, m)
+        rp, col, val = M.csr_from_lengths(lens, n, 5)
+        val = val * 10.0 ** rng.integers(-6, 6, val.size)           # narrowing to float must round, not just truncate zeros
+        x = rng.uniform(-1, 1, n).astype(np.float32)
+        R = oracle.RefCSRf32(rp, col, val, n)
+        y_ser = np.full(m, 1.0, np.float32)
+        R.spmv_serial(x, y_ser)
+        y_omp = np.full(m, 1.0, np.float32)
+        R.spmv(x, y_omp)
+        y = oracle.csr_spmv_f32(rp, col, val, x)
+        assert y.dtype == np.float32
+        assert np.array_equal(y, y_ser) and np.array_equal(y, y_omp), (m, n, per)
+        b = oracle.row_abs_bound_f32(rp, col, val, x)
+        assert np.all(np.abs(y.astype(np.float64) - oracle.csr_spmv(rp, col, val.astype(np.float32).astype(np.float64), x.astype(np.float64)))
+                      <= (lens + 2) * 2.0 ** -24 * b + 1e-300)
