@@ -23,6 +23,11 @@
  *     B200SPMV_DEVICE   = CUDA device ordinal (default: current device)
  *     B200SPMV_SELL_C / B200SPMV_SELL_SIGMA   slice height / sort window (defaults 32 / 16384, sell_c_s.cpp:58-60)
  * Errors follow the reference: message on stderr and exit(1) (lib/debug.h:135); there is no CPU fallback.
+ *
+ * The `_f` build axis (make.sh:215-216: -D'DOUBLE=0' -D'ValueType=float', ValueTypeReference stays double): the same file
+ * compiles to the fp32 plugin over b200spmv_f32_* -- csr_to_format narrows the double values on the GPU, spmv takes float
+ * vectors and accumulates in float like K/csr.cpp:334-350 built `_f`.  CSR only (B200_FORMAT_SELL / _AUTO are refused at
+ * compile time); format name B200_CSR_ADAPTIVE_F32.  x and y move on every call (no flags in the f32 entry point).
  */
 #include <stdlib.h>
 #include <stdio.h>
@@ -39,6 +44,13 @@
 	#error "INT_T must be defined by the harness build (make.sh:166)"
 #endif
 
+#if !defined(DOUBLE)
+	#error "DOUBLE must be defined by the harness build (make.sh:212-216): 1 = _d, 0 = _f"
+#endif
+#if DOUBLE == 0 && (defined(B200_FORMAT_SELL) || defined(B200_FORMAT_AUTO))
+	#error "the fp32 (_f) build of the B200 plugin is CSR only"
+#endif
+
 static void
 b200_die(const char * what)
 {
@@ -46,6 +58,8 @@ b200_die(const char * what)
 	exit(1);
 }
 
+
+#if DOUBLE
 
 struct B200_Format : Matrix_Format
 {
@@ -117,6 +131,59 @@ B200_Format::spmv(ValueType * x, ValueType * y)
 		b200_die("spmv");
 	calls++;
 }
+
+
+#else    /* ---- the `_f` build ---- */
+
+struct B200_Format : Matrix_Format
+{
+	b200spmv_f32_t * handle;
+	long calls;
+	double stats[7];
+	double convert_ms;
+
+	B200_Format(INT_T * row_ptr, INT_T * col_ind, ValueTypeReference * values, long m, long n, long nnz) : Matrix_Format(m, n, nnz)
+	{
+		static_assert(sizeof(INT_T) == 4, "libb200spmv takes int32 indices (INT_T = int32_t)");
+		static_assert(sizeof(ValueType) == 4 && sizeof(ValueTypeReference) == 8, "this is the fp32 (_f) build: float vectors, double matrix input");
+		format_name = (char *) "B200_CSR_ADAPTIVE_F32";
+		int device = -1;
+		const char * e;
+		if ((e = getenv("B200SPMV_DEVICE")) != NULL)
+			device = atoi(e);
+		calls = 0;
+		handle = NULL;
+		if (b200spmv_f32_create(&handle, (const int32_t *) row_ptr, (const int32_t *) col_ind, (const double *) values, m, n, nnz, device))
+			b200_die("csr_to_format (f32)");
+		const long ntiles = (nnz + 2047) / 2048;
+		mem_footprint = (double) ntiles * 2048 * (sizeof(float) + sizeof(INT_T)) + (double) (m + 1) * sizeof(INT_T) + (double) ntiles * 12;    /* padded streams + row_ptr + tile_row / carry / tail */
+		memset(stats, 0, sizeof(stats));
+		stats[1] = ntiles;
+		stats[3] = nnz;
+		convert_ms = 0;
+	}
+
+	~B200_Format()
+	{
+		b200spmv_f32_destroy(handle);
+	}
+
+	void spmv(ValueType * x, ValueType * y);
+	void statistics_start();
+	int statistics_print_data(char * buf, long buf_n);
+};
+
+
+void
+B200_Format::spmv(ValueType * x, ValueType * y)
+{
+	if (b200spmv_f32_spmv_host(handle, (const float *) x, (float *) y))    /* returns synchronised: the harness host-times the call */
+		b200_die("spmv (f32)");
+	calls++;
+}
+
+
+#endif
 
 
 struct Matrix_Format *

@@ -3,6 +3,7 @@ built unmodified by oracle/Makefile into oracle/_ref/) with a format plugin, and
 
   spmv_b200_csr_d.exe / spmv_b200_sell_d.exe : the harness linked with host/b200_plugin.cpp over libb200spmv.so
   spmv_csr_d.exe                              : the harness with the reference's CPU CSR plugin (K/csr.cpp)
+  spmv_csr_f.exe / spmv_b200_csr_f.exe        : the `_f` build axis (make.sh:215-216) of the two, float vectors
 
 Environment variables are the ones run.sh exports.  The harness prints the CSV
 row on stderr (bench_spmv.cpp:484-487) and timing / accuracy lines on stdout.
@@ -59,6 +60,9 @@ def run(name, args, gpu_kernel, threads=None, extra_env=None, timeout=900):
     me = re.search(r"errors spmv: (.*)", p.stdout)
     if me:
         out["errors"] = {k: float(v) for k, v in (kv.split("=") for kv in me.group(1).split(", "))}
+    mf = re.search(r"Test failed! \(([0-9.eE+-]+)\)", p.stdout)
+    if mf:
+        out["max_rel_diff"] = float(mf.group(1))          # bench_spmv.cpp:198-199: printed only above epsilon (1e-10 `_d`, 1e-7 `_f`)
     rows = [ln for ln in p.stderr.splitlines() if ln.count(",") > 10]
     if rows:
         out["csv"] = rows[-1].split(",")

@@ -288,3 +288,26 @@ def test_fp32_serial_csr_vs_reference_f_build(oracle):
         b = oracle.row_abs_bound_f32(rp, col, val, x)
         assert np.all(np.abs(y.astype(np.float64) - oracle.csr_spmv(rp, col, val.astype(np.float32).astype(np.float64), x.astype(np.float64)))
                       <= (lens + 2) * 2.0 ** -24 * b + 1e-300)
+
+
+def test_reference_f_harness_error_level(oracle, tmp_path):
+    """The reference's harness built on its `_f` axis (DOUBLE=0, ValueType=float; oracle/_ref/spmv_csr_f.exe) with its own CPU
+    CSR plugin: runs, reports float-level errors against the _Float128 gold -- and trips its own 1e-7 relative criterion
+    (bench_spmv.cpp:116,198).  The fp32 oracle agrees with what it computes (same mae to the printed digits), which is the
+    level tests/test_zz_f32_device.py holds the GPU plugin to."""
+    from spmv_research_b200 import amg, refharness as RH
+    if not RH.available("spmv_csr_f.exe"):
+        pytest.skip("oracle/_ref/spmv_csr_f.exe not built (needs /root/reference at build time)")
+    p = amg.MatrixParams.parse("30000 30000 12 6 normal random 0.3 50 0.5 0.5 14")
+    rp, col, val = amg.generate(p)
+    path = str(tmp_path / "amg_30000.mtx")
+    RH.write_matrix_market(path, rp, col, val, p.cols)
+    r = RH.run("spmv_csr_f.exe", [path], gpu_kernel=False, threads=2)
+    assert r["returncode"] == 0, r["stderr"][-2000:]
+    assert any("Custom_CSR_B" in f for f in r["csv"]), r["csv"]
+    assert 1e-9 < r["errors"]["mae"] < 1e-5                      # float, not double (the `_d` build gives ~1e-16)
+    # the harness multiplies by x = ones (bench_spmv.cpp:598-606): the oracle's `_f` kernel gives the same mean absolute error
+    y32 = oracle.csr_spmv_f32(rp, col, val, np.ones(p.cols, np.float32)).astype(np.float64)
+    gold = np.array([np.sum(np.sort(val[rp[i]:rp[i + 1]].astype(np.float32).astype(np.float64))) for i in range(p.rows)])
+    mae = np.mean(np.abs(y32 - gold))
+    assert abs(mae - r["errors"]["mae"]) <= 0.02 * r["errors"]["mae"], (mae, r["errors"]["mae"])
