@@ -1,6 +1,6 @@
 #!/bin/bash
 # Round 2, first GPU pass: (1) the suite, (2) the tests written after round 1's GPU budget ran out (host_pipeline, device
-# generator, COO -> CSR), each file on its own so that one failure does not hide the others, (3) bench default vs
+# generator, COO -> CSR, fp32 product + _f harness), each file on its own so that one failure does not hide the others, (3) bench default vs
 # --host-pipeline (e2e), (4) the N=1 power member with the host and the device generator (generate_s), (5) ingest timings,
 # (6) launch list of the device generator + COO conversion.  One GPU.
 #   /usr/local/graft/bin/gpurun --timeout 2400 -- 'bash tools/gpu_round2a.sh'
@@ -8,7 +8,7 @@ O=gpurun_out/r02a
 mkdir -p $O
 SECONDS=0
 timeout 900 python -m pytest tests -m gpu -x -q > $O/pytest_gpu.log 2>&1; echo "pytest rc=$? t=${SECONDS}s" >> $O/pytest_gpu.log
-for t in host_pipeline amg_device coo_device; do
+for t in host_pipeline amg_device coo_device f32_device; do
 	B200SPMV_TEST_NEW=1 timeout 600 python -m pytest tests/test_zz_$t.py -m gpu -q > $O/pytest_new_$t.log 2>&1; echo "pytest $t rc=$? t=${SECONDS}s" >> $O/pytest_new_$t.log
 done
 timeout 600 python tools/run_ingest.py > $O/ingest.jsonl 2> $O/ingest.err; echo "ingest rc=$? t=${SECONDS}s" >> $O/ingest.err
