@@ -11,6 +11,7 @@ timeout 900 python -m pytest tests -m gpu -x -q > $O/pytest_gpu.log 2>&1; echo "
 for t in host_pipeline amg_device coo_device f32_device; do
 	B200SPMV_TEST_NEW=1 timeout 600 python -m pytest tests/test_zz_$t.py -m gpu -q > $O/pytest_new_$t.log 2>&1; echo "pytest $t rc=$? t=${SECONDS}s" >> $O/pytest_new_$t.log
 done
+timeout 600 python tools/run_f32.py > $O/f32_vs_f64.jsonl 2> $O/f32_vs_f64.err; echo "f32 rc=$? t=${SECONDS}s" >> $O/f32_vs_f64.err
 timeout 600 python tools/run_ingest.py > $O/ingest.jsonl 2> $O/ingest.err; echo "ingest rc=$? t=${SECONDS}s" >> $O/ingest.err
 timeout 900 python bench.py --steps 20 --warmup 3 > $O/bench_n1.json 2> $O/bench_n1.err; echo "bench rc=$? t=${SECONDS}s" >> $O/bench_n1.err
 timeout 900 python bench.py --steps 20 --warmup 3 --host-pipeline --no-cpu-baseline > $O/bench_n1_pipeline.json 2> $O/bench_n1_pipeline.err; echo "bench pipeline rc=$? t=${SECONDS}s" >> $O/bench_n1_pipeline.err
