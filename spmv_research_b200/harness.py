@@ -63,6 +63,36 @@ def medium_dataset():
     return out
 
 
+def validation_twins_range(samples=10, percentage=30):
+    """BASELINE config 3: the 3 637 parameter lines of the reference's validation_matrices_10_samples_30_range_twins.txt, in
+    the file's order.  The file is an expansion (matrix_generation_parameters/create_validation_twins_param_file.py): for each of
+    the 52 twins, `samples` scalings in [1 - percentage %, 1 + percentage %] applied to one feature at a time -- rows and cols
+    together (truncated), then avg, std, bw, skew, neigh, crs (rounded to 5 decimals) -- with repeated lines dropped.  Stored as
+    the 52 base lines (params/validation_twins_rounded.txt), not as the expansion; tests/test_amg.py checks it line by line
+    against the reference's file when /root/reference is present.  Returns [(MatrixParams, text line)]."""
+    base = load_param_file(os.path.join(_HERE, "params", "validation_twins_rounded.txt"))
+    scale = np.linspace(1 - percentage * 0.01, 1 + percentage * 0.01, num=samples)
+    out, seen = [], set()
+
+    def emit(rows, cols, f, name):
+        text = " ".join(str(v) for v in (rows, cols, f[0], f[1], "normal", "random", f[2], f[3], f[4], f[5], 14))
+        if text not in seen:
+            seen.add(text)
+            out.append((amg.MatrixParams(rows, cols, float(f[0]), float(f[1]), "normal", "random", float(f[2]), float(f[3]), float(f[4]),
+                                         float(f[5]), 14, name), text))
+
+    for b in base:
+        f = [np.float64(v) for v in (b.avg, b.std, b.bw, b.skew, b.neigh, b.crs)]
+        for x in scale:
+            emit(int(b.rows * x), int(b.cols * x), f, b.name)
+        for k in range(6):
+            for x in scale:
+                g = list(f)
+                g[k] = np.round(f[k] * x, 5)
+                emit(b.rows, b.cols, g, b.name)
+    return out
+
+
 def footprint_class(p):
     """CSR footprint class of SURVEY 8d from the nominal nnz = rows x avg."""
     mb = (12 * p.rows * p.avg + 4 * (p.rows + 1)) / 2 ** 20

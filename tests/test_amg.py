@@ -83,3 +83,27 @@ def test_medium_dataset_grid_is_the_reference_file():
         pytest.skip("reference not mounted (authoring container only)")
     want = set(amg.MatrixParams.parse(l).line() for l in open(ref) if l.strip())
     assert want == set(p.line() for p in ds)
+
+
+TWINS_RANGE_SHA16 = "77a0d5396005bfcd"
+
+
+def test_validation_twins_range_is_the_reference_file():
+    """harness.validation_twins_range() (52 base lines expanded the way create_validation_twins_param_file.py does) is the
+    reference's validation_matrices_10_samples_30_range_twins.txt (BASELINE config 3), line by line and in order."""
+    import hashlib
+    import os
+    from spmv_research_b200 import harness as H
+    ds = H.validation_twins_range()
+    text = [t for _, t in ds]
+    assert len(ds) == 3637 and len(set(text)) == 3637                      # 52 x 7 x 10 minus the 3 repeated lines
+    assert max(p.rows for p, _ in ds) > 70_000_000 and all(p.seed == 14 and p.rows >= 100 for p, _ in ds)
+    # fingerprint of the expansion (holds where the reference is not mounted, e.g. on the GPU box)
+    assert hashlib.sha256("\n".join(text).encode()).hexdigest()[:16] == TWINS_RANGE_SHA16
+    for p, t in ds[::97]:                                                   # the parsed parameters are the text's
+        q = amg.MatrixParams.parse(t)
+        assert (q.rows, q.cols, q.avg, q.std, q.bw, q.skew, q.neigh, q.crs) == (p.rows, p.cols, p.avg, p.std, p.bw, p.skew, p.neigh, p.crs)
+    ref = "/root/reference/matrix_generation_parameters/validation_matrices_10_samples_30_range_twins.txt"
+    if not os.path.exists(ref):
+        pytest.skip("reference not mounted (authoring container only)")
+    assert [" ".join(l.split()) for l in open(ref) if l.strip()] == text

@@ -37,6 +37,10 @@ def main():
     ap.add_argument("--check-every", type=int, default=50, help="oracle parity with random x on every N-th matrix (0 = never)")
     ap.add_argument("--generator", default="device", choices=["device", "host"])
     ap.add_argument("--iters", type=int, default=5)
+    ap.add_argument("--dataset", default="medium", choices=["medium", "twins_range"],
+                    help="medium: synthetic_matrices_medium_dataset.txt (config 2); twins_range: the 3 637 lines of "
+                         "validation_matrices_10_samples_30_range_twins.txt (config 3), harness.validation_twins_range()")
+    ap.add_argument("--max-nnz", type=float, default=1.6e9, help="skip lines whose nominal rows x avg exceeds this (int32 index space / HBM)")
     args = ap.parse_args()
     from oracle import oracle as O          # checker only
 
@@ -46,10 +50,12 @@ def main():
         peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
     except Exception:
         peak = 6650.0
-    lines = [p for i, p in enumerate(H.medium_dataset()) if i % args.stride == args.offset % args.stride]
+    dataset = H.medium_dataset() if args.dataset == "medium" else [p for p, _ in H.validation_twins_range()]
+    lines = [p for i, p in enumerate(dataset) if i % args.stride == args.offset % args.stride and p.rows * p.avg <= args.max_nnz]
+    # pass 1 depends on (rows, cols, avg, std, distribution, skew, seed) only: lines that share those share row_ptr
     groups = collections.OrderedDict()
     for p in lines:
-        groups.setdefault((p.rows, p.avg, p.skew), []).append(p)
+        groups.setdefault((p.rows, p.cols, p.avg, p.std, p.distribution, p.skew, p.seed), []).append(p)
     pool = cf.ThreadPoolExecutor(max_workers=max(1, (os.cpu_count() or 2) - 1))
     flush = 256 << 20
     t_start = time.time()
@@ -61,7 +67,7 @@ def main():
         t0 = time.time()
         rp, _ = amg.row_ptr(plist[0])                       # pass 1: shared by the whole group
         t_pass1 += time.time() - t0
-        m = n = plist[0].rows
+        m, n = plist[0].rows, plist[0].cols
         nnz = int(rp[-1])
         bws = [pool.submit(amg.bw_corrected, p, nnz) for p in plist]      # ctypes releases the GIL
         d_rp = torch.from_numpy(rp).to(dev)
@@ -124,7 +130,7 @@ def main():
         del d_rp, d_col, d_val, dx
         torch.cuda.empty_cache()
     # summary per footprint class
-    summ = {"summary": True, "lines_run": done, "lines_selected": len(lines), "dataset_lines": 16190, "stride": args.stride,
+    summ = {"summary": True, "lines_run": done, "lines_selected": len(lines), "dataset": args.dataset, "dataset_lines": len(dataset), "stride": args.stride,
             "generator": args.generator, "wall_s": round(time.time() - t_start, 1), "pass1_host_s": round(t_pass1, 1),
             "fill_s": round(t_fill, 1), "hbm_peak_GBs": peak, "stopped_early": stopped, "classes": {}}
     for cls in ("<32MB", "32-128MB", "128-512MB", ">=512MB", "all"):
