@@ -35,6 +35,30 @@ def build_spmv(force=False, verbose=False):
     return so
 
 
+# experimental builds of the same library (kernel variants behind compile-time switches of csr_kernel.cu), timed against
+# the shipped one by tools/sweep_exp.py on the GPU box; never loaded unless B200SPMV_LIB points at one
+EXPERIMENTS = {
+    "lds128": ["-DCSR_EXP_LDS128=1"],
+    "lpr2": ["-DCSR_EXP_MIN_LPR=2"],
+    "lpr4": ["-DCSR_EXP_MIN_LPR=4"],
+    "lpr8": ["-DCSR_EXP_MIN_LPR=8"],
+}
+
+
+def build_experiments(tags=None, force=False):
+    out = {}
+    exp_dir = os.path.join(LIB, "exp")
+    os.makedirs(exp_dir, exist_ok=True)
+    srcs = [os.path.join(CSRC, f) for f in CU_SOURCES]
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    for tag in (tags or sorted(EXPERIMENTS)):
+        so = os.path.join(exp_dir, "libb200spmv_%s.so" % tag)
+        if force or _stale(so, srcs + [os.path.join(CSRC, "common.cuh")]):
+            subprocess.check_call([nvcc] + NVCC_FLAGS + EXPERIMENTS[tag] + ["-o", so] + srcs)
+        out[tag] = so
+    return out
+
+
 def build_amg(force=False):
     from . import amg
     return amg.build(force)

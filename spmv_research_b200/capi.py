@@ -9,7 +9,9 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_HERE, "lib", "libb200spmv.so")
+# B200SPMV_LIB: another build of the same library (tools/sweep_exp.py times experimental kernel builds, lib/exp/*.so);
+# unset = the shipped library.  Still a CUDA library either way: no CPU path exists.
+SO_PATH = os.environ.get("B200SPMV_LIB") or os.path.join(_HERE, "lib", "libb200spmv.so")
 
 CSR_ADAPTIVE = 0
 SELL_C_SIGMA = 1

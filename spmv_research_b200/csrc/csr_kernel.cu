@@ -25,6 +25,20 @@
 //    reduction (long rows), whole CTA for split-row partials.
 #include "common.cuh"
 
+// Experiment switches for the row reduction (tools/sweep_exp.py builds extra libraries with them; the shipped library is
+// compiled with both at 0 and is then token for token the kernel measured in profiles/):
+//   CSR_EXP_LDS128  = 1: thread-per-row bins read the products two at a time (LDS.128 on even positions) -- same additions
+//                        in the same ascending-j order, half the shared-memory load instructions;
+//   CSR_EXP_MIN_LPR = 2 / 4 / 8: no thread-per-row bin; every tile reduces with at least that many lanes per row (lanes of a
+//                        row read adjacent products, so a half-warp touches few distinct rows: fewer bank conflicts, at the
+//                        price of log2(lanes) shuffles per row and of the sequential summation order).
+#ifndef CSR_EXP_LDS128
+#define CSR_EXP_LDS128 0
+#endif
+#ifndef CSR_EXP_MIN_LPR
+#define CSR_EXP_MIN_LPR 0
+#endif
+
 __device__ __forceinline__ double block_sum_range(const double * s_prod, int a, int b, double * s_red)
 {
 	double acc = 0.0;
@@ -138,7 +152,7 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 	// 5. row reduction, binned by rows owned
 	double nrm = 0.0;
 	const int rows_full = tail_split ? nrows - 1 : nrows;      // rows this tile completes
-	if (rows_full > CSR_THREADS / 2) {
+	if (CSR_EXP_MIN_LPR == 0 && rows_full > CSR_THREADS / 2) {
 		// thread per row: sequential ascending-j sum (the oracle's summation order)
 		for (int r = tid; r < rows_full; r += CSR_THREADS) {
 			const int i = R0 + r;
@@ -151,8 +165,20 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 				b = (int) (row_ptr[i + 1] - base);
 			}
 			double sum = 0.0;
+#if CSR_EXP_LDS128
+			if ((a & 1) && a < b)
+				sum += s_prod[a++];
+			for (; a + 1 < b; a += 2) {
+				const double2 v2 = *reinterpret_cast<const double2 *>(s_prod + a);      // even position: 16-byte aligned
+				sum += v2.x;
+				sum += v2.y;
+			}
+			if (a < b)
+				sum += s_prod[a];
+#else
 			for (; a < b; a++)
 				sum += s_prod[a];
+#endif
 			if constexpr (PLAIN) {
 				out.y[i] = sum;
 			} else if constexpr (MODE == 1) {
@@ -169,13 +195,23 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 		int lpr = 2;
 		while (lpr < 32 && rows_full * (lpr * 2) <= CSR_THREADS)
 			lpr *= 2;
+#if CSR_EXP_MIN_LPR
+		if (lpr < CSR_EXP_MIN_LPR)
+			lpr = CSR_EXP_MIN_LPR;
+#endif
 		const int groups = CSR_THREADS / lpr;
 		const int g = tid / lpr, lane = tid % lpr;
 		for (int rb = 0; rb < rows_full; rb += groups) {
 			const int r = rb + g;
 			double sum = 0.0;
 			if (r < rows_full) {
+#if CSR_EXP_MIN_LPR
+				// more than CSR_THREADS rows can reach this bin: the staged row_ptr slice covers the first CSR_THREADS
+				const int a = r < CSR_THREADS ? s_rp[r] : (int) (row_ptr[R0 + r] - base);
+				const int b = r < CSR_THREADS ? s_rp[r + 1] : (int) (row_ptr[R0 + r + 1] - base);
+#else
 				const int a = s_rp[r], b = s_rp[r + 1];
+#endif
 				for (int j = a + lane; j < b; j += lpr)
 					sum += s_prod[j];
 			}
