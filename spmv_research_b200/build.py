@@ -26,7 +26,7 @@ def build_spmv(force=False, verbose=False):
     os.makedirs(LIB, exist_ok=True)
     so = os.path.join(LIB, "libb200spmv.so")
     srcs = [os.path.join(CSRC, f) for f in CU_SOURCES]
-    deps = srcs + [os.path.join(CSRC, f) for f in ("common.cuh", "amg_fill.h", "amg_fill_plan.h", "coo_sort.h", "f32_tile.h")] + \
+    deps = srcs + [os.path.join(CSRC, f) for f in ("common.cuh", "amg_fill.h", "amg_fill_plan.h", "coo_sort.h", "f32_tile.h", "csr_perm.h")] + \
            [os.path.join(HERE, "..", "include", f) for f in ("b200spmv.h", "b200amg.h")]
     if force or _stale(so, deps):
         nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
@@ -42,6 +42,8 @@ EXPERIMENTS = {
     "lpr2": ["-DCSR_EXP_MIN_LPR=2"],
     "lpr4": ["-DCSR_EXP_MIN_LPR=4"],
     "lpr8": ["-DCSR_EXP_MIN_LPR=8"],
+    "perm": ["-DCSR_EXP_PERM=1"],                                  # conflict-free row -> thread table (csr_perm.h); y bit-identical
+    "perm_lds128": ["-DCSR_EXP_PERM=1", "-DCSR_EXP_LDS128=1"],
 }
 
 
@@ -53,7 +55,7 @@ def build_experiments(tags=None, force=False):
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     for tag in (tags or sorted(EXPERIMENTS)):
         so = os.path.join(exp_dir, "libb200spmv_%s.so" % tag)
-        if force or _stale(so, srcs + [os.path.join(CSRC, "common.cuh")]):
+        if force or _stale(so, srcs + [os.path.join(CSRC, "common.cuh"), os.path.join(CSRC, "csr_perm.h")]):
             subprocess.check_call([nvcc] + NVCC_FLAGS + EXPERIMENTS[tag] + ["-o", so] + srcs)
         out[tag] = so
     return out

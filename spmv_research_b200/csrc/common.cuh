@@ -170,6 +170,8 @@ struct b200spmv {
 	int32_t * d_split_tile;   // [nsplit]
 	double * d_tile_head;     // [ntiles] partial of a split row entering the tile
 	double * d_tile_tail;     // [ntiles] partial of a split row leaving the tile
+	uint16_t * d_perm;        // CSR_EXP_PERM builds only (csr_perm.h): thread slot -> tile-local row; null otherwise
+	int64_t * d_perm_off;     // [ntiles + 1] slot offsets
 
 	// SELL-C-sigma (device)
 	int C;

@@ -5,6 +5,12 @@
 //                  inside sigma windows), sellcs_format.c:137-200 (slice widths / pointers,
 //                  column-major padded slices, zero padding).
 #include "common.cuh"
+#ifndef CSR_EXP_PERM
+#define CSR_EXP_PERM 0
+#endif
+#if CSR_EXP_PERM
+#include "csr_perm.h"
+#endif
 
 // ---------------------------------------------------------------------------------------------
 // exclusive scan of int64, in place (three-phase, recursive over block sums)
@@ -186,7 +192,7 @@ __global__ void max_owned_rows_kernel(const int2 * __restrict__ tile_info, int64
 static void free_tile_plan(b200spmv * h)
 {
 	void ** ptrs[] = { (void **) &h->d_tile_row, (void **) &h->d_split_row, (void **) &h->d_split_tile, (void **) &h->d_tile_head,
-	                   (void **) &h->d_tile_tail };
+	                   (void **) &h->d_tile_tail, (void **) &h->d_perm, (void **) &h->d_perm_off };
 	for (void ** q : ptrs) {
 		if (*q)
 			cudaFree(*q);
@@ -295,6 +301,22 @@ static int plan_tiles_on(b200spmv * h)
 	}
 	CU(cudaStreamSynchronize(h->stream));
 	CU(cudaFree(d_flag));
+#if CSR_EXP_PERM
+	{
+		// experiment: row -> thread table of the thread-per-row bin, built on the host (csr_perm.h)
+		std::vector<int32_t> rp((size_t) h->m_plan + 1), ti((size_t) 2 * (h->ntiles + 1));
+		CU(cudaMemcpy(rp.data(), h->d_rp_plan, rp.size() * sizeof(int32_t), cudaMemcpyDeviceToHost));
+		CU(cudaMemcpy(ti.data(), h->d_tile_row, ti.size() * sizeof(int32_t), cudaMemcpyDeviceToHost));
+		std::vector<int64_t> off;
+		std::vector<uint16_t> perm;
+		csr_perm_build(rp.data(), ti.data(), h->ntiles, T, h->ext, off, perm);
+		CU(cudaMalloc(&h->d_perm_off, off.size() * sizeof(int64_t)));
+		CU(cudaMalloc(&h->d_perm, (perm.size() + 1) * sizeof(uint16_t)));
+		CU(cudaMemcpy(h->d_perm_off, off.data(), off.size() * sizeof(int64_t), cudaMemcpyHostToDevice));
+		if (!perm.empty())
+			CU(cudaMemcpy(h->d_perm, perm.data(), perm.size() * sizeof(uint16_t), cudaMemcpyHostToDevice));
+	}
+#endif
 	return 0;
 }
 

@@ -38,6 +38,19 @@
 #ifndef CSR_EXP_MIN_LPR
 #define CSR_EXP_MIN_LPR 0
 #endif
+//   CSR_EXP_PERM    = 1: thread-per-row bins take their rows through a per-tile table (csr_perm.h) in which lane b of every
+//                        half-warp only gets rows starting at a position = b (mod 16): every step of the row sums is free
+//                        of bank conflicts; y is bit-identical (same sequential sum per row, another thread computes it).
+#ifndef CSR_EXP_PERM
+#define CSR_EXP_PERM 0
+#endif
+#if CSR_EXP_PERM
+#define CSR_PERM_PARAMS , const uint16_t * __restrict__ perm, const int64_t * __restrict__ perm_off
+#define CSR_PERM_ARGS , h->d_perm, h->d_perm_off
+#else
+#define CSR_PERM_PARAMS
+#define CSR_PERM_ARGS
+#endif
 
 __device__ __forceinline__ double block_sum_range(const double * s_prod, int a, int b, double * s_red)
 {
@@ -66,7 +79,7 @@ __global__ void __launch_bounds__(CSR_THREADS, (NPT <= 4) ? 8 : ((NPT <= 8) ? 6 
 csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict__ col, const double * __restrict__ val,
                 const int2 * __restrict__ tile_info, const double * __restrict__ x,
                 double * __restrict__ tile_head, double * __restrict__ tile_tail,
-                int64_t nnz, int ext_cap, const int32_t * __restrict__ rowmap, int64_t tile_base, YOut out)
+                int64_t nnz, int ext_cap, const int32_t * __restrict__ rowmap, int64_t tile_base, YOut out CSR_PERM_PARAMS)
 {
 	constexpr bool PLAIN = (MODE == 0);
 	constexpr int T = CSR_THREADS * NPT;
@@ -154,7 +167,20 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 	const int rows_full = tail_split ? nrows - 1 : nrows;      // rows this tile completes
 	if (CSR_EXP_MIN_LPR == 0 && rows_full > CSR_THREADS / 2) {
 		// thread per row: sequential ascending-j sum (the oracle's summation order)
+#if CSR_EXP_PERM
+		const int64_t slot0 = perm_off[tile];
+		const int nslots = (int) (perm_off[tile + 1] - slot0);
+		const int nwork = nslots > 0 ? nslots : rows_full;         // no table for this tile: row = thread, as shipped
+		for (int sl = tid; sl < nwork; sl += CSR_THREADS) {
+			int r = sl;
+			if (nslots > 0) {
+				r = perm[slot0 + sl];
+				if (r == 0xFFFF)
+					continue;                           // a hole of the table: no row for this lane in this half-warp
+			}
+#else
 		for (int r = tid; r < rows_full; r += CSR_THREADS) {
+#endif
 			const int i = R0 + r;
 			int a, b;
 			if (r < CSR_THREADS) {
@@ -338,7 +364,7 @@ static int launch_tiles_impl(b200spmv * h, const double * dx, cudaStream_t st, c
 		return 0;
 	csr_tile_kernel<NPT, HINT, MODE><<<(unsigned) count, CSR_THREADS, smem, st>>>(
 		h->d_rp_plan, h->d_col, h->d_val, reinterpret_cast<const int2 *>(h->d_tile_row), dx,
-		h->d_tile_head, h->d_tile_tail, h->nnz, h->ext, h->compressed ? h->d_rows_nz : nullptr, first, out);
+		h->d_tile_head, h->d_tile_tail, h->nnz, h->ext, h->compressed ? h->d_rows_nz : nullptr, first, out CSR_PERM_ARGS);
 	CU_LAUNCH();
 	return 0;
 }

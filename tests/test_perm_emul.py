@@ -1,0 +1,101 @@
+"""csrc/csr_perm.h -- the row -> thread table of the CSR_EXP_PERM experiment (not in the shipped library) --
+checked on the CPU: for every tile of the thread-per-row bin each completed row appears in exactly one slot, and within every
+group of 16 slots (a half-warp) the non-empty rows start at 16 different positions mod 16, which is what makes each step of
+the row sums free of shared-memory bank conflicts.  tile_info is recomputed here the way tile_info_kernel (convert.cu) does."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import matrices as M
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+SRC = os.path.join(HERE, "emul", "perm_emul.cpp")
+HDR = os.path.join(HERE, "..", "spmv_research_b200", "csrc", "csr_perm.h")
+SO = os.path.join(HERE, "emul", "libperm_emul.so")
+T, EXT = 2048, 256
+
+
+def load():
+    if not os.path.exists(SO) or any(os.path.getmtime(d) > os.path.getmtime(SO) for d in (SRC, HDR)):
+        subprocess.check_call(["g++", "-O2", "-fPIC", "-shared", "-Wall", "-Wextra", "-o", SO, SRC])
+    L = C.CDLL(SO)
+    L.perm_emul_build.restype = C.c_int64
+    L.perm_emul_build.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int64]
+    return L
+
+
+def tile_info(rp, T):
+    m, nnz = len(rp) - 1, int(rp[-1])
+    ntiles = max(1, (nnz + T - 1) // T)
+    ti = np.zeros((ntiles + 1, 2), np.int32)
+    for t in range(ntiles):
+        R0 = 0 if t == 0 else int(np.searchsorted(rp[:m], t * T, side="left"))       # first row with row_ptr >= base (row_ptr[m] = nnz)
+        ti[t] = (R0, rp[R0])
+    ti[ntiles] = (m, nnz)
+    return ntiles, ti
+
+
+def cases():
+    rng = np.random.default_rng(11)
+    out = [("avg 10", M.csr_from_lengths(np.clip(rng.normal(10, 3.3, 60000).round(), 0, None).astype(np.int64), 60000, 1)[0]),
+           ("avg 5 + empties", M.csr_from_lengths(rng.integers(0, 11, 80000), 80000, 2)[0]),
+           ("all length 8 (every start = 0 mod 8)", M.csr_from_lengths(np.full(30000, 8), 30000, 3)[0]),
+           ("length 1 rows (2048 rows per tile)", M.csr_from_lengths(np.ones(20000, np.int64), 20000, 4)[0]),
+           ("mostly empty", M.csr_from_lengths((rng.random(200000) < 0.05).astype(np.int64) * 7, 200000, 5)[0]),
+           ("long rows (no thread-per-row tiles)", M.csr_from_lengths(np.full(500, 300), 5000, 6)[0]),
+           ("giant row inside short ones", M.csr_from_lengths(np.r_[rng.integers(1, 9, 3000), 9000, rng.integers(1, 9, 3000)], 20000, 7)[0])]
+    return out
+
+
+def test_perm_table_covers_rows_once_and_is_conflict_free():
+    L = load()
+    total_tpr = 0
+    stats = {}
+    for name, rp in cases():
+        tables = skipped = 0
+        rp = np.ascontiguousarray(rp, np.int32)
+        ntiles, ti = tile_info(rp, T)
+        off = np.zeros(ntiles + 1, np.int64)
+        cap = 4 * len(rp) + 64
+        perm = np.zeros(cap, np.uint16)
+        n = L.perm_emul_build(rp.ctypes.data, ti.ctypes.data, ntiles, T, EXT, off.ctypes.data, perm.ctypes.data, cap)
+        assert 0 <= n <= cap and off[0] == 0 and off[-1] == n and np.all(np.diff(off) >= 0) and np.all(off % 16 == 0), name
+        for t in range(ntiles):
+            R0, R1 = int(ti[t, 0]), int(ti[t + 1, 0])
+            nrows = R1 - R0
+            over = int(ti[t + 1, 1]) - (t * T + T)
+            rows_full = nrows - 1 if (nrows > 0 and over > EXT) else nrows
+            tab = perm[off[t]:off[t + 1]]
+            if rows_full <= 128:
+                assert tab.size == 0, (name, t)
+                continue
+            total_tpr += 1
+            if tab.size == 0:                      # lopsided start residues: the tile keeps the natural order
+                r = np.arange(R0, R0 + rows_full)
+                ne = r[rp[r + 1] > rp[r]]
+                longest = np.bincount((rp[ne] - t * T) & 15, minlength=16).max()
+                assert 2 * 16 * longest > 5 * rows_full - 2 * 16 * (rows_full // 16 + 1), (name, t)
+                skipped += 1
+                continue
+            tables += 1
+            rows = tab[tab != 0xFFFF].astype(np.int64)
+            assert np.array_equal(np.sort(rows), np.arange(rows_full)), (name, t)              # every completed row exactly once
+            for g in range(0, tab.size, 16):
+                grp = tab[g:g + 16]
+                r = grp[grp != 0xFFFF].astype(np.int64) + R0
+                ne = r[rp[r + 1] > rp[r]]
+                res = (rp[ne] - t * T) & 15
+                assert np.unique(res).size == res.size, (name, t, g)                             # 16 lanes, 16 different bank pairs
+                lanes = np.nonzero(grp != 0xFFFF)[0]
+                rr = grp[lanes].astype(np.int64) + R0
+                keep = rp[rr + 1] > rp[rr]
+                assert np.array_equal((rp[rr[keep]] - t * T) & 15, lanes[keep]), (name, t, g)    # lane b takes starts = b (mod 16)
+            # cost of the table: slots per completed row (1.0 = no holes)
+            assert 2 * tab.size <= 5 * rows_full, (name, t)
+        stats[name] = (tables, skipped)
+    assert total_tpr > 100
+    assert stats["all length 8 (every start = 0 mod 8)"][0] == 0                  # two residues only: never worth a table
+    assert stats["avg 10"][1] <= 0.05 * stats["avg 10"][0] and stats["avg 5 + empties"][1] <= 0.05 * stats["avg 5 + empties"][0]

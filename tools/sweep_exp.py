@@ -3,7 +3,8 @@
 The reduction stage costs the CSR kernel ~30 % over its stream + gather floor while a conflict-free shared-memory round
 trip costs 14 % (profiles/r01a_kexp_floors.txt): the difference is mostly bank conflicts of the thread-per-row
 reads.  spmv_research_b200/build.py::EXPERIMENTS compiles the same library with csr_kernel.cu's switches (LDS.128 pair
-reads; at least 2 / 4 / 8 lanes per row instead of thread per row); this tool runs each library in its own process
+reads; at least 2 / 4 / 8 lanes per row instead of thread per row; the conflict-free row -> thread table of csr_perm.h, whose
+y must be bit-identical to the shipped library's, as must the pair reads'); this tool runs each library in its own process
 (B200SPMV_LIB), checks y against the oracle's serial CSR kernel under the per-row bound, and times cold products.
 
   python tools/sweep_exp.py                 # parent: builds are expected in lib/exp/ (python -m ... build_experiments here)
@@ -44,7 +45,7 @@ def child(tag):
         MF.handle.time_device(dx, dy, 3, flush)
         ms = MF.handle.time_device(dx, dy, 25, flush)
         bc = H.compulsory_bytes(m, n, nnz)
-        print(json.dumps({"lib": tag, "matrix": ln, "parity": ok, "ms_med": round(float(np.median(ms)), 5), "ms_min": round(float(ms.min()), 5),
+        print(json.dumps({"lib": tag, "matrix": ln, "parity": ok, "y_fnv": int(O.fnv1a64(y)), "ms_med": round(float(np.median(ms)), 5), "ms_min": round(float(ms.min()), 5),
                           "eff_GBs": round(bc / float(np.median(ms)) * 1e-6, 1)}), flush=True)
         MF.close()
         del dx, dy
@@ -83,6 +84,7 @@ def main():
         tot = sum(min(r["ms_med"] for r in rs) for rs in mats.values())
         tot0 = sum(min(r["ms_med"] for r in base[k]) for k in mats if k in base)
         print(json.dumps({"summary": tag, "matrices": len(mats), "parity_all": all(r["parity"] for rs in mats.values() for r in rs),
+                          "y_bit_identical_to_shipped": all(r["y_fnv"] == base[k][0]["y_fnv"] for k, rs in mats.items() if k in base for r in rs),
                           "sum_ms": round(tot, 4), "vs_shipped": round(tot / tot0, 4) if tot0 else None,
                           "per_matrix_vs_shipped": {k: round(min(r["ms_med"] for r in rs) / min(r["ms_med"] for r in base[k]), 3)
                                                     for k, rs in mats.items() if k in base}}), flush=True)
