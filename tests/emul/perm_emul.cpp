@@ -4,11 +4,11 @@
 #include <string.h>
 
 extern "C" int64_t perm_emul_build(const int32_t * row_ptr, const int32_t * tile_info, int64_t ntiles, int T, int ext, int64_t * off_out,
-                                   uint16_t * perm_out, int64_t perm_cap)
+                                   uint16_t * perm_out, int64_t perm_cap, int64_t * stats4)
 {
 	std::vector<int64_t> off;
 	std::vector<uint16_t> perm;
-	csr_perm_build(row_ptr, tile_info, ntiles, T, ext, off, perm);
+	csr_perm_build(row_ptr, tile_info, ntiles, T, ext, off, perm, stats4);
 	memcpy(off_out, off.data(), off.size() * sizeof(int64_t));
 	if ((int64_t) perm.size() <= perm_cap && !perm.empty())
 		memcpy(perm_out, perm.data(), perm.size() * sizeof(uint16_t));
