@@ -33,6 +33,32 @@ def wavefronts(starts, lens):
     return int(total)
 
 
+def wavefronts_lpr(starts, lens):
+    """the lanes-per-row bins (rows_full <= 128): LPR adjacent lanes stride one row's products; returns (wavefronts, LPR)"""
+    rows = len(starts)
+    lpr = 2
+    while lpr < 32 and rows * (lpr * 2) <= 256:
+        lpr *= 2
+    tid = np.arange(256)
+    g, lane = tid // lpr, tid % lpr
+    ok = g < rows
+    a = np.where(ok, starts[np.minimum(g, rows - 1)], 0)
+    ln = np.where(ok, lens[np.minimum(g, rows - 1)], 0)
+    total = 0
+    for w in range(8):
+        sl = slice(32 * w, 32 * w + 32)
+        steps = int(np.ceil(ln[sl].max() / lpr)) if ln[sl].max() > 0 else 0
+        for k in range(steps):
+            j = lane[sl] + k * lpr
+            act = j < ln[sl]
+            pos = a[sl] + j
+            for h in range(2):
+                m = act[16 * h:16 * h + 16]
+                if m.any():
+                    total += np.bincount(pos[16 * h:16 * h + 16][m] & 15, minlength=16).max()
+    return int(total), lpr
+
+
 def y_lines(rows_global):
     """distinct 128-byte lines of y one warp-wide store touches, summed over the warps (rows_global: -1 = idle lane)"""
     n = len(rows_global)
@@ -56,11 +82,19 @@ def main():
         perm = np.zeros(4 * len(rp) + 64, np.uint16)
         st = np.zeros(4, np.int64)
         L.perm_emul_build(rp.ctypes.data, ti.ctypes.data, ntiles, T, EXT, off.ctypes.data, perm.ctypes.data, perm.size, st.ctypes.data)
-        w0 = w1 = nnz = tpr = slots = rows = y0 = y1 = 0
+        w0 = w1 = nnz = tpr = slots = rows = y0 = y1 = lw = lnnz = 0
+        lprs = []
         for t in rng.choice(ntiles - 1, size=min(200, ntiles - 1), replace=False):
             R0, R1 = int(ti[t, 0]), int(ti[t + 1, 0])
             rows_full = R1 - R0
             if rows_full <= 128:
+                if rows_full > 0 and int(ti[t + 1, 1]) - (t * T + T) <= EXT:
+                    a = rp[R0:R1].astype(np.int64) - t * T
+                    ln = np.diff(rp[R0:R1 + 1]).astype(np.int64)
+                    wl, lpr = wavefronts_lpr(a, ln)
+                    lw += wl
+                    lnnz += int(ln.sum())
+                    lprs.append(lpr)
                 continue
             tpr += 1
             a = rp[R0:R1].astype(np.int64) - t * T
@@ -80,8 +114,10 @@ def main():
                 y1 += y_lines(np.where(hole, -1, R0 + r))
                 slots += tab.size
             rows += rows_full
+        if lnnz:
+            print("%-64s lanes-per-row tiles %3d (LPR median %d): LDS wavefronts per 32 nnz %.2f (floor 2.00)"
+                  % (line, len(lprs), int(np.median(lprs)), 32.0 * lw / lnnz))
         if not tpr:
-            print("%-64s no thread-per-row tiles in the sample" % line)
             continue
         print("%-64s tiles %3d  rows/tile %5.1f  slots/row %.2f  LDS wavefronts per 32 nnz: shipped %.2f  perm %.2f (floor 2.00); y store lines per 32 nnz: shipped %.2f  perm %.2f; tables on %d of %d tiles"
               % (line, tpr, rows / tpr, slots / rows, 32.0 * w0 / nnz, 32.0 * w1 / nnz, 32.0 * y0 / nnz, 32.0 * y1 / nnz, st[1], st[0]))
