@@ -38,11 +38,15 @@
 #ifndef CSR_EXP_MIN_LPR
 #define CSR_EXP_MIN_LPR 0
 #endif
-//   CSR_EXP_PERM    = 1: thread-per-row bins take their rows through a per-tile table (csr_perm.h) in which lane b of every
-//                        half-warp only gets rows starting at a position = b (mod 16): every step of the row sums is free
-//                        of bank conflicts; y is bit-identical (same sequential sum per row, another thread computes it).
+//   CSR_EXP_PERM    = 1: the bins with 1 / 2 / 4 / 8 lanes per row take their rows through a per-tile table (csr_perm.h) in
+//                        which the rows of a half-warp start at positions whose bank windows cannot collide (thread per
+//                        row: lane b only gets rows starting at b mod 16): the row sums are free of bank conflicts; y is
+//                        bit-identical (the same lanes add the same products in the same order, elsewhere in the CTA).
 #ifndef CSR_EXP_PERM
 #define CSR_EXP_PERM 0
+#endif
+#if CSR_EXP_PERM && CSR_EXP_MIN_LPR
+#error "CSR_EXP_PERM replays the shipped binning rule (csr_perm_lpr): not with CSR_EXP_MIN_LPR"
 #endif
 #if CSR_EXP_PERM
 #define CSR_PERM_PARAMS , const uint16_t * __restrict__ perm, const int64_t * __restrict__ perm_off
@@ -227,8 +231,22 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 #endif
 		const int groups = CSR_THREADS / lpr;
 		const int g = tid / lpr, lane = tid % lpr;
-		for (int rb = 0; rb < rows_full; rb += groups) {
+#if CSR_EXP_PERM
+		// group slots through the tile's table (csr_perm.h): the groups of a half-warp then read disjoint bank windows
+		const int64_t gslot0 = perm_off[tile];
+		const int ngslots = (int) (perm_off[tile + 1] - gslot0);
+		const int nwork = ngslots > 0 ? ngslots : rows_full;
+#else
+		const int nwork = rows_full;
+#endif
+		for (int rb = 0; rb < nwork; rb += groups) {
+#if CSR_EXP_PERM
+			int r = rb + g;
+			if (ngslots > 0)
+				r = r < ngslots ? (int) perm[gslot0 + r] : 0xFFFF;      // a hole (0xFFFF) is >= rows_full: skipped below
+#else
 			const int r = rb + g;
+#endif
 			double sum = 0.0;
 			if (r < rows_full) {
 #if CSR_EXP_MIN_LPR

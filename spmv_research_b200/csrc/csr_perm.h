@@ -7,6 +7,7 @@
  * So, per tile: bucket the rows the tile completes by (row start - window base) mod 16; half-warp h takes the h-th row of
  * each bucket; buckets shorter than the longest leave holes, which the tile's EMPTY rows (they read nothing) fill first.
  * Whether a tile gets a table, and in which of two orders, is decided by a wavefront model (csr_perm_cost below).
+ * The bins with 2 / 4 / 8 lanes per row get the same treatment with groups of lanes in place of lanes (see csr_perm_build).
  * A tile then needs 16 * (longest bucket) slots instead of rows_full, and y is stored scattered over the tile's rows.
  * The sum of a row is the same sequential ascending-j sum whichever thread computes it: y is bit-identical to the shipped
  * kernel's.  Built on the host at create time (experiment only); plain C++ so that tests/ can check it without a GPU.
@@ -33,27 +34,40 @@ static inline int csr_perm_rows_full(const int32_t * tile_info, int64_t tile, in
 	return tail_split ? nrows - 1 : nrows;
 }
 
-/* Modelled L1 data-pipe wavefronts of one tile's row sums for a given slot order (slot -> tile-local row or HOLE):
- * per warp and per step j of its longest row, each half-warp costs the highest multiplicity of a bank pair
- * ((start + j) mod 16) among its active lanes (64-bit shared loads are served per half-warp); plus one wavefront per
- * distinct 128-byte line of y the warp's store touches. */
-static inline int64_t csr_perm_cost(const int32_t * row_ptr, int R0, int64_t base, const uint16_t * slot, size_t nslots)
+/* lanes per row of a tile that completes rows_full rows: the kernel's binning rule (csr_kernel.cu step 5), 1 = thread per row */
+static inline int csr_perm_lpr(int rows_full)
 {
+	if (rows_full > CSR_PERM_MIN_ROWS)
+		return 1;
+	int lpr = 2;
+	while (lpr < 32 && rows_full * (lpr * 2) <= 256)
+		lpr *= 2;
+	return lpr;
+}
+
+/* Modelled L1 data-pipe wavefronts of one tile's row sums for a given order of its GROUP slots (a group = lpr adjacent
+ * lanes summing one row, lane l reading positions start + l + k * lpr; slot -> tile-local row or HOLE): per warp and per
+ * step k of its longest row, each half-warp costs the highest multiplicity of a bank pair (position mod 16) among its active
+ * lanes (64-bit shared loads are served per half-warp); plus one wavefront per distinct 128-byte line of y the warp stores. */
+static inline int64_t csr_perm_cost(const int32_t * row_ptr, int R0, int64_t base, const uint16_t * slot, size_t nslots, int lpr)
+{
+	const size_t gw = 32 / lpr, gh = 16 / lpr;              /* groups per warp / per half-warp */
 	int64_t cost = 0;
-	for (size_t w = 0; w < nslots; w += 32) {
-		const size_t we = w + 32 < nslots ? w + 32 : nslots;
+	for (size_t w = 0; w < nslots; w += gw) {
+		const size_t we = w + gw < nslots ? w + gw : nslots;
 		int64_t a[32], len[32], steps = 0, lines[32];
 		int nl = 0;
 		for (size_t s = w; s < we; s++) {
-			const size_t l = s - w;
+			const size_t g = s - w;
 			if (slot[s] == CSR_PERM_HOLE) {
-				a[l] = len[l] = 0;
+				a[g] = len[g] = 0;
 				continue;
 			}
 			const int64_t i = R0 + (int64_t) slot[s];
-			a[l] = row_ptr[i] - base;
-			len[l] = row_ptr[i + 1] - row_ptr[i];
-			steps = len[l] > steps ? len[l] : steps;
+			a[g] = row_ptr[i] - base;
+			len[g] = row_ptr[i + 1] - row_ptr[i];
+			const int64_t st = (len[g] + lpr - 1) / lpr;
+			steps = st > steps ? st : steps;
 			const int64_t line = i >> 4;
 			int k = 0;
 			while (k < nl && lines[k] != line)
@@ -62,13 +76,16 @@ static inline int64_t csr_perm_cost(const int32_t * row_ptr, int R0, int64_t bas
 				lines[nl++] = line;
 		}
 		cost += nl;
-		for (int64_t j = 0; j < steps; j++)
-			for (size_t h = w; h < we; h += 16) {
+		for (int64_t k = 0; k < steps; k++)
+			for (size_t h = w; h < we; h += gh) {
 				int cnt[16] = {0}, mx = 0;
-				for (size_t s = h; s < h + 16 && s < we; s++)
-					if (len[s - w] > j) {
-						const int c = ++cnt[(a[s - w] + j) & 15];
-						mx = c > mx ? c : mx;
+				for (size_t s = h; s < h + gh && s < we; s++)
+					for (int l = 0; l < lpr; l++) {
+						const int64_t pos = l + k * lpr;
+						if (pos < len[s - w]) {
+							const int c = ++cnt[(a[s - w] + pos) & 15];
+							mx = c > mx ? c : mx;
+						}
 					}
 				cost += mx;
 			}
@@ -76,10 +93,14 @@ static inline int64_t csr_perm_cost(const int32_t * row_ptr, int R0, int64_t bas
 	return cost;
 }
 
-/* off: ntiles + 1 slot offsets (multiples of 16); perm: tile-local row of each slot or CSR_PERM_HOLE.
- * Per tile three orders are costed with csr_perm_cost -- the natural one (row = thread, no table), the bucket table with rows
- * in index order (y stores stay local) and with rows longest-first (half-warps of similar length) -- and the cheapest kept.
- * stats (optional, 4 entries): tiles of the bin, tiles given a table, modelled cost natural / chosen. */
+/* off: ntiles + 1 slot offsets; perm: tile-local row of each group slot or CSR_PERM_HOLE.
+ * With lpr lanes per row (1, 2, 4 or 8; bins with 16 or 32 are conflict-free as they are) a half-warp sums G = 16 / lpr rows
+ * and group windows of lpr adjacent bank pairs never collide when the G rows start at the same offset c = start mod lpr and
+ * at G different values of q = (start / lpr) mod G.  So the rows are bucketed by (c, q) -- for lpr = 1 simply start mod 16 --
+ * and half-warp h of class c takes the h-th row of each of its G buckets.
+ * Per tile three orders are costed with csr_perm_cost -- the natural one (no table), the bucket table with rows in index
+ * order (y stores stay local) and with rows longest-first (half-warps of similar length) -- and the cheapest kept.
+ * stats (optional, 4 entries): tiles considered, tiles given a table, modelled cost natural / chosen. */
 static inline void csr_perm_build(const int32_t * row_ptr, const int32_t * tile_info, int64_t ntiles, int T, int ext_cap,
                                   std::vector<int64_t> & off, std::vector<uint16_t> & perm, int64_t * stats = nullptr)
 {
@@ -93,56 +114,66 @@ static inline void csr_perm_build(const int32_t * row_ptr, const int32_t * tile_
 		int R0;
 		const int rows_full = csr_perm_rows_full(tile_info, t, T, ext_cap, &R0);
 		off[t] = (int64_t) perm.size();
-		if (rows_full <= CSR_PERM_MIN_ROWS || rows_full >= (int) CSR_PERM_HOLE)
-			continue;                                  /* other bins (or too many rows for 16-bit slots): no table, off[t+1] == off[t] */
+		if (rows_full < 1 || rows_full >= (int) CSR_PERM_HOLE)
+			continue;                                  /* nothing to order (or too many rows for 16-bit slots): off[t+1] == off[t] */
+		const int lpr = csr_perm_lpr(rows_full);
+		if (lpr > 8)
+			continue;                                  /* one row per half-warp or per warp: adjacent positions, no conflicts */
+		const int G = 16 / lpr;
 		const int64_t base = t * (int64_t) T;
 		for (int b = 0; b < 16; b++)
 			bucket[b].clear();
 		empties.clear();
-		size_t longest = 0;
 		for (int r = 0; r < rows_full; r++) {
-			const int64_t a = row_ptr[R0 + r], e = row_ptr[R0 + r + 1];
+			const int64_t a = row_ptr[R0 + r] - base, e = row_ptr[R0 + r + 1] - base;
 			if (a == e) {
 				empties.push_back(r);
 				continue;
 			}
-			std::vector<int> & B = bucket[(a - base) & 15];
-			B.push_back(r);
-			longest = B.size() > longest ? B.size() : longest;
+			bucket[(a % lpr) * G + (a / lpr) % G].push_back(r);
 		}
-		size_t holes = 0;
-		for (int b = 0; b < 16; b++)
-			holes += longest - bucket[b].size();
-		const size_t extra = empties.size() > holes ? (empties.size() - holes + 15) / 16 : 0;       /* half-warps of empty rows only */
+		size_t halfwarps = 0, holes = 0, H[8];
+		for (int c = 0; c < lpr; c++) {
+			H[c] = 0;
+			for (int q = 0; q < G; q++)
+				H[c] = bucket[c * G + q].size() > H[c] ? bucket[c * G + q].size() : H[c];
+			for (int q = 0; q < G; q++)
+				holes += H[c] - bucket[c * G + q].size();
+			halfwarps += H[c];
+		}
+		const size_t extra = empties.size() > holes ? (empties.size() - holes + G - 1) / G : 0;     /* half-warps of empty rows only */
 		cand[0].resize(rows_full);
 		for (int r = 0; r < rows_full; r++)
 			cand[0][r] = (uint16_t) r;
-		const bool table_ok = 16 * (longest + extra) <= 4 * (size_t) rows_full;                     /* bound the table's size */
-		for (int c = 1; c <= 2 && table_ok; c++) {
-			if (c == 2)
+		const bool table_ok = G * (halfwarps + extra) <= 4 * (size_t) rows_full;                    /* bound the table's size */
+		for (int v = 1; v <= 2 && table_ok; v++) {
+			if (v == 2)
 				for (int b = 0; b < 16; b++)
 					std::stable_sort(bucket[b].begin(), bucket[b].end(), [&](int p, int q) {
 						return row_ptr[R0 + p + 1] - row_ptr[R0 + p] > row_ptr[R0 + q + 1] - row_ptr[R0 + q];
 					});
-			cand[c].clear();
+			cand[v].clear();
 			size_t ne = 0;
-			for (size_t h = 0; h < longest + extra; h++)
-				for (int b = 0; b < 16; b++) {
-					uint16_t v = CSR_PERM_HOLE;
-					if (h < bucket[b].size())
-						v = (uint16_t) bucket[b][h];
-					else if (ne < empties.size())
-						v = (uint16_t) empties[ne++];
-					cand[c].push_back(v);
-				}
+			for (int c = 0; c <= lpr; c++) {               /* c == lpr: the extra half-warps (empty rows only) */
+				const size_t Hc = c < lpr ? H[c] : extra;
+				for (size_t h = 0; h < Hc; h++)
+					for (int q = 0; q < G; q++) {
+						uint16_t e = CSR_PERM_HOLE;
+						if (c < lpr && h < bucket[c * G + q].size())
+							e = (uint16_t) bucket[c * G + q][h];
+						else if (ne < empties.size())
+							e = (uint16_t) empties[ne++];
+						cand[v].push_back(e);
+					}
+			}
 		}
 		int best = 0;
 		int64_t cost[3];
-		cost[0] = csr_perm_cost(row_ptr, R0, base, cand[0].data(), cand[0].size());
-		for (int c = 1; c <= 2 && table_ok; c++) {
-			cost[c] = csr_perm_cost(row_ptr, R0, base, cand[c].data(), cand[c].size());
-			if (cost[c] < cost[best])
-				best = c;
+		cost[0] = csr_perm_cost(row_ptr, R0, base, cand[0].data(), cand[0].size(), lpr);
+		for (int v = 1; v <= 2 && table_ok; v++) {
+			cost[v] = csr_perm_cost(row_ptr, R0, base, cand[v].data(), cand[v].size(), lpr);
+			if (cost[v] < cost[best])
+				best = v;
 		}
 		st[0]++;
 		st[2] += cost[0];

@@ -1,7 +1,7 @@
 """csrc/csr_perm.h -- the row -> thread table of the CSR_EXP_PERM experiment (not in the shipped library) --
-checked on the CPU: for every tile given a table each completed row appears in exactly one slot, and within every
-group of 16 slots (a half-warp) the non-empty rows start at 16 different positions mod 16, which is what makes each step of
-the row sums free of shared-memory bank conflicts.  tile_info is recomputed here the way tile_info_kernel (convert.cu) does."""
+checked on the CPU: for every tile given a table each completed row appears in exactly one group slot, and the rows of every
+half-warp (16 / LPR group slots, LPR = lanes per row of the tile's bin) start at the same offset mod LPR and in different
+bank windows, which is what makes each step of the row sums free of shared-memory bank conflicts (replayed for a sample).  tile_info is recomputed here the way tile_info_kernel (convert.cu) does."""
 import ctypes as C
 import os
 import subprocess
@@ -46,14 +46,42 @@ def cases():
            ("length 1 rows (2048 rows per tile)", M.csr_from_lengths(np.ones(20000, np.int64), 20000, 4)[0]),
            ("mostly empty", M.csr_from_lengths((rng.random(200000) < 0.05).astype(np.int64) * 7, 200000, 5)[0]),
            ("long rows (no thread-per-row tiles)", M.csr_from_lengths(np.full(500, 300), 5000, 6)[0]),
+           ("avg 20 (2 lanes per row)", M.csr_from_lengths(np.clip(rng.normal(20, 6.7, 30000).round(), 0, None).astype(np.int64), 30000, 8)[0]),
+           ("avg 50 (4 lanes per row)", M.csr_from_lengths(np.clip(rng.normal(50, 16.7, 12000).round(), 0, None).astype(np.int64), 12000, 9)[0]),
+           ("avg 100 (8 lanes per row)", M.csr_from_lengths(np.clip(rng.normal(100, 33, 6000).round(), 0, None).astype(np.int64), 6000, 10)[0]),
            ("giant row inside short ones", M.csr_from_lengths(np.r_[rng.integers(1, 9, 3000), 9000, rng.integers(1, 9, 3000)], 20000, 7)[0])]
     return out
 
 
+def lpr_of(rows_full):
+    if rows_full > 128:
+        return 1
+    lpr = 2
+    while lpr < 32 and rows_full * (lpr * 2) <= 256:
+        lpr *= 2
+    return lpr
+
+
+def bank_conflicts(rp, R0, base, groups, lpr):
+    """highest multiplicity of a bank pair over all steps of one half-warp (groups: global rows of its G group slots)"""
+    worst = 0
+    steps = max([-(-int(rp[r + 1] - rp[r]) // lpr) for r in groups] + [0])
+    for k in range(steps):
+        cnt = np.zeros(16, np.int64)
+        for r in groups:
+            a, ln = int(rp[r]) - base, int(rp[r + 1] - rp[r])
+            for l in range(lpr):
+                if l + k * lpr < ln:
+                    cnt[(a + l + k * lpr) & 15] += 1
+        worst = max(worst, int(cnt.max()))
+    return worst
+
+
 def test_perm_table_covers_rows_once_and_is_conflict_free():
     L = load()
-    total_tpr = 0
+    total = 0
     stats = {}
+    seen_lpr = set()
     for name, rp in cases():
         tables = skipped = 0
         rp = np.ascontiguousarray(rp, np.int32)
@@ -63,38 +91,40 @@ def test_perm_table_covers_rows_once_and_is_conflict_free():
         perm = np.zeros(cap, np.uint16)
         st = np.zeros(4, np.int64)
         n = L.perm_emul_build(rp.ctypes.data, ti.ctypes.data, ntiles, T, EXT, off.ctypes.data, perm.ctypes.data, cap, st.ctypes.data)
-        assert 0 <= n <= cap and off[0] == 0 and off[-1] == n and np.all(np.diff(off) >= 0) and np.all(off % 16 == 0), name
+        assert 0 <= n <= cap and off[0] == 0 and off[-1] == n and np.all(np.diff(off) >= 0), name
         for t in range(ntiles):
             R0, R1 = int(ti[t, 0]), int(ti[t + 1, 0])
             nrows = R1 - R0
             over = int(ti[t + 1, 1]) - (t * T + T)
             rows_full = nrows - 1 if (nrows > 0 and over > EXT) else nrows
             tab = perm[off[t]:off[t + 1]]
-            if rows_full <= 128:
-                assert tab.size == 0, (name, t)
+            lpr = lpr_of(rows_full) if rows_full > 0 else 32
+            if rows_full < 1 or lpr > 8:
+                assert tab.size == 0, (name, t)               # nothing to order / conflict-free as it is
                 continue
-            total_tpr += 1
-            if tab.size == 0:                      # the wavefront model kept the natural order for this tile
+            total += 1
+            if tab.size == 0:                                  # the wavefront model kept the natural order for this tile
                 skipped += 1
                 continue
             tables += 1
+            seen_lpr.add(lpr)
+            G = 16 // lpr
+            assert tab.size % G == 0 and tab.size <= 4 * rows_full, (name, t)                     # whole half-warps, bounded size
             rows = tab[tab != 0xFFFF].astype(np.int64)
-            assert np.array_equal(np.sort(rows), np.arange(rows_full)), (name, t)              # every completed row exactly once
-            for g in range(0, tab.size, 16):
-                grp = tab[g:g + 16]
+            assert np.array_equal(np.sort(rows), np.arange(rows_full)), (name, t)                  # every completed row exactly once
+            for g in range(0, tab.size, G):
+                grp = tab[g:g + G]
                 r = grp[grp != 0xFFFF].astype(np.int64) + R0
                 ne = r[rp[r + 1] > rp[r]]
-                res = (rp[ne] - t * T) & 15
-                assert np.unique(res).size == res.size, (name, t, g)                             # 16 lanes, 16 different bank pairs
-                lanes = np.nonzero(grp != 0xFFFF)[0]
-                rr = grp[lanes].astype(np.int64) + R0
-                keep = rp[rr + 1] > rp[rr]
-                assert np.array_equal((rp[rr[keep]] - t * T) & 15, lanes[keep]), (name, t, g)    # lane b takes starts = b (mod 16)
-            assert tab.size <= 4 * rows_full, (name, t)                                       # bounded table size
+                a = rp[ne].astype(np.int64) - t * T
+                assert np.unique(a % lpr).size <= 1, (name, t, g)                                  # one offset class per half-warp
+                assert np.unique((a // lpr) % G).size == a.size, (name, t, g)                      # G different bank windows
+                if t % 7 == 0 and g % (5 * G) == 0:
+                    assert bank_conflicts(rp, R0, t * T, list(ne), lpr) <= 1, (name, t, g)         # ... hence no conflict at any step
         stats[name] = (tables, skipped)
         assert st[0] == tables + skipped and st[1] == tables and st[3] <= st[2], (name, st)       # never worse than natural, by the model
-        if name in ("avg 10", "avg 5 + empties"):
-            assert st[3] < 0.9 * st[2], (name, st)                     # modelled wavefronts (sums + y stores) drop by > 10 %
-    assert total_tpr > 100
+        if name in ("avg 10", "avg 5 + empties", "avg 20 (2 lanes per row)"):
+            assert st[3] < 0.9 * st[2], (name, st)                                               # modelled wavefronts (sums + y stores) drop by > 10 %
+    assert total > 300 and {1, 2, 4} <= seen_lpr
     assert stats["all length 8 (every start = 0 mod 8)"][0] == 0                  # two residues only: never worth a table
     assert stats["avg 10"][1] <= 0.05 * stats["avg 10"][0] and stats["avg 5 + empties"][1] <= 0.05 * stats["avg 5 + empties"][0]

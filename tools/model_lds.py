@@ -33,30 +33,34 @@ def wavefronts(starts, lens):
     return int(total)
 
 
-def wavefronts_lpr(starts, lens):
-    """the lanes-per-row bins (rows_full <= 128): LPR adjacent lanes stride one row's products; returns (wavefronts, LPR)"""
+def wavefronts_lpr(starts, lens, order=None):
+    """the lanes-per-row bins (rows_full <= 128): LPR adjacent lanes stride one row's products; `order` = the tile's table of
+    group slots (row or -1), default the natural order; returns (wavefronts, LPR, y store lines)"""
     rows = len(starts)
     lpr = 2
     while lpr < 32 and rows * (lpr * 2) <= 256:
         lpr *= 2
-    tid = np.arange(256)
-    g, lane = tid // lpr, tid % lpr
-    ok = g < rows
-    a = np.where(ok, starts[np.minimum(g, rows - 1)], 0)
-    ln = np.where(ok, lens[np.minimum(g, rows - 1)], 0)
-    total = 0
-    for w in range(8):
-        sl = slice(32 * w, 32 * w + 32)
-        steps = int(np.ceil(ln[sl].max() / lpr)) if ln[sl].max() > 0 else 0
+    order = np.arange(rows) if order is None else order
+    gw, gh = 32 // lpr, max(16 // lpr, 1)
+    total = ylines = 0
+    for w in range(0, len(order), gw):
+        grp = order[w:w + gw]
+        act_rows = grp[grp >= 0]
+        if act_rows.size == 0:
+            continue
+        ylines += np.unique((act_rows + 0) >> 4).size
+        steps = int(np.ceil(lens[act_rows].max() / lpr)) if lens[act_rows].max() > 0 else 0
         for k in range(steps):
-            j = lane[sl] + k * lpr
-            act = j < ln[sl]
-            pos = a[sl] + j
-            for h in range(2):
-                m = act[16 * h:16 * h + 16]
-                if m.any():
-                    total += np.bincount(pos[16 * h:16 * h + 16][m] & 15, minlength=16).max()
-    return int(total), lpr
+            for h in range(0, len(grp), gh):
+                cnt = np.zeros(16, np.int64)
+                for r in grp[h:h + gh]:
+                    if r < 0:
+                        continue
+                    pos = np.arange(lpr) + k * lpr
+                    pos = pos[pos < lens[r]]
+                    np.add.at(cnt, (starts[r] + pos) & 15, 1)
+                total += int(cnt.max())
+    return int(total), lpr, int(ylines)
 
 
 def y_lines(rows_global):
@@ -82,7 +86,7 @@ def main():
         perm = np.zeros(4 * len(rp) + 64, np.uint16)
         st = np.zeros(4, np.int64)
         L.perm_emul_build(rp.ctypes.data, ti.ctypes.data, ntiles, T, EXT, off.ctypes.data, perm.ctypes.data, perm.size, st.ctypes.data)
-        w0 = w1 = nnz = tpr = slots = rows = y0 = y1 = lw = lnnz = 0
+        w0 = w1 = nnz = tpr = slots = rows = y0 = y1 = lw = lw1 = ly0 = ly1 = lnnz = 0
         lprs = []
         for t in rng.choice(ntiles - 1, size=min(200, ntiles - 1), replace=False):
             R0, R1 = int(ti[t, 0]), int(ti[t + 1, 0])
@@ -91,8 +95,14 @@ def main():
                 if rows_full > 0 and int(ti[t + 1, 1]) - (t * T + T) <= EXT:
                     a = rp[R0:R1].astype(np.int64) - t * T
                     ln = np.diff(rp[R0:R1 + 1]).astype(np.int64)
-                    wl, lpr = wavefronts_lpr(a, ln)
+                    wl, lpr, yl = wavefronts_lpr(a, ln)
                     lw += wl
+                    ly0 += yl
+                    tab = perm[off[t]:off[t + 1]].astype(np.int64)
+                    if tab.size:
+                        wl, _, yl = wavefronts_lpr(a, ln, np.where(tab == 0xFFFF, -1, tab))
+                    lw1 += wl
+                    ly1 += yl
                     lnnz += int(ln.sum())
                     lprs.append(lpr)
                 continue
@@ -115,8 +125,8 @@ def main():
                 slots += tab.size
             rows += rows_full
         if lnnz:
-            print("%-64s lanes-per-row tiles %3d (LPR median %d): LDS wavefronts per 32 nnz %.2f (floor 2.00)"
-                  % (line, len(lprs), int(np.median(lprs)), 32.0 * lw / lnnz))
+            print("%-64s lanes-per-row tiles %3d (LPR median %d): LDS wavefronts per 32 nnz: shipped %.2f  perm %.2f (floor 2.00); y store lines: shipped %.2f  perm %.2f"
+                  % (line, len(lprs), int(np.median(lprs)), 32.0 * lw / lnnz, 32.0 * lw1 / lnnz, 32.0 * ly0 / lnnz, 32.0 * ly1 / lnnz))
         if not tpr:
             continue
         print("%-64s tiles %3d  rows/tile %5.1f  slots/row %.2f  LDS wavefronts per 32 nnz: shipped %.2f  perm %.2f (floor 2.00); y store lines per 32 nnz: shipped %.2f  perm %.2f; tables on %d of %d tiles"
