@@ -138,6 +138,25 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 		if (tid == 0 && npre == CSR_THREADS)
 			rp_pre2 = (int) (row_ptr[R0 + CSR_THREADS] - base);
 	}
+#if CSR_EXP_PERM
+	// the thread's first table entry travels with the stream loads (it would otherwise be a dependent global load right
+	// after the barrier): slot tid in the thread-per-row bin, slot tid / LPR in the lanes-per-row bins
+	const int64_t pslot0 = perm_off[tile];
+	const int pslots = (int) (perm_off[tile + 1] - pslot0);
+	int perm_pre = 0xFFFF;
+	{
+		const int rf = tail_split ? nrows - 1 : nrows;
+		int idx = tid;
+		if (rf <= CSR_THREADS / 2) {
+			int lp = 2;
+			while (lp < 32 && rf * (lp * 2) <= CSR_THREADS)
+				lp *= 2;
+			idx = tid / lp;
+		}
+		if (idx < pslots)
+			perm_pre = perm[pslot0 + idx];
+	}
+#endif
 
 	// 3. gathers and products -> shared memory in nnz order (conflict-free STS.64)
 	#pragma unroll
@@ -172,13 +191,13 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 	if (CSR_EXP_MIN_LPR == 0 && rows_full > CSR_THREADS / 2) {
 		// thread per row: sequential ascending-j sum (the oracle's summation order)
 #if CSR_EXP_PERM
-		const int64_t slot0 = perm_off[tile];
-		const int nslots = (int) (perm_off[tile + 1] - slot0);
+		const int64_t slot0 = pslot0;
+		const int nslots = pslots;
 		const int nwork = nslots > 0 ? nslots : rows_full;         // no table for this tile: row = thread, as shipped
 		for (int sl = tid; sl < nwork; sl += CSR_THREADS) {
 			int r = sl;
 			if (nslots > 0) {
-				r = perm[slot0 + sl];
+				r = sl == tid ? perm_pre : (int) perm[slot0 + sl];
 				if (r == 0xFFFF)
 					continue;                           // a hole of the table: no row for this lane in this half-warp
 			}
@@ -233,8 +252,8 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 		const int g = tid / lpr, lane = tid % lpr;
 #if CSR_EXP_PERM
 		// group slots through the tile's table (csr_perm.h): the groups of a half-warp then read disjoint bank windows
-		const int64_t gslot0 = perm_off[tile];
-		const int ngslots = (int) (perm_off[tile + 1] - gslot0);
+		const int64_t gslot0 = pslot0;
+		const int ngslots = pslots;
 		const int nwork = ngslots > 0 ? ngslots : rows_full;
 #else
 		const int nwork = rows_full;
@@ -243,7 +262,7 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 #if CSR_EXP_PERM
 			int r = rb + g;
 			if (ngslots > 0)
-				r = r < ngslots ? (int) perm[gslot0 + r] : 0xFFFF;      // a hole (0xFFFF) is >= rows_full: skipped below
+				r = rb == 0 ? perm_pre : (r < ngslots ? (int) perm[gslot0 + r] : 0xFFFF);      // a hole (0xFFFF) is >= rows_full: skipped below
 #else
 			const int r = rb + g;
 #endif
