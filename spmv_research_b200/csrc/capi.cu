@@ -417,7 +417,7 @@ static void free_handle(b200spmv * h)
 	for (cudaEvent_t e : h->up_ev)
 		if (e)
 			cudaEventDestroy(e);
-	void * ptrs[] = { h->d_row_ptr, h->d_col, h->d_val, h->d_tile_row, h->d_split_row, h->d_split_tile, h->d_tile_head, h->d_tile_tail, h->d_perm, h->d_perm_off,
+	void * ptrs[] = { h->d_row_ptr, h->d_col, h->d_val, h->d_tile_row, h->d_split_row, h->d_split_tile, h->d_tile_head, h->d_tile_tail, h->d_perm, h->d_perm_off, h->d_rot,
 	                  h->d_row_order, h->d_slice_width, h->d_slice_ptr, h->d_scol, h->d_sval, h->d_x, h->d_y, h->d_norm_partial,
 	                  h->d_sell_items, h->d_sell_cuts, h->d_sell_partial, h->d_rp_nz, h->d_rows_nz, h->d_empty_rows, h->d_diag };
 	for (void * p : ptrs)

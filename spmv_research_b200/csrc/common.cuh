@@ -172,6 +172,7 @@ struct b200spmv {
 	double * d_tile_tail;     // [ntiles] partial of a split row leaving the tile
 	uint16_t * d_perm;        // CSR_EXP_PERM builds only (csr_perm.h): thread slot -> tile-local row; null otherwise
 	int64_t * d_perm_off;     // [ntiles + 1] slot offsets
+	uint8_t * d_rot;          // CSR_EXP_ROT builds only (csr_perm.h): start rotation of each row's sum; null otherwise
 
 	// SELL-C-sigma (device)
 	int C;

@@ -8,7 +8,10 @@
 #ifndef CSR_EXP_PERM
 #define CSR_EXP_PERM 0
 #endif
-#if CSR_EXP_PERM
+#ifndef CSR_EXP_ROT
+#define CSR_EXP_ROT 0
+#endif
+#if CSR_EXP_PERM || CSR_EXP_ROT
 #include "csr_perm.h"
 #endif
 
@@ -192,7 +195,7 @@ __global__ void max_owned_rows_kernel(const int2 * __restrict__ tile_info, int64
 static void free_tile_plan(b200spmv * h)
 {
 	void ** ptrs[] = { (void **) &h->d_tile_row, (void **) &h->d_split_row, (void **) &h->d_split_tile, (void **) &h->d_tile_head,
-	                   (void **) &h->d_tile_tail, (void **) &h->d_perm, (void **) &h->d_perm_off };
+	                   (void **) &h->d_tile_tail, (void **) &h->d_perm, (void **) &h->d_perm_off, (void **) &h->d_rot };
 	for (void ** q : ptrs) {
 		if (*q)
 			cudaFree(*q);
@@ -315,6 +318,18 @@ static int plan_tiles_on(b200spmv * h)
 		CU(cudaMemcpy(h->d_perm_off, off.data(), off.size() * sizeof(int64_t), cudaMemcpyHostToDevice));
 		if (!perm.empty())
 			CU(cudaMemcpy(h->d_perm, perm.data(), perm.size() * sizeof(uint16_t), cudaMemcpyHostToDevice));
+	}
+#endif
+#if CSR_EXP_ROT
+	{
+		// experiment: start rotation of every row sum of the thread-per-row bin, built on the host (csr_perm.h)
+		std::vector<int32_t> rp((size_t) h->m_plan + 1), ti((size_t) 2 * (h->ntiles + 1));
+		CU(cudaMemcpy(rp.data(), h->d_rp_plan, rp.size() * sizeof(int32_t), cudaMemcpyDeviceToHost));
+		CU(cudaMemcpy(ti.data(), h->d_tile_row, ti.size() * sizeof(int32_t), cudaMemcpyDeviceToHost));
+		std::vector<uint8_t> rot;
+		csr_rot_build(rp.data(), ti.data(), h->ntiles, h->m_plan, T, h->ext, rot);
+		CU(cudaMalloc(&h->d_rot, rot.size()));
+		CU(cudaMemcpy(h->d_rot, rot.data(), rot.size(), cudaMemcpyHostToDevice));
 	}
 #endif
 	return 0;

@@ -48,9 +48,21 @@
 #if CSR_EXP_PERM && CSR_EXP_MIN_LPR
 #error "CSR_EXP_PERM replays the shipped binning rule (csr_perm_lpr): not with CSR_EXP_MIN_LPR"
 #endif
+//   CSR_EXP_ROT     = 1: thread-per-row bins keep row = thread but start each row at a per-row rotation (csr_perm.h,
+//                        csr_rot_build) chosen so that the 16 lanes of a half-warp collide least; wraps around the row.
+//                        No holes, y stays coalesced; the sum is a cyclic rotation of the ascending-j one (not bit-equal).
+#ifndef CSR_EXP_ROT
+#define CSR_EXP_ROT 0
+#endif
+#if CSR_EXP_PERM && CSR_EXP_ROT
+#error "CSR_EXP_PERM and CSR_EXP_ROT are alternative experiments"
+#endif
 #if CSR_EXP_PERM
 #define CSR_PERM_PARAMS , const uint16_t * __restrict__ perm, const int64_t * __restrict__ perm_off
 #define CSR_PERM_ARGS , h->d_perm, h->d_perm_off
+#elif CSR_EXP_ROT
+#define CSR_PERM_PARAMS , const uint8_t * __restrict__ rot
+#define CSR_PERM_ARGS , h->d_rot
 #else
 #define CSR_PERM_PARAMS
 #define CSR_PERM_ARGS
@@ -138,6 +150,12 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 		if (tid == 0 && npre == CSR_THREADS)
 			rp_pre2 = (int) (row_ptr[R0 + CSR_THREADS] - base);
 	}
+#if CSR_EXP_ROT
+	// the rotation of the thread's first row travels with the stream loads
+	int rot_pre = 0;
+	if (tid < nrows)
+		rot_pre = rot[R0 + tid];
+#endif
 #if CSR_EXP_PERM
 	// the thread's first table entry travels with the stream loads (it would otherwise be a dependent global load right
 	// after the barrier): slot tid in the thread-per-row bin, slot tid / LPR in the lanes-per-row bins
@@ -214,7 +232,15 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 				b = (int) (row_ptr[i + 1] - base);
 			}
 			double sum = 0.0;
-#if CSR_EXP_LDS128
+#if CSR_EXP_ROT
+			{
+				int idx = a + (r == tid ? rot_pre : (int) rot[i]);          // rotation < row length (0 for an empty row)
+				for (int j = a; j < b; j++) {
+					sum += s_prod[idx];
+					idx = (idx + 1 == b) ? a : idx + 1;
+				}
+			}
+#elif CSR_EXP_LDS128
 			if ((a & 1) && a < b)
 				sum += s_prod[a++];
 			for (; a + 1 < b; a += 2) {

@@ -188,3 +188,75 @@ static inline void csr_perm_build(const int32_t * row_ptr, const int32_t * tile_
 		for (int k = 0; k < 4; k++)
 			stats[k] = st[k];
 }
+
+/* ---------------------------------------------------------------------------------------------------------------------
+ * CSR_EXP_ROT -- second experiment on the same conflicts, thread-per-row bin only: rows keep their threads (y stays
+ * coalesced, no holes), but thread l starts its row at element phi_l and wraps around: at step j it reads
+ * s_prod[a_l + (j + phi_l) mod len_l].  phi is chosen per half-warp (16 consecutive tile-local rows), lane by lane, as the
+ * rotation that collides least with the lanes already placed, counted over every step (greedy).  The row sum becomes a
+ * cyclic rotation of the ascending-j sum: deterministic and inside the per-row bound, but no longer bit-equal to the
+ * sequential order.  rot: one byte per row of the plan's row space (0 outside the bin).  stats: modelled row-sum
+ * wavefronts natural / rotated.
+ */
+static inline void csr_rot_build(const int32_t * row_ptr, const int32_t * tile_info, int64_t ntiles, int64_t m, int T, int ext_cap,
+                                 std::vector<uint8_t> & rot, int64_t * stats = nullptr)
+{
+	rot.assign((size_t) (m > 0 ? m : 1), 0);
+	int64_t st[2] = {0, 0};
+	std::vector<int> occ;
+	for (int64_t t = 0; t < ntiles; t++) {
+		int R0;
+		const int rows_full = csr_perm_rows_full(tile_info, t, T, ext_cap, &R0);
+		if (rows_full <= CSR_PERM_MIN_ROWS)
+			continue;
+		const int64_t base = t * (int64_t) T;
+		for (int h = 0; h < rows_full; h += 16) {
+			const int he = h + 16 < rows_full ? h + 16 : rows_full;
+			int64_t steps = 0;
+			for (int r = h; r < he; r++) {
+				const int64_t len = row_ptr[R0 + r + 1] - row_ptr[R0 + r];
+				steps = len > steps ? len : steps;
+			}
+			if (steps == 0)
+				continue;
+			/* occ[j * 16 + bank pair]: lanes placed so far that read this bank pair at step j; nat: the same with phi = 0 */
+			occ.assign((size_t) steps * 32, 0);
+			int * nat = occ.data() + steps * 16;
+			for (int r = h; r < he; r++) {
+				const int64_t a = row_ptr[R0 + r] - base, len = row_ptr[R0 + r + 1] - row_ptr[R0 + r];
+				if (len == 0)
+					continue;
+				int best_phi = 0;
+				int64_t best = -1;
+				const int64_t tries = len < 16 ? len : 16;              /* rotations beyond 15 repeat the bank offsets */
+				for (int64_t p = 0; p < tries; p++) {
+					int64_t c = 0;
+					for (int64_t j = 0; j < len; j++)
+						c += occ[(size_t) j * 16 + ((a + (j + p) % len) & 15)];
+					if (best < 0 || c < best) {
+						best = c;
+						best_phi = (int) p;
+					}
+				}
+				rot[(size_t) R0 + r] = (uint8_t) best_phi;
+				for (int64_t j = 0; j < len; j++) {
+					occ[(size_t) j * 16 + ((a + (j + best_phi) % len) & 15)]++;
+					nat[(size_t) j * 16 + ((a + j) & 15)]++;
+				}
+			}
+			for (int64_t j = 0; j < steps; j++) {
+				int m0 = 0, m1 = 0;
+				for (int b = 0; b < 16; b++) {
+					m0 = nat[j * 16 + b] > m0 ? nat[j * 16 + b] : m0;
+					m1 = occ[(size_t) j * 16 + b] > m1 ? occ[(size_t) j * 16 + b] : m1;
+				}
+				st[0] += m0;
+				st[1] += m1;
+			}
+		}
+	}
+	if (stats) {
+		stats[0] = st[0];
+		stats[1] = st[1];
+	}
+}

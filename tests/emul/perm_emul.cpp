@@ -14,3 +14,11 @@ extern "C" int64_t perm_emul_build(const int32_t * row_ptr, const int32_t * tile
 		memcpy(perm_out, perm.data(), perm.size() * sizeof(uint16_t));
 	return (int64_t) perm.size();
 }
+
+extern "C" void rot_emul_build(const int32_t * row_ptr, const int32_t * tile_info, int64_t ntiles, int64_t m, int T, int ext, uint8_t * rot_out,
+                               int64_t * stats2)
+{
+	std::vector<uint8_t> rot;
+	csr_rot_build(row_ptr, tile_info, ntiles, m, T, ext, rot, stats2);
+	memcpy(rot_out, rot.data(), (size_t) (m > 0 ? m : 1));
+}

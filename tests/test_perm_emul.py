@@ -128,3 +128,48 @@ def test_perm_table_covers_rows_once_and_is_conflict_free():
     assert total > 300 and {1, 2, 4} <= seen_lpr
     assert stats["all length 8 (every start = 0 mod 8)"][0] == 0                  # two residues only: never worth a table
     assert stats["avg 10"][1] <= 0.05 * stats["avg 10"][0] and stats["avg 5 + empties"][1] <= 0.05 * stats["avg 5 + empties"][0]
+
+
+def test_rotation_table_is_valid_and_lowers_the_modelled_conflicts():
+    """CSR_EXP_ROT (csr_rot_build): every rotation is smaller than its row's length (0 for rows outside the thread-per-row
+    bin), and the wavefronts of the rotated reads -- recomputed here from the bank arithmetic -- are what the builder reports
+    and fewer than the natural order's; rows of one even length (stride-10 starts: a 2-way conflict) become conflict-free."""
+    L = load()
+    L.rot_emul_build.restype = None
+    L.rot_emul_build.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+    extra = [("all length 10", M.csr_from_lengths(np.full(30000, 10), 30000, 12)[0])]
+    for name, rp in cases()[:5] + extra:
+        rp = np.ascontiguousarray(rp, np.int32)
+        m = len(rp) - 1
+        ntiles, ti = tile_info(rp, T)
+        rot = np.zeros(max(m, 1), np.uint8)
+        st = np.zeros(2, np.int64)
+        L.rot_emul_build(rp.ctypes.data, ti.ctypes.data, ntiles, m, T, EXT, rot.ctypes.data, st.ctypes.data)
+        ln = np.diff(rp)
+        assert np.all(rot[:m] < np.maximum(ln, 1)), name
+        nat = got = 0
+        in_bin = np.zeros(m, bool)
+        for t in range(ntiles):
+            R0, R1 = int(ti[t, 0]), int(ti[t + 1, 0])
+            over = int(ti[t + 1, 1]) - (t * T + T)
+            rows_full = R1 - R0 - 1 if (R1 > R0 and over > EXT) else R1 - R0
+            if rows_full <= 128:
+                continue
+            in_bin[R0:R0 + rows_full] = True
+            if t % 5:
+                continue
+            for h in range(R0, R0 + rows_full, 16):
+                rows = np.arange(h, min(h + 16, R0 + rows_full))
+                a, l, ph = rp[rows].astype(np.int64) - t * T, ln[rows].astype(np.int64), rot[rows].astype(np.int64)
+                for j in range(int(l.max()) if l.size else 0):
+                    act = l > j
+                    nat += np.bincount((a[act] + j) & 15, minlength=16).max()
+                    got += np.bincount((a[act] + (j + ph[act]) % l[act]) & 15, minlength=16).max()
+        assert not rot[:m][~in_bin].any(), name
+        assert st[1] <= st[0], (name, st)
+        if nat:
+            assert got <= nat and abs(got / nat - st[1] / st[0]) < 0.05, (name, got, nat, st)      # the sample agrees with the builder's totals
+        if name in ("avg 10", "avg 5 + empties"):
+            assert st[1] < 0.7 * st[0], (name, st)
+        if name == "all length 10":
+            assert st[0] == 2 * st[1], (name, st)                                                 # 2-way conflict -> none

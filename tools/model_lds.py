@@ -5,6 +5,7 @@ for (a) the shipped order (row = thread) and (b) the CSR_EXP_PERM table (csr_per
 Prints wavefronts per 32 non-zeros; the ncu figure to compare with is 79 500 shared wavefronts per SM on the captured
 matrix = 9.5 per 32 non-zeros, 2 of which are the product stores (profiles/r01e_ncu_full_csr_tile_kernel_key_metrics.txt).
   python tools/model_lds.py ["generator line" ...]"""
+import ctypes as C
 import os
 import sys
 
@@ -16,12 +17,14 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 T, EXT = 2048, 256
 
 
-def wavefronts(starts, lens):
-    """starts / lens of the rows given to consecutive threads (-1 start = idle lane); returns LDS wavefronts"""
+def wavefronts(starts, lens, phi=None):
+    """starts / lens of the rows given to consecutive threads (-1 start = idle lane), optional start rotation of each row
+    (CSR_EXP_ROT); returns LDS wavefronts"""
     n = len(starts)
     pad = (-n) % 32
     a = np.r_[starts, np.full(pad, -1)].reshape(-1, 2, 16)            # warp, half-warp, lane
     ln = np.r_[lens, np.zeros(pad, np.int64)].reshape(-1, 2, 16)
+    ph = np.r_[phi if phi is not None else np.zeros(n, np.int64), np.zeros(pad, np.int64)].reshape(-1, 2, 16)
     total = 0
     steps = ln.reshape(len(a), -1).max(axis=1)                        # a warp runs until its longest row ends
     for w in range(len(a)):
@@ -29,7 +32,7 @@ def wavefronts(starts, lens):
             for h in range(2):
                 act = (ln[w, h] > j) & (a[w, h] >= 0)
                 if act.any():
-                    total += np.bincount((a[w, h][act] + j) & 15, minlength=16).max()
+                    total += np.bincount((a[w, h][act] + (j + ph[w, h][act]) % ln[w, h][act]) & 15, minlength=16).max()
     return int(total)
 
 
@@ -86,6 +89,12 @@ def main():
         perm = np.zeros(4 * len(rp) + 64, np.uint16)
         st = np.zeros(4, np.int64)
         L.perm_emul_build(rp.ctypes.data, ti.ctypes.data, ntiles, T, EXT, off.ctypes.data, perm.ctypes.data, perm.size, st.ctypes.data)
+        L.rot_emul_build.restype = None
+        rot = np.zeros(len(rp), np.uint8)
+        st2 = np.zeros(2, np.int64)
+        L.rot_emul_build(C.c_void_p(rp.ctypes.data), C.c_void_p(ti.ctypes.data), C.c_int64(ntiles), C.c_int64(len(rp) - 1), C.c_int(T), C.c_int(EXT),
+                         C.c_void_p(rot.ctypes.data), C.c_void_p(st2.ctypes.data))
+        w2 = 0
         w0 = w1 = nnz = tpr = slots = rows = y0 = y1 = lw = lw1 = ly0 = ly1 = lnnz = 0
         lprs = []
         for t in rng.choice(ntiles - 1, size=min(200, ntiles - 1), replace=False):
@@ -111,6 +120,7 @@ def main():
             ln = np.diff(rp[R0:R1 + 1]).astype(np.int64)
             nnz += int(ln.sum())
             w0 += wavefronts(a, ln)
+            w2 += wavefronts(a, ln, rot[R0:R1].astype(np.int64))
             y0 += y_lines(np.arange(R0, R1))
             tab = perm[off[t]:off[t + 1]].astype(np.int64)
             if tab.size == 0:
@@ -129,8 +139,8 @@ def main():
                   % (line, len(lprs), int(np.median(lprs)), 32.0 * lw / lnnz, 32.0 * lw1 / lnnz, 32.0 * ly0 / lnnz, 32.0 * ly1 / lnnz))
         if not tpr:
             continue
-        print("%-64s tiles %3d  rows/tile %5.1f  slots/row %.2f  LDS wavefronts per 32 nnz: shipped %.2f  perm %.2f (floor 2.00); y store lines per 32 nnz: shipped %.2f  perm %.2f; tables on %d of %d tiles"
-              % (line, tpr, rows / tpr, slots / rows, 32.0 * w0 / nnz, 32.0 * w1 / nnz, 32.0 * y0 / nnz, 32.0 * y1 / nnz, st[1], st[0]))
+        print("%-64s tiles %3d  rows/tile %5.1f  slots/row %.2f  LDS wavefronts per 32 nnz: shipped %.2f  perm %.2f  rot %.2f (floor 2.00); y store lines per 32 nnz: shipped %.2f  perm %.2f  rot %.2f; tables on %d of %d tiles"
+              % (line, tpr, rows / tpr, slots / rows, 32.0 * w0 / nnz, 32.0 * w1 / nnz, 32.0 * w2 / nnz, 32.0 * y0 / nnz, 32.0 * y1 / nnz, 32.0 * y0 / nnz, st[1], st[0]))
 
 
 if __name__ == "__main__":
