@@ -62,8 +62,9 @@ def main():
         if os.path.exists(so):
             libs[tag] = so
     res = {}
-    for rep in range(2):                          # two rounds, interleaved, so that drift of the box shows
-        for tag, so in libs.items():
+    order = list(libs.items()) + [("shipped", None)]      # the shipped library first and last, so that drift of the box shows
+    for rep, (tag, so) in enumerate(order):
+        if True:
             env = dict(os.environ)
             if so:
                 env["B200SPMV_LIB"] = so
@@ -76,10 +77,13 @@ def main():
                 continue
             for ln in out.stdout.splitlines():
                 r = json.loads(ln)
-                r["rep"] = rep
+                r["run"] = rep
                 print(json.dumps(r), flush=True)
                 res.setdefault(tag, {}).setdefault(r["matrix"], []).append(r)
     base = res.get("shipped", {})
+    if base and all(len(rs) > 1 for rs in base.values()):
+        print(json.dumps({"drift_shipped_last_over_first": round(sum(rs[-1]["ms_med"] for rs in base.values()) / sum(rs[0]["ms_med"] for rs in base.values()), 4)}),
+              flush=True)
     for tag, mats in res.items():
         tot = sum(min(r["ms_med"] for r in rs) for rs in mats.values())
         tot0 = sum(min(r["ms_med"] for r in base[k]) for k in mats if k in base)
