@@ -152,9 +152,11 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 	}
 #if CSR_EXP_ROT
 	// the rotation of the thread's first row travels with the stream loads
-	int rot_pre = 0;
+	int rot_pre = 0;                                   // low byte: row tid, next byte: row tid + CSR_THREADS (tiles of short rows)
 	if (tid < nrows)
 		rot_pre = rot[R0 + tid];
+	if (tid + CSR_THREADS < nrows)
+		rot_pre |= (int) rot[R0 + tid + CSR_THREADS] << 8;
 #endif
 #if CSR_EXP_PERM
 	// the thread's first table entry travels with the stream loads (it would otherwise be a dependent global load right
@@ -234,7 +236,7 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 			double sum = 0.0;
 #if CSR_EXP_ROT
 			{
-				int idx = a + (r == tid ? rot_pre : (int) rot[i]);          // rotation < row length (0 for an empty row)
+				int idx = a + (r == tid ? (rot_pre & 0xff) : (r == tid + CSR_THREADS ? (rot_pre >> 8) : (int) rot[i]));   // rotation < row length
 				for (int j = a; j < b; j++) {
 					sum += s_prod[idx];
 					idx = (idx + 1 == b) ? a : idx + 1;
