@@ -44,6 +44,7 @@ EXPERIMENTS = {
     "lpr8": ["-DCSR_EXP_MIN_LPR=8"],
     "perm": ["-DCSR_EXP_PERM=1"],                                  # conflict-free row -> thread table (csr_perm.h); y bit-identical
     "perm_lds128": ["-DCSR_EXP_PERM=1", "-DCSR_EXP_LDS128=1"],
+    "rot_perm": ["-DCSR_EXP_ROT=1", "-DCSR_EXP_PERM=1"],           # rotation in the thread-per-row bin + table in the lanes-per-row bins
     "rot": ["-DCSR_EXP_ROT=1"],                                    # per-row start rotation (csr_perm.h, csr_rot_build): no holes, y coalesced
 }
 

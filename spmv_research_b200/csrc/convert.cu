@@ -312,7 +312,7 @@ static int plan_tiles_on(b200spmv * h)
 		CU(cudaMemcpy(ti.data(), h->d_tile_row, ti.size() * sizeof(int32_t), cudaMemcpyDeviceToHost));
 		std::vector<int64_t> off;
 		std::vector<uint16_t> perm;
-		csr_perm_build(rp.data(), ti.data(), h->ntiles, T, h->ext, off, perm);
+		csr_perm_build(rp.data(), ti.data(), h->ntiles, T, h->ext, off, perm, nullptr, CSR_EXP_ROT != 0);
 		CU(cudaMalloc(&h->d_perm_off, off.size() * sizeof(int64_t)));
 		CU(cudaMalloc(&h->d_perm, (perm.size() + 1) * sizeof(uint16_t)));
 		CU(cudaMemcpy(h->d_perm_off, off.data(), off.size() * sizeof(int64_t), cudaMemcpyHostToDevice));

@@ -54,10 +54,11 @@
 #ifndef CSR_EXP_ROT
 #define CSR_EXP_ROT 0
 #endif
+// Both: rotation in the thread-per-row bin, table in the lanes-per-row bins (the table builder then skips the former).
 #if CSR_EXP_PERM && CSR_EXP_ROT
-#error "CSR_EXP_PERM and CSR_EXP_ROT are alternative experiments"
-#endif
-#if CSR_EXP_PERM
+#define CSR_PERM_PARAMS , const uint16_t * __restrict__ perm, const int64_t * __restrict__ perm_off, const uint8_t * __restrict__ rot
+#define CSR_PERM_ARGS , h->d_perm, h->d_perm_off, h->d_rot
+#elif CSR_EXP_PERM
 #define CSR_PERM_PARAMS , const uint16_t * __restrict__ perm, const int64_t * __restrict__ perm_off
 #define CSR_PERM_ARGS , h->d_perm, h->d_perm_off
 #elif CSR_EXP_ROT
@@ -150,32 +151,39 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 		if (tid == 0 && npre == CSR_THREADS)
 			rp_pre2 = (int) (row_ptr[R0 + CSR_THREADS] - base);
 	}
-#if CSR_EXP_ROT
-	// the rotation of the thread's first row travels with the stream loads
-	int rot_pre = 0;                                   // low byte: row tid, next byte: row tid + CSR_THREADS (tiles of short rows)
-	if (tid < nrows)
-		rot_pre = rot[R0 + tid];
-	if (tid + CSR_THREADS < nrows)
-		rot_pre |= (int) rot[R0 + tid + CSR_THREADS] << 8;
-#endif
+#if CSR_EXP_PERM || CSR_EXP_ROT
+	// The thread's first table entry / its rows' rotations travel with the stream loads (they would otherwise be dependent
+	// global loads right after the barrier).  One register: a tile uses either the rotations (thread-per-row bin: low byte
+	// row tid, next byte row tid + CSR_THREADS) or a table entry (slot tid there, slot tid / LPR in the lanes-per-row bins).
+	int meta_pre = 0xFFFF;
+	const bool tpr_bin = (tail_split ? nrows - 1 : nrows) > CSR_THREADS / 2;
 #if CSR_EXP_PERM
-	// the thread's first table entry travels with the stream loads (it would otherwise be a dependent global load right
-	// after the barrier): slot tid in the thread-per-row bin, slot tid / LPR in the lanes-per-row bins
 	const int64_t pslot0 = perm_off[tile];
 	const int pslots = (int) (perm_off[tile + 1] - pslot0);
-	int perm_pre = 0xFFFF;
-	{
+	if (!(CSR_EXP_ROT && tpr_bin)) {
 		const int rf = tail_split ? nrows - 1 : nrows;
 		int idx = tid;
-		if (rf <= CSR_THREADS / 2) {
+		if (!tpr_bin) {
 			int lp = 2;
 			while (lp < 32 && rf * (lp * 2) <= CSR_THREADS)
 				lp *= 2;
 			idx = tid / lp;
 		}
 		if (idx < pslots)
-			perm_pre = perm[pslot0 + idx];
+			meta_pre = perm[pslot0 + idx];
 	}
+#endif
+#if CSR_EXP_ROT
+	if (tpr_bin) {
+		meta_pre = 0;
+		if (tid < nrows)
+			meta_pre = rot[R0 + tid];
+		if (tid + CSR_THREADS < nrows)
+			meta_pre |= (int) rot[R0 + tid + CSR_THREADS] << 8;
+	}
+#endif
+#define perm_pre meta_pre
+#define rot_pre meta_pre
 #endif
 
 	// 3. gathers and products -> shared memory in nnz order (conflict-free STS.64)
@@ -210,7 +218,7 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 	const int rows_full = tail_split ? nrows - 1 : nrows;      // rows this tile completes
 	if (CSR_EXP_MIN_LPR == 0 && rows_full > CSR_THREADS / 2) {
 		// thread per row: sequential ascending-j sum (the oracle's summation order)
-#if CSR_EXP_PERM
+#if CSR_EXP_PERM && !CSR_EXP_ROT
 		const int64_t slot0 = pslot0;
 		const int nslots = pslots;
 		const int nwork = nslots > 0 ? nslots : rows_full;         // no table for this tile: row = thread, as shipped

@@ -100,9 +100,10 @@ static inline int64_t csr_perm_cost(const int32_t * row_ptr, int R0, int64_t bas
  * and half-warp h of class c takes the h-th row of each of its G buckets.
  * Per tile three orders are costed with csr_perm_cost -- the natural one (no table), the bucket table with rows in index
  * order (y stores stay local) and with rows longest-first (half-warps of similar length) -- and the cheapest kept.
- * stats (optional, 4 entries): tiles considered, tiles given a table, modelled cost natural / chosen. */
+ * stats (optional, 4 entries): tiles considered, tiles given a table, modelled cost natural / chosen.
+ * lanes_bins_only: leave the thread-per-row bin alone (the build that rotates those rows instead, CSR_EXP_ROT). */
 static inline void csr_perm_build(const int32_t * row_ptr, const int32_t * tile_info, int64_t ntiles, int T, int ext_cap,
-                                  std::vector<int64_t> & off, std::vector<uint16_t> & perm, int64_t * stats = nullptr)
+                                  std::vector<int64_t> & off, std::vector<uint16_t> & perm, int64_t * stats = nullptr, bool lanes_bins_only = false)
 {
 	off.assign(ntiles + 1, 0);
 	perm.clear();
@@ -117,7 +118,7 @@ static inline void csr_perm_build(const int32_t * row_ptr, const int32_t * tile_
 		if (rows_full < 1 || rows_full >= (int) CSR_PERM_HOLE)
 			continue;                                  /* nothing to order (or too many rows for 16-bit slots): off[t+1] == off[t] */
 		const int lpr = csr_perm_lpr(rows_full);
-		if (lpr > 8)
+		if (lpr > 8 || (lpr == 1 && lanes_bins_only))
 			continue;                                  /* one row per half-warp or per warp: adjacent positions, no conflicts */
 		const int G = 16 / lpr;
 		const int64_t base = t * (int64_t) T;
