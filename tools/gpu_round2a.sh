@@ -8,7 +8,7 @@ O=gpurun_out/r02a
 mkdir -p $O
 SECONDS=0
 timeout 900 python -m pytest tests -m gpu -x -q > $O/pytest_gpu.log 2>&1; echo "pytest rc=$? t=${SECONDS}s" >> $O/pytest_gpu.log
-for t in host_pipeline amg_device coo_device f32_device; do
+for t in host_pipeline amg_device coo_device f32_device plain_sell; do
 	B200SPMV_TEST_NEW=1 timeout 600 python -m pytest tests/test_zz_$t.py -m gpu -q > $O/pytest_new_$t.log 2>&1; echo "pytest $t rc=$? t=${SECONDS}s" >> $O/pytest_new_$t.log
 done
 timeout 600 python tools/run_f32.py > $O/f32_vs_f64.jsonl 2> $O/f32_vs_f64.err; echo "f32 rc=$? t=${SECONDS}s" >> $O/f32_vs_f64.err
