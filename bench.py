@@ -13,11 +13,14 @@ import json
 import os
 
 # torchrun sets OMP_NUM_THREADS=1; the host-side generator (OpenMP) should use this rank's share of the cores.
+# The reference arm (--impl reference) runs on rank 0 alone and gets ALL host cores: both arms then do the same work.
+import sys
 if int(os.environ.get("WORLD_SIZE", "1")) > 1 and os.environ.get("B200_KEEP_OMP") != "1":
-    os.environ["OMP_NUM_THREADS"] = str(max(1, (os.cpu_count() or 1) // int(os.environ.get("LOCAL_WORLD_SIZE", os.environ["WORLD_SIZE"]))))
+    _ref_arm = any(a == "reference" or a == "--impl=reference" for a in sys.argv[1:])
+    _share = 1 if _ref_arm else int(os.environ.get("LOCAL_WORLD_SIZE", os.environ["WORLD_SIZE"]))
+    os.environ["OMP_NUM_THREADS"] = str(max(1, (os.cpu_count() or 1) // _share))
 
 import subprocess
-import sys
 import threading
 import time
 
@@ -191,6 +194,20 @@ def workload_params(args, world):
     return wl, [H.config5(world, args.rows_per_gpu)]
 
 
+L2_NOTE = "inputs larger than the 126 MB L2 (every matrix / shard >= 320 MB, a step streams GBs); no explicit flush"
+
+
+def single_config(wl, plist, x):
+    """`config` of the N = 1 line: the same dict on the b200 arm and on the reference arm."""
+    return {"workload": wl, "matrices": len(plist), "lines": [p.line() for p in plist], "x": x, "l2": L2_NOTE}
+
+
+def power_config(p, rows_per_gpu, world):
+    """`config` of the N > 1 line (row-sharded power iteration): the same dict on both arms."""
+    return {"workload": "power_iteration config5-series", "line": p.line(), "rows_per_gpu": int(rows_per_gpu), "shards": int(world),
+            "x": "power iteration from x = 1", "l2": L2_NOTE}
+
+
 # ------------------------------------------------------------------------------------------------
 # N = 1: one SpMV of every matrix of the workload per step, everything resident in HBM
 # ------------------------------------------------------------------------------------------------
@@ -216,12 +233,14 @@ def run_single(args):
         rp, col, val = amg.generate(p)
         t_gen += time.time() - t0
         m, n, nnz = p.rows, p.cols, int(rp[-1])
+        t0 = time.time()
         MF = S.csr_to_format(rp, col, val, m, n, nnz, 0, 0, format=fmt, host_pipeline=(1 if args.host_pipeline else 0))
+        t_create = time.time() - t0
         MFo = [S.csr_to_format(rp, col, val, m, n, nnz, 0, 0, format=f) for f in others]
         x_h = np.ones(n) if args.x == "ones" else np.random.default_rng(14).uniform(-1, 1, n)
         dx = torch.from_numpy(x_h).to(dev)
         dy = torch.full((m,), 1.0, dtype=torch.float64, device=dev)
-        rec = dict(p=p, m=m, n=n, nnz=nnz, MF=MF, MFo=MFo, dx=dx, dy=dy, x_h=x_h, bc=H.compulsory_bytes(m, n, nnz))
+        rec = dict(p=p, m=m, n=n, nnz=nnz, MF=MF, MFo=MFo, dx=dx, dy=dy, x_h=x_h, bc=H.compulsory_bytes(m, n, nnz), create_s=t_create)
         # CPU baseline leg (rank 0, bounded: 1 warm-up + 3 timed calls per matrix) and a parity spot check
         if not args.no_cpu_baseline:
             from oracle import oracle as O
@@ -234,14 +253,19 @@ def run_single(args):
             cpu["t"] += time.time() - t0
             cpu["flops"] += 2.0 * nnz * cpu["iters"]
             cpu["kind"], cpu["cores"] = kind, cores
-            y_ser = O.csr_spmv(rp, col, val, x_h)
-            bound = O.row_abs_bound(rp, col, val, x_h)
-            y_gpu = np.full(m, 1.0)
-            MF.spmv(x_h, y_gpu)
-            ratio = float(np.max(np.abs(y_gpu - y_ser) / np.maximum(bound, 1e-300)))
-            cpu["max_err_over_bound"] = max(cpu["max_err_over_bound"], ratio)
-            if ratio > 1e-12:
-                raise SystemExit("bench.py: parity check failed on %s (err/bound %.3g)" % (p.line(), ratio))
+            # Parity leg: x ~ U[-1, 1) (seed 14) whatever the timed x is.  With x = 1 and the generator's dyadic 31-bit values
+            # every row sum is exact in any order and every gathered x equal, so that check could not fail.
+            x_par = np.random.default_rng(14).uniform(-1.0, 1.0, n)
+            y_ser = O.csr_spmv(rp, col, val, x_par)
+            bound = O.row_abs_bound(rp, col, val, x_par)
+            for F in [MF] + MFo:
+                y_gpu = np.full(m, 1.0)
+                F.spmv(x_par, y_gpu)
+                ratio = float(np.max(np.abs(y_gpu - y_ser) / (1e-12 * np.maximum(bound, 1e-300))))
+                cpu["max_err_over_bound"] = max(cpu["max_err_over_bound"], ratio)
+                if not ratio <= 1.0:
+                    raise SystemExit("bench.py: parity check failed on %s, %s (err / (1e-12 bound) = %.3g)" % (p.line(), F.format_name, ratio))
+            del x_par, y_ser, bound
         mats.append(rec)
         del rp, col, val
 
@@ -282,7 +306,8 @@ def run_single(args):
         st = r["MF"].handle.stats()
         per.append({"matrix": r["p"].line(), "format": r["MF"].format_name, "trial_ms": r["MF"].trial_ms, "nnz": r["nnz"], "ms": round(t, 5), "gflops": round(2.0 * r["nnz"] / t * 1e-6, 1),
                     "eff_GBs": round(r["bc"] / t * 1e-6, 1), "frac_of_measured": round(r["bc"] / t * 1e-6 / peak, 4),
-                    "launches": r["MF"].gpu_launches_per_spmv, "split_rows": int(st["nsplit"])})
+                    "launches": r["MF"].gpu_launches_per_spmv, "split_rows": int(st["nsplit"]),
+                    "convert_ms": round(float(st["convert_ms"]), 3), "csr_to_format_s": round(r["create_s"], 3)})
     launches = K * sum(r["MF"].gpu_launches_per_spmv for r in mats)
 
     # the other format, same protocol, reported beside (not the headline)
@@ -328,12 +353,13 @@ def run_single(args):
         "metric": METRIC, "value": round(gflops, 2), "unit": "GFLOP/s", "n_gpus": 1, "steps": K, "warmup": W,
         "ms_per_step": round(ms_step, 5), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic (reference artificial-matrix-generator restated bit-exactly, seed 14), x = %s" % args.x,
-        "config": {"workload": wl, "format": {S.AUTO: "B200_AUTO (per matrix: CSR-adaptive or SELL-C-sigma, picked by a device-timed trial inside csr_to_format)",
-                                                  S.CSR_ADAPTIVE: "B200_CSR_ADAPTIVE", S.SELL_C_SIGMA: "B200_SELL_C_SIGMA"}[fmt], "matrices": len(mats), "total_nnz": int(tot_nnz),
-                   "compulsory_bytes_per_step": int(tot_bc),
-                   "l2_note": "every matrix >= 320 MB CSR (> 126 MB L2) and a step streams %.1f GB, so nothing of a matrix survives "
-                              "in L2 between its uses; no explicit flush" % (tot_bc * 1e-9),
-                   "generate_s": round(t_gen, 1)},
+        "config": single_config(wl, plist, args.x),
+        "config_detail": {"format": {S.AUTO: "B200_AUTO (per matrix: CSR-adaptive or SELL-C-sigma, picked by a device-timed trial inside csr_to_format)",
+                                     S.CSR_ADAPTIVE: "B200_CSR_ADAPTIVE", S.SELL_C_SIGMA: "B200_SELL_C_SIGMA"}[fmt], "total_nnz": int(tot_nnz),
+                          "compulsory_bytes_per_step": int(tot_bc), "generate_s": round(t_gen, 1),
+                          "csr_to_format_s_total": round(sum(r["create_s"] for r in mats), 2),
+                          "csr_to_format_note": "format construction (upload + plan / conversion; AUTO adds two SELL conversions and 3 x 5 timed "
+                                                "trial products) is outside GFLOP/s, as in the reference harness (bench.cpp:600-633); per matrix in per_matrix[]"},
         "effective_GBs": round(eff, 1), "roofline_frac_nominal_8TBs": round(eff / NOMINAL_HBM_GBS, 4),
         "roofline": {"bound": "hbm", "kernel": {S.AUTO: "csr_tile_kernel / sell_kernel (per matrix, see per_matrix[].format)",
                                                 S.CSR_ADAPTIVE: "csr_tile_kernel", S.SELL_C_SIGMA: "sell_kernel"}[fmt],
@@ -345,7 +371,8 @@ def run_single(args):
     if not args.no_cpu_baseline and cpu["t"] > 0:
         out["cpu_baseline"] = {"value": round(cpu["flops"] / cpu["t"] * 1e-9, 3), "unit": "GFLOP/s", "cores": cpu["cores"], "kind": cpu["kind"],
                                "sample": "every matrix of the workload, 1 warm-up + %d timed calls each of the OpenMP CSR kernel" % cpu["iters"],
-                               "parity_max_err_over_bound": cpu["max_err_over_bound"]}
+                               "parity_max_err_over_1e-12_bound": cpu["max_err_over_bound"],
+                               "parity_note": "x ~ U[-1,1) seed 14, every format built (AUTO pick, CSR, SELL) vs the serial oracle, must be <= 1"}
     emit(out)
 
 
@@ -594,8 +621,8 @@ def run_power(args):
             "metric": METRIC, "value": round(gflops, 2), "unit": "GFLOP/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": round(ms_step, 5), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic (reference artificial-matrix-generator restated bit-exactly, seed 14), power iteration from x = 1",
-            "config": {"workload": "power_iteration config5-series: %s" % p.line(), "format": MF.format_name, "col_panels": MF.col_panels,
-                       "rows_per_gpu": args.rows_per_gpu,
+            "config": power_config(p, args.rows_per_gpu, world),
+            "config_detail": {"format": MF.format_name, "col_panels": MF.col_panels,
                        "total_nnz": int(nnz), "shard_rows": [int(b[1] - b[0]) for b in bounds], "exchange": {"mc": "fused: SpMV epilogue stores each y row once to an NVSwitch multicast address (NVLS) mapped over every rank's next-x buffer + NCCL scalar all-reduce",
                                     "p2p": "fused: SpMV epilogue stores y rows into every peer's next-x buffer over NVLink (CUDA IPC) + NCCL scalar all-reduce",
                                     "nccl": "NCCL in-place all-gather of y slots (one broadcast per owner) + scalar all-reduce"}[exchange],
@@ -644,47 +671,71 @@ def run_reference(args):
     from spmv_research_b200 import amg, harness as H
     wl, plist = workload_params(args, world)
     K, W = args.steps, args.warmup
-    items, sample = [], ""
-    if wl == "power":
-        p = plist[0]
-        rp, bw = amg.row_ptr(p)
-        from oracle import oracle as O
-        b = O.partition(world, rp, p.rows, int(rp[-1]))
-        i_s, i_e = int(b[0, 0]), int(b[0, 1])
-        col, val = amg.fill(p, rp, bw, i_s, i_e)
-        items.append(((rp[i_s:i_e + 1] - rp[i_s]).astype(np.int32), col, val, p.cols))
-        sample = "rank-0 row shard (1/%d of the rows, nnz-balanced) of %s; one SpMV per step" % (world, p.line())
-    else:
-        for p in plist:
-            rp, col, val = amg.generate(p)
-            items.append((rp, col, val, p.cols))
-        sample = "every matrix of the %s workload, one SpMV each per step (timed matrix by matrix, K calls each)" % wl
-    # One matrix at a time: the reference's CSR plugin keeps its per-thread row ranges in file-scope arrays
-    # (K/csr.cpp thread_i_s / thread_i_e), so a second csr_to_format() re-partitions EVERY live object; timing several
-    # objects in turn would run all of them on the last matrix's row ranges (an incomplete, far too fast product).
     from oracle import oracle as O
-    cores, kind, t, nnzs, verified = 0, "port", 0.0, [], True
-    for rp, col, val, n in items:
-        run, kind, cores = cpu_csr_runner(rp, col, val, n)
-        x, y = np.ones(n), np.full(len(rp) - 1, 1.0)
-        for _ in range(max(W, 1)):
-            run(x, y)
-        t0 = time.perf_counter()
-        for _ in range(K):
-            run(x, y)
-        t += (time.perf_counter() - t0) / K
-        nnzs.append(int(rp[-1]))
-        y_ser = O.csr_spmv(rp, col, val, x)
-        verified = verified and bool(np.all(np.abs(y - y_ser) <= 1e-12 * O.row_abs_bound(rp, col, val, x)))
+
+    def time_items(items_iter):
+        """One matrix (or row shard) at a time: the reference's CSR plugin keeps its per-thread row ranges in file-scope arrays
+        (K/csr.cpp thread_i_s / thread_i_e), so a second csr_to_format() re-partitions EVERY live object; timing several
+        objects in turn would run all of them on the last matrix's row ranges (an incomplete, far too fast product)."""
+        cores, kind, t, nnzs, ok = 0, "port", 0.0, [], True
+        for rp, col, val, n in items_iter:
+            run, kind, cores = cpu_csr_runner(rp, col, val, n)
+            x, y = np.ones(n), np.full(len(rp) - 1, 1.0)
+            for _ in range(max(W, 1)):
+                run(x, y)
+            t0 = time.perf_counter()
+            for _ in range(K):
+                run(x, y)
+            t += (time.perf_counter() - t0) / K
+            nnzs.append(int(rp[-1]))
+            xr = np.random.default_rng(14).uniform(-1.0, 1.0, n)          # verification with a random x (the timed x is ones)
+            run(xr, y)
+            y_ser = O.csr_spmv(rp, col, val, xr)
+            ok = ok and bool(np.all(np.abs(y - y_ser) <= 1e-12 * O.row_abs_bound(rp, col, val, xr)))
+            del run
+        return cores, kind, t, nnzs, ok
+
+    if wl == "power":
+        # The WHOLE N-GPU matrix on ALL host cores (the b200 arm's value is the aggregate over all shards): the row shards of
+        # the reference partitioner are generated and timed one after the other, their times summed -- one step = one product
+        # of the whole matrix.  Bounded: shards are taken in order until `budget_s` of wall time is spent (at least one, all of
+        # them on a box with >= 32 cores); value = 2 * (nnz of the shards timed) / (their summed time).
+        p = plist[0]
+        cfg = power_config(p, args.rows_per_gpu, world)
+        rp, bw = amg.row_ptr(p)
+        b = O.partition(world, rp, p.rows, int(rp[-1]))
+        budget_s, t_begin, done = float(os.environ.get("B200_REF_BUDGET_S", "240")), time.time(), []
+
+        def shards():
+            for q in range(world):
+                if q > 0 and time.time() - t_begin > budget_s:
+                    return
+                i_s, i_e = int(b[q, 0]), int(b[q, 1])
+                col, val = amg.fill(p, rp, bw, i_s, i_e)
+                done.append(q)
+                yield (rp[i_s:i_e + 1] - rp[i_s]).astype(np.int32), col, val, p.cols
+        cores, kind, t, nnzs, verified = time_items(shards())
+        t_scale = float(rp[-1]) / max(1.0, float(sum(nnzs)))          # 1.0 when every shard was timed
+        sample = "row shards %s of %d (reference partitioner, nnz-balanced) of %s, each timed on all %d host cores in turn, times summed; " \
+                 "one product per step" % (done, world, p.line(), cores)
+    else:
+        cfg = single_config(wl, plist, "ones")
+        t_scale = 1.0
+
+        def mats():
+            for p in plist:
+                rp, col, val = amg.generate(p)
+                yield rp, col, val, p.cols
+        cores, kind, t, nnzs, verified = time_items(mats())
+        sample = "every matrix of the %s workload, one SpMV each per step (timed matrix by matrix, K calls each)" % wl
     if not verified:
         raise SystemExit("bench.py --impl reference: the CPU kernel's y does not match the serial oracle")
-    runners = [(None, None, None, z) for z in nnzs]
-    flops = sum(2.0 * r[3] for r in runners)
+    flops = sum(2.0 * z for z in nnzs)
     val_ = round(flops / t * 1e-9, 3)
     emit({"impl": "reference", "metric": METRIC, "value": val_, "unit": "GFLOP/s", "n_gpus": world, "steps": K, "warmup": W,
-          "ms_per_step": round(t * 1e3, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+          "ms_per_step": round(t * t_scale * 1e3, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
           "data": "synthetic (same generator and parameter lines as the b200 arm)",
-          "config": {"workload": wl, "format": "Custom_CSR_B (reference OpenMP CSR, K/csr.cpp)"},
+          "config": cfg, "config_detail": {"format": "Custom_CSR_B (reference OpenMP CSR, K/csr.cpp)", "total_nnz_timed": int(sum(nnzs))},
           "cpu_baseline": {"value": val_, "unit": "GFLOP/s", "cores": cores, "kind": kind, "sample": sample,
                            "verified_against_serial_oracle": verified},
           "e2e": {"value": val_, "unit": "GFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})

@@ -38,12 +38,12 @@ def build_spmv(force=False, verbose=False):
 # experimental builds of the same library (kernel variants behind compile-time switches of csr_kernel.cu), timed against
 # the shipped one by tools/sweep_exp.py on the GPU box; never loaded unless B200SPMV_LIB points at one
 EXPERIMENTS = {
-    "lds128": ["-DCSR_EXP_LDS128=1"],
+    "nolds128": ["-DCSR_EXP_LDS128=0"],                            # round 1's shipped row sum (one LDS.64 per product)
     "lpr2": ["-DCSR_EXP_MIN_LPR=2"],
     "lpr4": ["-DCSR_EXP_MIN_LPR=4"],
     "lpr8": ["-DCSR_EXP_MIN_LPR=8"],
     "perm": ["-DCSR_EXP_PERM=1"],                                  # conflict-free row -> thread table (csr_perm.h); y bit-identical
-    "perm_lds128": ["-DCSR_EXP_PERM=1", "-DCSR_EXP_LDS128=1"],
+    "perm_nolds128": ["-DCSR_EXP_PERM=1", "-DCSR_EXP_LDS128=0"],
     "rot_perm": ["-DCSR_EXP_ROT=1", "-DCSR_EXP_PERM=1"],           # rotation in the thread-per-row bin + table in the lanes-per-row bins
     "rot": ["-DCSR_EXP_ROT=1"],                                    # per-row start rotation (csr_perm.h, csr_rot_build): no holes, y coalesced
 }

@@ -25,16 +25,16 @@
 //    reduction (long rows), whole CTA for split-row partials.
 #include "common.cuh"
 
-// Experiment switches for the row reduction (tools/sweep_exp.py builds extra libraries with them; the shipped library is
-// compiled with both at 0 and is then token for token the kernel measured in profiles/):
+// Experiment switches for the row reduction (tools/sweep_exp.py builds extra libraries with them; measured on a B200 in round 2,
+// profiles/r02c_sweep_exp_row_reduction.txt):
 //   CSR_EXP_LDS128  = 1: thread-per-row bins read the products two at a time (LDS.128 on even positions) -- same additions
 //                        in the same ascending-j order, half the shared-memory load instructions;
 //   CSR_EXP_MIN_LPR = 2 / 4 / 8: no thread-per-row bin; every tile reduces with at least that many lanes per row (lanes of a
 //                        row read adjacent products, so a half-warp touches few distinct rows: fewer bank conflicts, at the
 //                        price of log2(lanes) shuffles per row and of the sequential summation order).
 #ifndef CSR_EXP_LDS128
-#define CSR_EXP_LDS128 0
-#endif
+#define CSR_EXP_LDS128 1      // shipped since round 2: the only variant that won (-1 % on the sample, -4.5 % on config 1, y bit-identical;
+#endif                        // profiles/r02c_sweep_exp_row_reduction.txt).  MIN_LPR / PERM / ROT all measured slower or flat.
 #ifndef CSR_EXP_MIN_LPR
 #define CSR_EXP_MIN_LPR 0
 #endif

@@ -1,9 +1,8 @@
 """b200spmv_amg_fill_device: pass 2 of the synthetic generator on the GPU, bit-identical to the host generator
 (and so to the reference), whole matrices and row shards; the generated arrays feed b200spmv_create_device directly.
 
-Written after round 1's GPU budget was spent: the kernel's SOURCE is verified on the CPU (tests/test_amg_device_emul.py), the
-launch itself has not been seen on a B200 yet, so these run only with B200SPMV_TEST_NEW=1
-(`B200SPMV_TEST_NEW=1 python -m pytest tests/test_zz_amg_device.py -m gpu`)."""
+Green on a B200 since round 2's first GPU pass (profiles/r02a_pytest_new_paths.txt); the kernel source is also replayed on the CPU
+(tests/emul/)."""
 import os
 
 import numpy as np
@@ -12,8 +11,7 @@ import pytest
 import matrices as M
 from spmv_research_b200 import amg
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get("B200SPMV_TEST_NEW") != "1", reason="not yet verified on a B200 (set B200SPMV_TEST_NEW=1)")]
+pytestmark = [pytest.mark.gpu]
 
 LINES = list(M.GOLDEN_LINES) + [
     "5000 5000 20 6 normal simple 0.05 0 1.9 0.95 3",

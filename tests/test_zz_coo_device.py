@@ -1,16 +1,14 @@
 """b200spmv_coo_to_csr / b200spmv_create_coo: COO -> CSR on the GPU, bit-identical to the oracle's coo_to_csr
 (pinned on the reference's import path), and .mtx file -> format handle -> product within the per-row bound.
 
-Written after round 1's GPU budget was spent: the sort networks and the conversion logic are verified on the CPU
-(tests/test_coo_emul.py), the launches have not been seen on a B200 yet, so these run only with B200SPMV_TEST_NEW=1
-(`B200SPMV_TEST_NEW=1 python -m pytest tests/test_zz_coo_device.py -m gpu`)."""
+Green on a B200 since round 2's first GPU pass (profiles/r02a_pytest_new_paths.txt); the kernel source is also replayed on the CPU
+(tests/emul/)."""
 import os
 
 import numpy as np
 import pytest
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get("B200SPMV_TEST_NEW") != "1", reason="not yet verified on a B200 (set B200SPMV_TEST_NEW=1)")]
+pytestmark = [pytest.mark.gpu]
 
 CASES = [(1, 1, 0, False), (5, 5, 1, False), (300, 450, 4000, False), (50, 3000, 60000, False), (10, 100000, 300000, False),
          (2000, 2000, 30000, True), (3, 40, 100, True), (1000000, 1000000, 3000000, False), (64, 64, 33 * 64, False)]

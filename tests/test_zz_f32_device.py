@@ -2,15 +2,14 @@
 on the reference's `_f` build) under the fp32 per-row tolerance of tests/test_f32_emul.py, and BIT-EQUAL to the CPU replay of
 the kernel's own operation order (tests/emul/f32_emul.cpp).
 
-Written after round 1's GPU budget was spent: tile bookkeeping verified on the CPU, the launches not yet seen on a B200, so
-these run only with B200SPMV_TEST_NEW=1 (`B200SPMV_TEST_NEW=1 python -m pytest tests/test_zz_f32_device.py -m gpu`)."""
+Green on a B200 since round 2's first GPU pass (profiles/r02a_pytest_new_paths.txt); the kernel source is also replayed on the CPU
+(tests/emul/)."""
 import os
 
 import numpy as np
 import pytest
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get("B200SPMV_TEST_NEW") != "1", reason="not yet verified on a B200 (set B200SPMV_TEST_NEW=1)")]
+pytestmark = [pytest.mark.gpu]
 
 
 def test_f32_product_vs_oracle_and_replay(native, oracle, golden_matrices):

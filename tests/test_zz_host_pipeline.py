@@ -1,9 +1,8 @@
 """host_pipeline = 1: b200spmv_spmv_host uploads x range by range (the columns each unit range of rows references) on a
 third stream so that H2D overlaps D2H.  Same y as the default path and as the oracle.
 
-Written after round 1's GPU budget was spent: the code path is OFF by default (opts.host_pipeline = 0) and these tests run
-only with B200SPMV_TEST_NEW=1 until they have been seen green on a B200 (first thing to run in round 2:
-`B200SPMV_TEST_NEW=1 python -m pytest tests/test_zz_host_pipeline.py -m gpu`)."""
+Green on a B200 since round 2 (profiles/r02a_pytest_new_paths.txt); the path stays opt-in (opts.host_pipeline = 0 by default):
+measured, it does not help matrices whose every row range references the whole band (profiles/r02a_bench_n1_pipeline.json)."""
 import os
 
 import numpy as np
@@ -11,8 +10,7 @@ import pytest
 
 import matrices as M
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get("B200SPMV_TEST_NEW") != "1", reason="not yet verified on a B200 (set B200SPMV_TEST_NEW=1)")]
+pytestmark = [pytest.mark.gpu]
 
 
 def _banded(m, per_row, half_band, seed):

@@ -46,6 +46,5 @@ def test_gpu_sell_with_sigma_equal_C_is_plain_sell(native, oracle):
             P = oracle.sell_plain_convert(rp, col, val, VL, 1)
             y_plain = oracle.sell_plain_spmv(P, x)[:m]
             assert oracle.within_bound(y, y_plain, oracle.row_abs_bound(rp, col, val, x)), (name, VL)
-            if os.environ.get("B200SPMV_TEST_NEW") == "1":          # the bit-for-bit claim has not been seen on a B200 yet (round 2, first pass)
-                assert np.array_equal(y, y_plain), (name, VL)
+            assert np.array_equal(y, y_plain), (name, VL)          # same slices, same per-row FMA chain: bit for bit (green on a B200, round 2)
             MF.close()

@@ -41,6 +41,9 @@ def main():
                     help="medium: synthetic_matrices_medium_dataset.txt (config 2); twins_range: the 3 637 lines of "
                          "validation_matrices_10_samples_30_range_twins.txt (config 3), harness.validation_twins_range()")
     ap.add_argument("--max-nnz", type=float, default=1.6e9, help="skip lines whose nominal rows x avg exceeds this (int32 index space / HBM)")
+    ap.add_argument("--resume", action="append", default=[],
+                    help="JSONL of an earlier (interrupted) run of the same sweep: lines already measured there are not run again and "
+                         "count in the summary (the reference's sweep script retries / skips finished work too, benchmark_code/BENCH/run.sh:672-745); repeatable")
     args = ap.parse_args()
     from oracle import oracle as O          # checker only
 
@@ -52,6 +55,20 @@ def main():
         peak = 6650.0
     dataset = H.medium_dataset() if args.dataset == "medium" else [p for p, _ in H.validation_twins_range()]
     lines = [p for i, p in enumerate(dataset) if i % args.stride == args.offset % args.stride and p.rows * p.avg <= args.max_nnz]
+    # resume: records of earlier runs (kept for the summary), their lines skipped
+    prior = {}
+    for path in args.resume:
+        if os.path.exists(path):
+            for ln in open(path):
+                try:
+                    r = json.loads(ln)
+                except ValueError:
+                    continue                     # a line cut off when the earlier run was killed
+                if "matrix" in r and "best_ms" in r:
+                    prior[r["matrix"]] = r
+    wanted = {p.line() for p in lines}
+    resumed = [r for k, r in prior.items() if k in wanted]
+    lines = [p for p in lines if p.line() not in prior]
     # pass 1 depends on (rows, cols, avg, std, distribution, skew, seed) only: lines that share those share row_ptr
     groups = collections.OrderedDict()
     for p in lines:
@@ -59,7 +76,7 @@ def main():
     pool = cf.ThreadPoolExecutor(max_workers=max(1, (os.cpu_count() or 2) - 1))
     flush = 256 << 20
     t_start = time.time()
-    recs, done, stopped = [], 0, False
+    recs, done, stopped = list(resumed), 0, False
     t_pass1 = t_fill = 0.0
     for key, plist in groups.items():
         if stopped:
@@ -130,7 +147,7 @@ def main():
         del d_rp, d_col, d_val, dx
         torch.cuda.empty_cache()
     # summary per footprint class
-    summ = {"summary": True, "lines_run": done, "lines_selected": len(lines), "dataset": args.dataset, "dataset_lines": len(dataset), "stride": args.stride,
+    summ = {"summary": True, "lines_run": done, "lines_resumed": len(resumed), "lines_selected": len(lines) + len(resumed), "dataset": args.dataset, "dataset_lines": len(dataset), "stride": args.stride,
             "generator": args.generator, "wall_s": round(time.time() - t_start, 1), "pass1_host_s": round(t_pass1, 1),
             "fill_s": round(t_fill, 1), "hbm_peak_GBs": peak, "stopped_early": stopped, "classes": {}}
     for cls in ("<32MB", "32-128MB", "128-512MB", ">=512MB", "all"):
