@@ -157,7 +157,7 @@ def parse_args():
     ap.add_argument("--format", default=None, choices=["auto", "csr", "sell"],
                     help="default: auto at N=1 (both formats built, the faster kept per matrix / per column panel), csr at N>1")
     ap.add_argument("--rows-per-gpu", type=int, default=4194304)
-    ap.add_argument("--exchange", default="p2p", choices=["nccl", "p2p", "mc"],
+    ap.add_argument("--exchange", default="p2p", choices=["nccl", "p2p", "mc"],   # --power-impl python only (mc implies it)
                     help="N>1: p2p = fused unicast peer stores (default; measured fastest at N=8, profiles/r01g_bench_n8*.json), "
                          "mc = fused stores to an NVSwitch multicast address (falls back to p2p), nccl = all-gather")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -172,6 +172,12 @@ def parse_args():
                     help="power workload: generate each rank's non-zeros on the GPU (b200spmv_amg_fill_device; bit-identical, "
                          "not yet verified on a B200 -> off by default)")
     ap.add_argument("--line", default=None, help="one generator parameter line to use as the N=1 workload (profiling)")
+    ap.add_argument("--power-impl", default="c", choices=["c", "python"],
+                    help="power workload: c = b200spmv_power_* (C host loop, default); python = round 1's loop over torch.distributed")
+    ap.add_argument("--variant", default="auto", help="power workload, N>1: auto = verify + trial every entry of POWER_VARIANTS and run the fastest, or one name")
+    ap.add_argument("--host-generator", action="store_true", help="power workload: generate the shard on the host (default: pass 2 on the GPU)")
+    ap.add_argument("--no-power-parity", action="store_true", help="power workload: skip the per-step oracle check on the small member")
+    ap.add_argument("--no-n1-legs", action="store_true", help="power workload, N>1: skip the two single-GPU scaling references")
     return ap.parse_args()
 
 
@@ -379,7 +385,9 @@ def run_single(args):
 # ------------------------------------------------------------------------------------------------
 # N >= 1 under torchrun: row-sharded power iteration, one process per GPU
 # ------------------------------------------------------------------------------------------------
-def run_power(args):
+def run_power_python(args):
+    """Round 1's implementation of the sharded power iteration: the loop in Python over torch.distributed (power.ShardedPowerIteration).
+    Kept for --power-impl python (cross-check of the C layer, and the NVSwitch-multicast experiment --exchange mc)."""
     import torch
     import torch.distributed as dist
     import spmv_research_b200 as S
@@ -661,6 +669,317 @@ def run_power(args):
 
 
 # ------------------------------------------------------------------------------------------------
+# N >= 1 under torchrun: row-sharded power iteration through the C-ABI (b200spmv_power_*), one process per GPU
+# ------------------------------------------------------------------------------------------------
+# What is tried per run (all of them verified per step against the oracle on a small member first, then timed for a few
+# iterations; the fastest runs the timed K steps and every trial time is reported):
+POWER_VARIANTS = {
+    "fused_allreduce":   dict(exchange="fused", scalar_sync=0, panels=1, chunks=0),     # round 1's default, now in C
+    "fused_mailbox":     dict(exchange="fused", scalar_sync=1, panels=1, chunks=0),     # no NCCL call inside the iteration
+    "fused_mailbox_p2c4": dict(exchange="fused", scalar_sync=1, panels=2, chunks=4),    # 2 column panels interleaved over 4 row chunks
+    "fused_mailbox_p2c8": dict(exchange="fused", scalar_sync=1, panels=2, chunks=8),
+    "nccl_c4":           dict(exchange="nccl", scalar_sync=0, panels=1, chunks=4),      # NCCL all-gather, chunk c under kernel c + 1
+    "nccl_p2c4":         dict(exchange="nccl", scalar_sync=0, panels=2, chunks=4),
+}
+
+
+def _power_shard(p, rp, bw, i_s, i_e, fmt, local, dev, panels_wanted, device_generator, keep_host=False):
+    """This rank's rows [i_s, i_e) as format handles, one per column-panel setting in panels_wanted (0 = auto)."""
+    import torch
+    import spmv_research_b200 as S
+    from spmv_research_b200 import amg, formats
+    n = p.cols
+    rp_loc = (rp[i_s:i_e + 1] - rp[i_s]).astype(np.int32)
+    nnz_loc = int(rp_loc[-1])
+    host = None
+    out = {}
+    if device_generator and not keep_host:
+        d_rp = torch.from_numpy(rp).to(dev)
+        col = torch.empty(max(nnz_loc, 1), dtype=torch.int32, device=dev)
+        val = torch.empty(max(nnz_loc, 1), dtype=torch.float64, device=dev)
+        amg.fill_device(p, d_rp, bw, i_s, i_e, col, val, torch.cuda.current_stream().cuda_stream)
+        d_rp_loc = torch.from_numpy(rp_loc).to(dev)
+        for cp in panels_wanted:
+            out[cp] = formats.csr_to_format_device(d_rp_loc, col, val, i_e - i_s, n, nnz_loc, format=fmt, device=local, col_panels=cp)
+        del d_rp, d_rp_loc, col, val
+    else:
+        col, val = amg.fill(p, rp, bw, i_s, i_e)
+        for cp in panels_wanted:
+            out[cp] = S.csr_to_format(rp_loc, col, val, i_e - i_s, n, nnz_loc, 0, 0, format=fmt, device=local, col_panels=cp)
+        if keep_host:
+            host = (rp_loc, col, val)
+    return out, nnz_loc, host
+
+
+def _power_parity(world, rank, local, dev, fmt, names, rows_per_gpu=262144, steps=3):
+    """SURVEY 8e 'parity for iterated runs', on hardware, for every variant about to be timed: on a small member of the series
+    copy x_k to the host, apply the oracle's serial CSR kernel (K/csr.cpp:334-350) to this rank's shard, require the GPU's slot
+    of x_{k+1} within 1e-12 * sum |a_ij x_j| per row, and the exchanged band rows bit-equal on every rank (what the peers
+    received).  Returns {variant: worst err / (1e-12 bound) over ranks and steps}; raises SystemExit on any failure."""
+    import hashlib
+    import torch
+    import torch.distributed as dist
+    from spmv_research_b200 import amg, capi, harness as H, power
+    from oracle import oracle as O          # checker only
+    p = H.config5(world, rows_per_gpu)
+    rp, bw = amg.row_ptr(p)
+    m, n, nnz = p.rows, p.cols, int(rp[-1])
+    bounds = power.shard_bounds(rp, m, nnz, world, capi.partition)
+    i_s, i_e = int(bounds[rank, 0]), int(bounds[rank, 1])
+    need = sorted({POWER_VARIANTS[v]["panels"] for v in names})
+    shards, _, (rp_loc, col, val) = _power_shard(p, rp, bw, i_s, i_e, fmt, local, dev, need, False, keep_host=True)
+    x0 = np.random.default_rng(5).uniform(0.5, 1.5, n)
+    res = {}
+    for name in names:
+        v = POWER_VARIANTS[name]
+        MF = shards[v["panels"]]
+        it = power.CPowerIteration(MF, bounds, n, rank, world, local, exchange=v["exchange"], chunks=v["chunks"], use_graph=False,
+                                   scalar_sync=v["scalar_sync"])
+        info = it.info()
+        it.set_start(x0)
+        c_lo, c_hi = MF.handle.col_range()
+        worst, digests = 0.0, []
+        for k in range(steps):
+            xk, s = it.get_x()
+            xr = np.zeros(n)
+            xr[c_lo:c_hi] = xk[c_lo:c_hi]          # columns this shard never reads may hold stale rows: not part of the product
+            y_ref = s * O.csr_spmv(rp_loc, col, val, xr)
+            bound = abs(s) * O.row_abs_bound(rp_loc, col, val, xr)
+            it.iterate(1)
+            xn, _ = it.get_x()
+            worst = max(worst, float(np.max(np.abs(xn[i_s:i_e] - y_ref) / (1e-12 * np.maximum(bound, 1e-300)))))
+            digests.append(hashlib.sha1(xn[info["band_lo"]:info["band_hi"]].tobytes()).hexdigest())
+        it.close()
+        ok_bits = True
+        if world > 1:
+            every = [None] * world
+            dist.all_gather_object(every, digests)
+            ok_bits = all(e == every[0] for e in every)
+            t = torch.tensor([worst], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            worst = float(t.item())
+        if not (worst <= 1.0 and ok_bits):
+            raise SystemExit("bench.py: multi-GPU per-step parity failed for variant %s: worst err / (1e-12 bound) = %.3g, band rows "
+                             "bit-equal on every rank: %s" % (name, worst, ok_bits))
+        res[name] = round(worst, 4)
+    for MF in shards.values():
+        MF.close()
+    return {"matrix": p.line(), "steps": steps, "worst_err_over_1e-12_bound": res, "band_rows_bit_equal_on_every_rank": True,
+            "check": "x_k copied to the host, oracle serial CSR on the rank's shard, GPU slot of x_{k+1} under the per-row bound"}
+
+
+def run_power(args):
+    import torch
+    import torch.distributed as dist
+    import spmv_research_b200 as S
+    from spmv_research_b200 import amg, capi, formats, harness as H, power
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)      # plumbing: id hand-over, barriers, max-over-ranks of the timings
+    stream = torch.cuda.current_stream().cuda_stream
+    capi.check(capi.lib().b200spmv_set_device(local))
+    # CSR for the sharded run: the fused exchange stores y rows to the peers from the epilogue, and only the CSR kernel writes
+    # rows in order (coalesced NVLink stores); SELL-C-sigma scatters them through row_order (2.61 vs 1.10 ms at N=8, r01s)
+    fmt = {"auto": S.AUTO, "csr": S.CSR_ADAPTIVE, "sell": S.SELL_C_SIGMA}[args.format or "csr"]
+    peak, peak_src = measured_peak()
+    p = H.config5(world, args.rows_per_gpu)
+    K, W = args.steps, max(args.warmup, 3)
+    use_graph = not args.no_graph
+
+    def max_over_ranks(v):
+        if world == 1:
+            return float(v)
+        t = torch.tensor([v], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    if world == 1:
+        names = ["n1"]
+        POWER_VARIANTS["n1"] = dict(exchange="fused", scalar_sync=0, panels=0, chunks=0)        # panels: the auto rule
+    elif args.variant == "auto":
+        names = list(POWER_VARIANTS)
+    else:
+        names = [args.variant]
+    parity = None
+    if not args.no_power_parity:
+        parity = _power_parity(world, rank, local, dev, fmt, names)
+
+    # the matrix: every rank runs pass 1 (row lengths; cheap, deterministic), then generates only its own rows -- on its GPU
+    t0 = time.time()
+    rp, bw = amg.row_ptr(p)
+    m, n, nnz = p.rows, p.cols, int(rp[-1])
+    bounds = power.shard_bounds(rp, m, nnz, world, capi.partition)        # reference partitioner, on the GPU
+    i_s, i_e = int(bounds[rank, 0]), int(bounds[rank, 1])
+    need = sorted({POWER_VARIANTS[v]["panels"] for v in names})
+    shards, nnz_loc, _ = _power_shard(p, rp, bw, i_s, i_e, fmt, local, dev, need, not args.host_generator)
+    torch.cuda.synchronize()
+    t_gen = time.time() - t0
+
+    def make(name, graph):
+        v = POWER_VARIANTS[name]
+        it = power.CPowerIteration(shards[v["panels"]], bounds, n, rank, world, local, exchange=v["exchange"], chunks=v["chunks"],
+                                   use_graph=graph, scalar_sync=v["scalar_sync"])
+        it.set_start(np.ones(n))
+        return it
+
+    # trial: every variant, a few iterations each (eager launches; the graph is for the timed run)
+    trial = {}
+    for name in names:
+        it = make(name, False)
+        it.iterate(W)
+        barrier()
+        trial[name] = round(max_over_ranks(it.iterate(6)) / 6, 5)
+        it.close()
+    best = min(names, key=lambda k: trial[k])
+    vbest = POWER_VARIANTS[best]
+    MF = shards[vbest["panels"]]
+
+    # kernel-only time of the local shard (no exchange, no epilogue), for the roofline entry
+    xk = torch.ones(n, dtype=torch.float64, device=dev)
+    yk = torch.zeros(max(i_e - i_s, 1), dtype=torch.float64, device=dev)
+    k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for _ in range(2):
+        MF.spmv_device(xk, yk, stream)
+    torch.cuda.synchronize()
+    k0.record()
+    for _ in range(5):
+        MF.spmv_device(xk, yk, stream)
+    k1.record()
+    torch.cuda.synchronize()
+    kern_ms = max_over_ranks(k0.elapsed_time(k1) / 5)
+    del xk, yk
+
+    # the timed run: W warm-up iterations (the CUDA graph of two iterations is captured inside them), then exactly K
+    it = make(best, use_graph)
+    it.iterate(max(W, 4) if use_graph else W)
+    with ClockSampler(local) as clk:
+        barrier()
+        clk.mark_start()
+        ms = it.iterate(K)
+        torch.cuda.synchronize()
+        barrier()
+        ms_step = max_over_ranks(ms) / K
+        n_soak = min(int(max_over_ranks(0.6 / max(ms_step * 1e-3, 1e-5))), 4000)
+        it.iterate(n_soak + (n_soak & 1))
+        clk.t1 = time.time()
+        barrier()
+    eig = it.eigenvalue()
+    info = it.info()
+    it.close()
+
+    # scaling references, timed on rank 0 alone while the others wait (SURVEY 8d: scaling = t(1 GPU) / t(P)):
+    #   n1_same_series: the N = 1 member of the weak-scaling series (rows_per_gpu rows on one GPU)
+    #   n1_same_matrix: THIS N-GPU matrix on one GPU with the best single-GPU settings (AUTO format, automatic column panels)
+    n1_series = n1_matrix = None
+    if world > 1 and not args.no_n1_legs:
+        if rank == 0:
+            def one_gpu(pp, f):
+                rp1, bw1 = amg.row_ptr(pp)
+                sh, _, _ = _power_shard(pp, rp1, bw1, 0, pp.rows, f, local, dev, [0], True)
+                b1 = np.array([[0, pp.rows]], np.int64)
+                it1 = power.CPowerIteration(sh[0], b1, pp.cols, 0, 1, local, use_graph=use_graph)
+                it1.set_start(np.ones(pp.cols))
+                it1.iterate(max(W, 4))
+                t1 = it1.iterate(K) / K
+                r = {"matrix": pp.line(), "format": sh[0].format_name, "col_panels": sh[0].col_panels, "ms_per_step": round(t1, 5),
+                     "gflops": round(2.0 * int(rp1[-1]) / t1 * 1e-6, 2)}
+                it1.close()
+                sh[0].close()
+                return r
+            try:
+                n1_series = one_gpu(H.config5(1, args.rows_per_gpu), fmt)
+            except Exception as ex:
+                n1_series = {"error": str(ex).splitlines()[0][:200]}
+            for MFs in shards.values():
+                if MFs is not MF:
+                    MFs.close()
+            torch.cuda.empty_cache()
+            try:
+                n1_matrix = one_gpu(p, S.AUTO)
+            except Exception as ex:
+                n1_matrix = {"error": str(ex).splitlines()[0][:200]}
+        barrier()
+
+    # end to end through the host-vector call: this rank's shard product with x from pinned host memory, y back to the host
+    tx = torch.ones(n, dtype=torch.float64).pin_memory()
+    ty = torch.ones(i_e - i_s + 64, dtype=torch.float64).pin_memory()
+    MF.spmv(tx.numpy(), ty.numpy())
+    barrier()
+    t0 = time.perf_counter()
+    Ke = 5
+    for _ in range(Ke):
+        MF.spmv(tx.numpy(), ty.numpy())
+    te = max_over_ranks((time.perf_counter() - t0) / Ke)
+
+    if rank == 0:
+        bc = H.compulsory_bytes(m, n, nnz)
+        bc_loc = H.compulsory_bytes(i_e - i_s, n, nnz_loc)
+        gflops = 2.0 * nnz / (ms_step * 1e-3) * 1e-9
+        xdesc = {"fused": "fused: the SpMV epilogue stores each finished y row of the band into every peer's next-x buffer over NVLink (CUDA IPC)",
+                 "nccl": "NCCL: y slots all-gathered in place (grouped ncclBroadcast per owner, band rows only) per row chunk on a second stream"}[vbest["exchange"]]
+        sdesc = "mailbox barrier over peer memory (one-warp kernel, no NCCL call in the iteration)" if vbest["scalar_sync"] else "ncclAllReduce of the norm"
+        out = {
+            "metric": METRIC, "value": round(gflops, 2), "unit": "GFLOP/s", "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": round(ms_step, 5), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic (reference artificial-matrix-generator restated bit-exactly, seed 14), power iteration from x = 1",
+            "config": power_config(p, args.rows_per_gpu, world),
+            "config_detail": {"format": MF.format_name, "col_panels": MF.col_panels, "total_nnz": int(nnz),
+                              "shard_rows": [int(b[1] - b[0]) for b in bounds], "variant": best, "exchange": xdesc, "scalar_sync": sdesc,
+                              "row_chunks": info["chunks"], "exchange_rows": "rows [%d, %d) of %d (the union of the shards' referenced column bands)"
+                              % (info["band_lo"], info["band_hi"], n),
+                              "loop": "b200spmv_power_iterate (C host code, csrc/power.cu); NCCL bound inside the library",
+                              "launch": "cuda_graph(2 iterations per replay)" if info["graph"] else "eager",
+                              "generate_s": round(t_gen, 1), "generator": "host" if args.host_generator else "device pass 2 (b200spmv_amg_fill_device)"},
+            "effective_GBs": round(bc / (ms_step * 1e-3) * 1e-9, 1),
+            "roofline_frac_nominal_8TBs": round(bc / (ms_step * 1e-3) * 1e-9 / (NOMINAL_HBM_GBS * world), 4),
+            "roofline": {"bound": "hbm", "kernel": "csr_tile_kernel" if MF.format == S.CSR_ADAPTIVE else "sell_kernel",
+                         "achieved": round(bc_loc / kern_ms * 1e-6, 1), "peak": peak, "unit": "GB/s",
+                         "frac": round(bc_loc / kern_ms * 1e-6 / peak, 4), "traffic": None, "peak_source": peak_src,
+                         "kernel_only_ms": round(kern_ms, 5),
+                         "achieved_def": "rank-0 shard compulsory bytes / slowest rank's kernel-only SpMV time (CUDA events, 5 launches, plain product)"},
+            "limiter": {"kernel_only_ms": round(kern_ms, 5), "iteration_ms": round(ms_step, 5),
+                        "exchange_and_sync_ms": round(ms_step - kern_ms, 5)},
+            "e2e": {"value": round(2.0 * nnz / te * 1e-9, 2), "unit": "GFLOP/s", "h2d_bytes_per_step": int(8 * (MF.handle.col_range()[1] - MF.handle.col_range()[0]) * world),
+                    "d2h_bytes_per_step": int(8 * m), "ms_per_step": round(te * 1e3, 4),
+                    "call": "per rank Matrix_Format::spmv(x, y) on its row shard, pinned host x / y, max over ranks"},
+            "gpu_launches": int(K * info["launches_per_iteration"]), "nccl_calls_per_iteration": info["nccl_calls_per_iteration"],
+            "clocks": clk.summary(), "eigenvalue_estimate": eig,
+            "variant_trials_ms_per_iteration": trial, "parity_per_step": parity,
+            "n1_same_series": n1_series, "n1_same_matrix": n1_matrix,
+        }
+        if n1_series and "ms_per_step" in n1_series:
+            out["scaling_weak_vs_same_series"] = round(world * n1_series["ms_per_step"] / ms_step, 3)
+        if n1_matrix and "ms_per_step" in n1_matrix:
+            out["scaling_strong_vs_same_matrix"] = round(n1_matrix["ms_per_step"] / ms_step, 3)
+        emit(out)
+    for MFs in shards.values():
+        MFs.close()
+    # a communicator teardown that stalls must not keep the GPUs leased: a watchdog ends the process 30 s after the line is out
+    def _bail():
+        os._exit(0)
+    wd = threading.Timer(30.0, _bail)
+    wd.daemon = True
+    wd.start()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    wd.cancel()
+
+
+# ------------------------------------------------------------------------------------------------
 # reference arm: the reference's CPU CSR kernel on the host cores, same workload definition
 # ------------------------------------------------------------------------------------------------
 def run_reference(args):
@@ -747,7 +1066,7 @@ def main():
         return run_reference(args)
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if world > 1 or args.workload == "power":
-        return run_power(args)
+        return run_power_python(args) if (args.power_impl == "python" or args.exchange == "mc") else run_power(args)
     return run_single(args)
 
 

@@ -12,6 +12,7 @@
  *                               (reference GPU-plugin convention: K/GPU_clean/cuda_csr.cu:353-430)
  *   b200spmv_spmv_device()   <- the same product with x / y already resident in HBM (iterated SpMV;
  *                               nearest reference caller benchmark_code/BENCH/src/bench_cg.cpp:93-292)
+ *   b200spmv_power_*()       <- net-new multi-GPU layer (row shards by the reference partitioner, see below)
  *   b200spmv_partition*()    <- loop_partitioner_balance_prefix_sums()            lib/parallel_util.h:156-184
  *   b200spmv_merge_coords()  <- MergePathSearch()                                 K/merge.cpp:230-251
  *   b200spmv_export()        <- read-back of the converted layout for bit-exact tests
@@ -68,7 +69,7 @@ typedef struct b200spmv_opts {
 	int32_t sell_C;           /* slice height: power of two in [2, 256]; default 32                     */
 	int32_t sell_sigma;       /* sort window, multiple of sell_C; default 16384 (K/sell_c_s.cpp:59)     */
 	int32_t csr_nnz_per_thread; /* 4 | 8 | 16 | 32 non-zeros per thread of a 256-thread tile; 0 = auto  */
-	int32_t csr_ext;          /* tail-extension capacity in nnz (multiple of 8); 0 = auto               */
+	int32_t csr_ext;          /* tail-extension capacity in nnz (multiple of 64 in [64, 8192]); 0 = auto               */
 	int32_t x_hint;           /* 0: L2 evict_last hint on x gathers (default), 1: plain loads           */
 	int32_t sell_sigma_alt;   /* AUTO only: second sort window tried (0 = default 256, -1 = none)       */
 	int32_t sell_variant;     /* SELL kernel shape (k steps in flight x resident warps per SM): 0 = chosen from
@@ -76,8 +77,7 @@ typedef struct b200spmv_opts {
 	                             4 = 16 x 16                                                             */
 	int32_t csr_compress_rows; /* CSR: plan and run on the non-empty rows only, zero the empty ones in a separate balanced
 	                             launch: 0 = when a tile would own more than 2 tiles' worth of rows, 1 = never, 2 = always */
-	int32_t x_l2_mb;          /* unused (a fractional L2 evict_last budget for x was measured, <= 2 %, and removed;
-	                             column panels handle x bands larger than L2)                                    */
+	int32_t reserved0;        /* must be 0 (keeps the layout of earlier builds)                                       */
 	int32_t keep_diag;        /* 1: extract diag(A) at create time (square matrices; needed by b200spmv_pcg)            */
 	int32_t pin_host_vectors; /* 1: b200spmv_spmv_host page-locks (cudaHostRegister) each distinct x / y buffer it is handed
 	                             the first time it sees it (the harness's aligned_alloc vectors live for the whole run,
@@ -238,6 +238,63 @@ int b200spmv_f32_spmv_host(b200spmv_f32_t * h, const float * x, float * y);     
 int b200spmv_f32_spmv_device(b200spmv_f32_t * h, const float * dx, float * dy, void * stream);    /* device vectors, asynchronous */
 int b200spmv_f32_time_device(b200spmv_f32_t * h, const float * dx, float * dy, int32_t iters, int64_t flush_bytes, float * ms_out);
 void b200spmv_f32_destroy(b200spmv_f32_t * h);
+
+
+/* ---- multi-GPU iterated SpMV (power iteration) over a row-sharded matrix: one process per GPU (net-new, the
+ * reference has no multi-GPU code -- what it contributes is the row partition: rank p owns the rows that
+ * loop_partitioner_balance_prefix_sums(), lib/parallel_util.h:156-184, gives worker p of P, see b200spmv_partition*).
+ * The iteration loop, the exchange of y (the next x) and the scalar arithmetic all run under this C-ABI; a caller
+ * needs nothing but a way to hand a 128-byte id from rank 0 to the other ranks (a file, MPI, a torch store).
+ *   exchange B200SPMV_X_NCCL : y slots all-gathered over NVLink with NCCL (grouped ncclBroadcast, unequal counts, in place in
+ *                              the next-x buffer), band-limited (only rows some rank's columns reference), in `chunks` row
+ *                              chunks so that chunk c travels under the kernel of chunk c + 1; ncclAllReduce of the norm.
+ *   exchange B200SPMV_X_FUSED: the SpMV epilogue stores every finished row of the band straight into all peers' next-x
+ *                              buffers (CUDA IPC mappings, NVLink P2P stores); the only synchronisation left is the scalar:
+ *                              ncclAllReduce (scalar_sync 0) or a mailbox barrier over peer memory (scalar_sync 1).
+ * With a column-panel shard (opts.col_panels) the launches are interleaved by row chunk -- chunk 0 of panel 0, chunk 0 of
+ * panel 1, chunk 1 of panel 0, ... -- so rows become final (and leave over NVLink) progressively while each panel's part
+ * of x stays L2-resident across a chunk.  NCCL is bound at run time (dlopen of libnccl.so.2, or $B200SPMV_NCCL_LIB). */
+typedef struct b200spmv_comm b200spmv_comm_t;
+typedef struct b200spmv_power b200spmv_power_t;
+enum { B200SPMV_X_NCCL = 0, B200SPMV_X_FUSED = 1 };
+
+typedef struct b200spmv_power_opts {
+	int32_t exchange;         /* B200SPMV_X_NCCL | B200SPMV_X_FUSED                                                   */
+	int32_t chunks;           /* row chunks per iteration, 1..16; 0 = auto (4 when the shard can be launched by tile ranges)  */
+	int32_t full_exchange;    /* 1 = exchange every row, 0 (default) = only the union of the shards' referenced column bands */
+	int32_t use_graph;        /* 1 = two iterations (one per buffer parity) are captured into a CUDA graph and replayed     */
+	int32_t scalar_sync;      /* FUSED: 0 = ncclAllReduce of the norm, 1 = mailbox barrier over peer memory (no NCCL call)  */
+	int32_t reserved[3];
+} b200spmv_power_opts;
+
+int b200spmv_comm_unique_id(unsigned char id_out[128]);                  /* ncclGetUniqueId: call on ONE rank, hand to all */
+int b200spmv_comm_create(b200spmv_comm_t ** out, const unsigned char id[128], int32_t rank, int32_t world, int32_t device);
+void b200spmv_comm_destroy(b200spmv_comm_t * c);
+
+/* shard: this rank's rows [bounds[2 rank], bounds[2 rank + 1]) of the n x n matrix as a handle with m = that many rows and
+ * n columns (CSR-adaptive, optionally column panels; SELL shards run unchunked).  bounds: 2 * world row bounds tiling
+ * [0, n).  Collective over the communicator.  The shard handle stays owned by the caller and must outlive the object. */
+int b200spmv_power_create(b200spmv_power_t ** out, b200spmv_t * shard, b200spmv_comm_t * comm, const int64_t * bounds, int64_t n,
+                          const b200spmv_power_opts * opts);
+/* x0: n doubles (HOST), the same on every rank; the iterate is kept un-normalised with its scale 1 / ||x|| beside it */
+int b200spmv_power_set_start(b200spmv_power_t * pw, const double * x0_host);
+/* `iters` iterations u' = s A u, s' = 1 / ||u'||.  eigenvalue_out (optional): ||A x|| of the last iteration with ||x|| = 1;
+ * ms_out (optional): device time of the iterations (CUDA events on the launching stream).  Collective. */
+int b200spmv_power_iterate(b200spmv_power_t * pw, int32_t iters, double * eigenvalue_out, float * ms_out);
+/* The current un-normalised iterate (HOST, n doubles; rows outside the exchanged band that this rank does not own are stale
+ * by design: nothing reads them) and its scale -- for per-step parity checks against the serial reference kernel. */
+int b200spmv_power_get_x(b200spmv_power_t * pw, double * x_host, double * scale_out);
+/* info_out[0] = row chunks used, [1] = column panels of the shard, [2] = band lo, [3] = band hi (global rows exchanged),
+ * [4] = 1 when a CUDA graph is active, [5] = kernel launches per iteration, [6] = NCCL calls per iteration */
+int b200spmv_power_info(const b200spmv_power_t * pw, int64_t * info_out, int32_t n_out);
+void b200spmv_power_destroy(b200spmv_power_t * pw);
+
+/* The row-chunk x column-panel launch order used above, as a pure host function (testable without a GPU): tile_row[q] =
+ * B200SPMV_X_TILE_ROW of panel q (ntiles[q] + 1 entries, last = m).  unit_out[q * (K + 1) + c] = first tile of panel q in chunk
+ * c; final_row_out[c] = rows [0, final_row_out[c]) are final once chunks < c of every panel have run.  Invariant: the rows a
+ * panel finishes in chunk c were finished by every earlier panel in chunks <= c. */
+int b200spmv_chunk_schedule(int32_t P, int32_t K, int64_t m, const int32_t * const * tile_row, const int64_t * ntiles,
+                            int64_t * unit_out, int64_t * final_row_out);
 
 const char * b200spmv_last_error(void);
 const char * b200spmv_version(void);

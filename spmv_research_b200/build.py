@@ -10,9 +10,9 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "lib")
-CU_SOURCES = ["capi.cu", "csr_kernel.cu", "sell_kernel.cu", "convert.cu", "partition.cu", "pcg.cu", "panels.cu", "amg_device.cu", "coo.cu", "f32.cu"]
+CU_SOURCES = ["capi.cu", "csr_kernel.cu", "sell_kernel.cu", "convert.cu", "partition.cu", "pcg.cu", "panels.cu", "amg_device.cu", "coo.cu", "f32.cu", "power.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
-              "-Xcompiler", "-fPIC", "-shared", "--cudart", "static"]
+              "-Xcompiler", "-fPIC", "-shared", "--cudart", "static", "-ldl"]      # -ldl: power.cu binds NCCL with dlopen (no link-time NCCL)
 
 
 def _stale(target, deps):

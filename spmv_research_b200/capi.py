@@ -29,12 +29,20 @@ class B200Error(RuntimeError):
 
 class Opts(C.Structure):
     _fields_ = [("format", C.c_int32), ("device", C.c_int32), ("sell_C", C.c_int32), ("sell_sigma", C.c_int32),
-                ("csr_nnz_per_thread", C.c_int32), ("csr_ext", C.c_int32), ("x_hint", C.c_int32), ("sell_sigma_alt", C.c_int32), ("sell_variant", C.c_int32), ("csr_compress_rows", C.c_int32), ("x_l2_mb", C.c_int32), ("keep_diag", C.c_int32), ("pin_host_vectors", C.c_int32), ("col_panels", C.c_int32), ("host_pipeline", C.c_int32), ("reserved", C.c_int32 * 1)]
+                ("csr_nnz_per_thread", C.c_int32), ("csr_ext", C.c_int32), ("x_hint", C.c_int32), ("sell_sigma_alt", C.c_int32), ("sell_variant", C.c_int32), ("csr_compress_rows", C.c_int32), ("reserved0", C.c_int32), ("keep_diag", C.c_int32), ("pin_host_vectors", C.c_int32), ("col_panels", C.c_int32), ("host_pipeline", C.c_int32), ("reserved", C.c_int32 * 1)]
 
 
 class Launch(C.Structure):
     _fields_ = [("scale", C.c_void_p), ("norm2", C.c_void_p), ("y_peer", C.c_void_p * 8), ("n_peer", C.c_int32), ("pad_", C.c_int32),
                 ("peer_row_lo", C.c_int64), ("peer_row_hi", C.c_int64)]
+
+
+class PowerOpts(C.Structure):
+    _fields_ = [("exchange", C.c_int32), ("chunks", C.c_int32), ("full_exchange", C.c_int32), ("use_graph", C.c_int32),
+                ("scalar_sync", C.c_int32), ("reserved", C.c_int32 * 3)]
+
+
+X_NCCL, X_FUSED = 0, 1
 
 
 class PcgResult(C.Structure):
@@ -95,6 +103,16 @@ def lib():
         "b200spmv_f32_time_device": (C.c_int, [vp, vp, vp, i32, i64, vp]),
         "b200spmv_f32_destroy": (None, [vp]),
         "b200spmv_amg_fill_device": (C.c_int, [vp, vp, C.c_double, i64, i64, vp, vp, vp]),
+        "b200spmv_comm_unique_id": (C.c_int, [vp]),
+        "b200spmv_comm_create": (C.c_int, [C.POINTER(vp), vp, i32, i32, i32]),
+        "b200spmv_comm_destroy": (None, [vp]),
+        "b200spmv_power_create": (C.c_int, [C.POINTER(vp), vp, vp, vp, i64, C.POINTER(PowerOpts)]),
+        "b200spmv_power_set_start": (C.c_int, [vp, vp]),
+        "b200spmv_power_iterate": (C.c_int, [vp, i32, C.POINTER(C.c_double), C.POINTER(C.c_float)]),
+        "b200spmv_power_get_x": (C.c_int, [vp, vp, C.POINTER(C.c_double)]),
+        "b200spmv_power_info": (C.c_int, [vp, vp, i32]),
+        "b200spmv_power_destroy": (None, [vp]),
+        "b200spmv_chunk_schedule": (C.c_int, [i32, i32, i64, vp, vp, vp, vp]),
         "b200spmv_last_error": (C.c_char_p, []),
         "b200spmv_version": (C.c_char_p, []),
     }
@@ -313,3 +331,82 @@ def ipc_import(handle_bytes):
     p = C.c_void_p()
     check(lib().b200spmv_ipc_import(buf, C.byref(p)))
     return p.value
+
+
+# ---- multi-GPU power iteration (csrc/power.cu): thin callers, no arithmetic here ------------------------------------------
+def comm_unique_id():
+    buf = (C.c_ubyte * 128)()
+    check(lib().b200spmv_comm_unique_id(buf))
+    return bytes(buf)
+
+
+class Comm:
+    """Owns one b200spmv_comm_t* (an NCCL communicator created inside the library)."""
+
+    def __init__(self, uid, rank, world, device=-1):
+        self._c = C.c_void_p()
+        self.rank, self.world = int(rank), int(world)
+        buf = (C.c_ubyte * 128).from_buffer_copy(uid)
+        check(lib().b200spmv_comm_create(C.byref(self._c), buf, self.rank, self.world, int(device)))
+
+    def close(self):
+        if getattr(self, "_c", None) is not None and self._c.value and _lib is not None:
+            _lib.b200spmv_comm_destroy(self._c)
+            self._c = C.c_void_p()
+
+    __del__ = close
+
+
+class Power:
+    """Owns one b200spmv_power_t*: the row-sharded power iteration of include/b200spmv.h."""
+
+    def __init__(self, handle, comm, bounds, n, exchange=X_NCCL, chunks=0, full_exchange=False, use_graph=False, scalar_sync=0):
+        self._p = C.c_void_p()
+        self._keep = (handle, comm)                       # the shard and the communicator must outlive the object
+        self.n = int(n)
+        b = np.ascontiguousarray(np.asarray(bounds, np.int64).reshape(-1))
+        o = PowerOpts(exchange=int(exchange), chunks=int(chunks), full_exchange=int(bool(full_exchange)), use_graph=int(bool(use_graph)),
+                      scalar_sync=int(scalar_sync))
+        check(lib().b200spmv_power_create(C.byref(self._p), handle._h, comm._c if comm is not None else None, b.ctypes.data, self.n, C.byref(o)))
+
+    def set_start(self, x0):
+        x0 = np.ascontiguousarray(x0, np.float64)
+        assert x0.size == self.n
+        check(lib().b200spmv_power_set_start(self._p, x0.ctypes.data))
+
+    def iterate(self, iters):
+        """Returns (eigenvalue estimate, device ms of the iterations)."""
+        eig, ms = C.c_double(), C.c_float()
+        check(lib().b200spmv_power_iterate(self._p, int(iters), C.byref(eig), C.byref(ms)))
+        return eig.value, ms.value
+
+    def get_x(self):
+        """(current un-normalised iterate as a host array, its scale)."""
+        x = np.empty(self.n)
+        s = C.c_double()
+        check(lib().b200spmv_power_get_x(self._p, x.ctypes.data, C.byref(s)))
+        return x, s.value
+
+    def info(self):
+        v = (C.c_int64 * 7)()
+        check(lib().b200spmv_power_info(self._p, v, 7))
+        return dict(zip(("chunks", "panels", "band_lo", "band_hi", "graph", "launches_per_iteration", "nccl_calls_per_iteration"), [int(t) for t in v]))
+
+    def close(self):
+        if getattr(self, "_p", None) is not None and self._p.value and _lib is not None:
+            _lib.b200spmv_power_destroy(self._p)
+            self._p = C.c_void_p()
+
+    __del__ = close
+
+
+def chunk_schedule(tile_rows, K, m):
+    """b200spmv_chunk_schedule: tile_rows = one int32 array per column panel; returns (unit[P, K + 1], final_row[K + 1])."""
+    P = len(tile_rows)
+    arrs = [np.ascontiguousarray(a, np.int32) for a in tile_rows]
+    ptrs = (C.c_void_p * P)(*[a.ctypes.data for a in arrs])
+    nt = np.array([a.size - 1 for a in arrs], np.int64)
+    unit = np.zeros((P, K + 1), np.int64)
+    fin = np.zeros(K + 1, np.int64)
+    check(lib().b200spmv_chunk_schedule(P, int(K), int(m), ptrs, nt.ctypes.data, unit.ctypes.data, fin.ctypes.data))
+    return unit, fin

@@ -177,6 +177,34 @@ static int compute_block_col_ranges(b200spmv * h)
 	return 0;
 }
 
+// row_ptr must start at 0, never decrease and end at nnz: a malformed array would send the kernels out of bounds
+__global__ void validate_row_ptr_kernel(const int32_t * __restrict__ rp, int64_t m, int64_t nnz, int * __restrict__ bad)
+{
+	const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (i > m)
+		return;
+	bool b = (i < m) ? (rp[i] > rp[i + 1]) : ((int64_t) rp[m] != nnz);
+	if (i == 0)
+		b = b || rp[0] != 0;
+	if (b)
+		atomicExch(bad, 1);
+}
+
+static int validate_row_ptr(b200spmv * h)
+{
+	int * d = nullptr, bad = 0;
+	CU(cudaMalloc(&d, sizeof(int)));
+	CU(cudaMemsetAsync(d, 0, sizeof(int), h->stream));
+	validate_row_ptr_kernel<<<(unsigned) ((h->m + 1 + 255) / 256), 256, 0, h->stream>>>(h->d_row_ptr, h->m, h->nnz, d);
+	CU_LAUNCH();
+	CU(cudaMemcpyAsync(&bad, d, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+	CU(cudaStreamSynchronize(h->stream));
+	CU(cudaFree(d));
+	if (bad)
+		B200_FAIL("row_ptr is malformed: it must start at 0, be non-decreasing and end at nnz = %lld", (long long) h->nnz);
+	return 0;
+}
+
 __global__ void rebase_row_ptr_kernel(const int32_t * __restrict__ in, int32_t * __restrict__ out, int64_t m1)
 {
 	const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
@@ -492,6 +520,7 @@ static int create_common(b200spmv ** out, const int32_t * row_ptr, const int32_t
 			if (cudaMemcpyAsync(h->d_val, values, nnz * sizeof(double), kind, h->stream) != cudaSuccess) break;
 		}
 		if (cudaStreamSynchronize(h->stream) != cudaSuccess) break;
+		if (validate_row_ptr(h)) goto fail;
 		if (compute_col_range(h)) goto fail;
 		if (compute_block_col_ranges(h)) goto fail;
 		if (o.keep_diag && pcg_extract_diag(h)) goto fail;
@@ -501,8 +530,8 @@ static int create_common(b200spmv ** out, const int32_t * row_ptr, const int32_t
 			// column panels: this handle becomes a shell around P sub-handles (panels.cu)
 			b200spmv_opts sub = o;
 			sub.col_panels = 1;
-			sub.csr_compress_rows = 1;          // every panel launch must pass every row through y_finish
-			sub.keep_diag = 0;
+			sub.keep_diag = 0;                  // (a panel may compress its rows: csr_zero_rows_kernel passes the rows that are empty
+			                                    // in the panel through y_finish like the tile kernel does -- accumulate / scale / norm)
 			sub.host_pipeline = 0;              // the shell's host entry point uploads the band once
 			sub.device = -1;
 			if (panels_split(h, P, &sub)) goto fail;
@@ -519,11 +548,11 @@ static int create_common(b200spmv ** out, const int32_t * row_ptr, const int32_t
 			norm_slots = 1;
 		} else if (h->format == B200SPMV_AUTO) {
 			if (auto_select(h, o)) goto fail;           // convert_ms of an AUTO handle includes the trials
-			norm_slots = (h->format == B200SPMV_CSR_ADAPTIVE) ? h->ntiles + h->nsplit
+			norm_slots = (h->format == B200SPMV_CSR_ADAPTIVE) ? h->ntiles + h->nsplit + CSR_ZERO_CTAS
 			                                                   : (h->sell_nitems + 3) / 4 + (h->sell_ncuts + 3) / 4;
 		} else if (h->format == B200SPMV_CSR_ADAPTIVE) {
 			if (csr_plan_tiles(h)) goto fail;
-			norm_slots = h->ntiles + h->nsplit;
+			norm_slots = h->ntiles + h->nsplit + CSR_ZERO_CTAS;
 		} else {
 			if (sell_convert(h)) goto fail;
 			// the CSR copies of col / val are not needed any more
@@ -603,7 +632,7 @@ extern "C" int32_t b200spmv_launches_per_spmv(const b200spmv_t * h)
 
 // One product: a plain handle launches its kernel(s); a panel shell launches its sub-handles in ascending column order, the
 // last of which receives the caller's epilogue (scale, norm, peer destinations).
-static int launch_product(b200spmv * h, const double * dx, double * dy, cudaStream_t st, const b200spmv_launch * l)
+int launch_product(b200spmv * h, const double * dx, double * dy, cudaStream_t st, const b200spmv_launch * l)
 {
 	if (h->npanels > 1) {
 		for (int q = 0; q < h->npanels; q++) {

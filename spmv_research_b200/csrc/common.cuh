@@ -31,6 +31,7 @@ extern thread_local char g_b200_err[512];
 // Tunables of the nnz-tiled CSR kernel
 // ---------------------------------------------------------------------------------------------
 constexpr int CSR_THREADS = 256;          // threads per tile CTA
+constexpr int CSR_ZERO_CTAS = 148 * 8;    // most CTAs csr_zero_rows_kernel is launched with (compressed rows); one norm slot each
 constexpr int SELL_THREADS = 128;         // threads per SELL CTA: four warps, one work item each
 constexpr int SELL_KCH = 128;             // slice columns per work item
 
@@ -234,6 +235,8 @@ int device_exclusive_scan_i64(int64_t * d_data, int64_t n, cudaStream_t st);
 int launch_csr_spmv(b200spmv * h, const double * dx, double * dy, cudaStream_t st, const b200spmv_launch * l);
 int launch_sell_spmv(b200spmv * h, const double * dx, double * dy, cudaStream_t st, const b200spmv_launch * l);
 int launch_norm_reduce(b200spmv * h, int64_t slots, double * d_out, cudaStream_t st);
+int launch_csr_tiles_range(b200spmv * h, const double * dx, double * dy, cudaStream_t st, const b200spmv_launch * l, int64_t first, int64_t count);
+int launch_product(b200spmv * h, const double * dx, double * dy, cudaStream_t st, const b200spmv_launch * l);      // capi.cu
 int launch_spmv_any(b200spmv * h, const double * dx, double * dy, cudaStream_t st);     // capi.cu: dispatch on h->format
 int pcg_extract_diag(b200spmv * h);
 // panels.cu

@@ -389,11 +389,30 @@ __global__ void csr_fixup_kernel(const int32_t * __restrict__ row_ptr, const int
 	}
 }
 
-// Compressed row space: the empty rows, listed at plan time, are written 0 by a balanced grid-stride pass.
-__global__ void csr_zero_rows_kernel(const int32_t * __restrict__ empty_rows, int64_t n_empty, YOut out)
+// Compressed row space: the empty rows, listed at plan time, are finished by a balanced grid-stride pass -- written 0 in a plain
+// handle; in a column panel "empty" means empty in THIS panel, so the row goes through y_finish like any other (the partial
+// of earlier panels is kept / scaled / sent to the peers / added to the norm).
+__global__ void csr_zero_rows_kernel(const int32_t * __restrict__ empty_rows, int64_t n_empty, YOut out, int64_t norm_base)
 {
-	for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n_empty; i += (int64_t) gridDim.x * blockDim.x)
-		y_finish(out, empty_rows[i], 0.0, 1.0);
+	__shared__ double s_red[8];
+	const double scale = out.scale ? *out.scale : 1.0;
+	double nrm = 0.0;
+	for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n_empty; i += (int64_t) gridDim.x * blockDim.x) {
+		const double v = y_finish(out, empty_rows[i], 0.0, scale);
+		nrm += v * v;
+	}
+	if (out.norm_partial) {
+		nrm = warp_sum(nrm);
+		if ((threadIdx.x & 31) == 0)
+			s_red[threadIdx.x >> 5] = nrm;
+		__syncthreads();
+		if (threadIdx.x == 0) {
+			double tot = 0.0;
+			for (int w = 0; w < (int) (blockDim.x >> 5); w++)
+				tot += s_red[w];
+			out.norm_partial[norm_base + blockIdx.x] = tot;
+		}
+	}
 }
 
 // Deterministic final reduction of the per-CTA norm partials (single CTA, fixed tree).
@@ -426,10 +445,12 @@ template <int NPT, bool HINT, int MODE>
 static int launch_tiles_impl(b200spmv * h, const double * dx, cudaStream_t st, const YOut & out)
 {
 	const size_t smem = (size_t) (h->tile_nnz + h->ext) * sizeof(double);
-	static bool attr_set = false;
-	if (!attr_set) {
+	// the opt-in for > 48 KB of dynamic shared memory is per device (a process may drive several: opts.device)
+	static unsigned char attr_set[64] = { 0 };
+	const int dv = (h->device >= 0 && h->device < 64) ? h->device : 0;
+	if (!attr_set[dv]) {
 		CU(cudaFuncSetAttribute(csr_tile_kernel<NPT, HINT, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-		attr_set = true;
+		attr_set[dv] = 1;
 	}
 	const int64_t first = h->range_count >= 0 ? h->range_first : 0;
 	const int64_t count = h->range_count >= 0 ? h->range_count : h->ntiles;
@@ -452,9 +473,9 @@ static int launch_tiles(b200spmv * h, const double * dx, cudaStream_t st, const 
 	return full ? launch_tiles_impl<NPT, HINT, 2>(h, dx, st, out) : launch_tiles_impl<NPT, HINT, 1>(h, dx, st, out);
 }
 
-int launch_csr_spmv(b200spmv * h, const double * dx, double * dy, cudaStream_t st, const b200spmv_launch * l)
+// y destinations / epilogue of one launch from the caller's b200spmv_launch and the handle's panel role
+static int csr_make_out(const b200spmv * h, double * dy, const b200spmv_launch * l, YOut & out)
 {
-	YOut out;
 	memset(&out, 0, sizeof(out));
 	out.y = dy;
 	if (l) {
@@ -474,22 +495,35 @@ int launch_csr_spmv(b200spmv * h, const double * dx, double * dy, cudaStream_t s
 	}
 	out.accum = h->acc_mode & 1;
 	out.partial = (h->acc_mode >> 1) & 1;
-	int rc;
+	return 0;
+}
+
+static int csr_launch_tiles(b200spmv * h, const double * dx, cudaStream_t st, const YOut & out)
+{
 	const bool hint = (h->x_hint == 0);
-	if (h->compressed && h->n_empty > 0) {
-		const int64_t want = (h->n_empty + 255) / 256;
-		csr_zero_rows_kernel<<<(unsigned) (want < 148 * 8 ? want : 148 * 8), 256, 0, st>>>(h->d_empty_rows, h->n_empty, out);
-		CU_LAUNCH();
-	}
 	switch (h->npt) {
-	case 4:  rc = hint ? launch_tiles<4, true>(h, dx, st, out) : launch_tiles<4, false>(h, dx, st, out); break;
-	case 8:  rc = hint ? launch_tiles<8, true>(h, dx, st, out) : launch_tiles<8, false>(h, dx, st, out); break;
-	case 16: rc = hint ? launch_tiles<16, true>(h, dx, st, out) : launch_tiles<16, false>(h, dx, st, out); break;
-	case 32: rc = hint ? launch_tiles<32, true>(h, dx, st, out) : launch_tiles<32, false>(h, dx, st, out); break;
+	case 4:  return hint ? launch_tiles<4, true>(h, dx, st, out) : launch_tiles<4, false>(h, dx, st, out);
+	case 8:  return hint ? launch_tiles<8, true>(h, dx, st, out) : launch_tiles<8, false>(h, dx, st, out);
+	case 16: return hint ? launch_tiles<16, true>(h, dx, st, out) : launch_tiles<16, false>(h, dx, st, out);
+	case 32: return hint ? launch_tiles<32, true>(h, dx, st, out) : launch_tiles<32, false>(h, dx, st, out);
 	default: B200_FAIL("unsupported csr_nnz_per_thread %d", h->npt);
 	}
-	if (rc)
-		return rc;
+}
+
+int launch_csr_spmv(b200spmv * h, const double * dx, double * dy, cudaStream_t st, const b200spmv_launch * l)
+{
+	YOut out;
+	if (csr_make_out(h, dy, l, out))
+		return 1;
+	int64_t zero_ctas = 0;
+	if (h->compressed && h->n_empty > 0) {
+		const int64_t want = (h->n_empty + 255) / 256;
+		zero_ctas = want < CSR_ZERO_CTAS ? want : CSR_ZERO_CTAS;
+		csr_zero_rows_kernel<<<(unsigned) zero_ctas, 256, 0, st>>>(h->d_empty_rows, h->n_empty, out, h->ntiles + h->nsplit);
+		CU_LAUNCH();
+	}
+	if (csr_launch_tiles(h, dx, st, out))
+		return 1;
 	if (h->nsplit > 0) {
 		csr_fixup_kernel<<<(unsigned) h->nsplit, 32, 0, st>>>(h->d_rp_plan, h->d_split_row, h->d_split_tile, h->d_tile_head,
 		                                                     h->d_tile_tail, h->nsplit, h->tile_nnz, h->ntiles,
@@ -497,6 +531,25 @@ int launch_csr_spmv(b200spmv * h, const double * dx, double * dy, cudaStream_t s
 		CU_LAUNCH();
 	}
 	if (l && l->norm2)
-		return launch_norm_reduce(h, h->ntiles + h->nsplit, l->norm2, st);
+		return launch_norm_reduce(h, h->ntiles + h->nsplit + zero_ctas, l->norm2, st);
 	return 0;
+}
+
+// Tiles [first, first + count) only -- the rows STARTING in them are final when the launch ends.  For handles whose rows are
+// all finished by the tile kernel (no split rows, no row compression); no norm reduction: the caller (power.cu) composes
+// several ranges -- of several column panels -- and reduces the norm partials once, after the last.
+int launch_csr_tiles_range(b200spmv * h, const double * dx, double * dy, cudaStream_t st, const b200spmv_launch * l, int64_t first, int64_t count)
+{
+	if (h->format != B200SPMV_CSR_ADAPTIVE || h->npanels > 1 || h->nsplit > 0 || h->compressed)
+		B200_FAIL("tile-range launches need a plain CSR handle without split rows / row compression");
+	if (first < 0 || count < 0 || first + count > h->ntiles)
+		B200_FAIL("tile range [%lld, +%lld) outside [0, %lld)", (long long) first, (long long) count, (long long) h->ntiles);
+	YOut out;
+	if (csr_make_out(h, dy, l, out))
+		return 1;
+	h->range_first = first;
+	h->range_count = count;
+	const int rc = csr_launch_tiles(h, dx, st, out);
+	h->range_count = -1;
+	return rc;
 }

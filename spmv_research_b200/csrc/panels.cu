@@ -133,8 +133,17 @@ int panels_split(b200spmv * h, int P, const b200spmv_opts * sub_opts)
 		snprintf(g_b200_err, sizeof(g_b200_err), "column panels: CUDA failure: %s", cudaGetErrorString(cudaGetLastError()));
 	for (int q = 0; q < P && !rc; q++) {
 		rc = create_from_device(&h->panel[q], d_prp + (int64_t) q * (m + 1), d_pcol + base[q], d_pval + base[q], m, h->n, tot[q], sub_opts);
-		if (!rc)
+		if (!rc) {
 			h->npanels = q + 1;
+			// a panel never runs the host-vector entry point (the shell stages x / y): drop what an AUTO trial left behind
+			b200spmv * s = h->panel[q];
+			if (s->d_x)
+				cudaFree(s->d_x);
+			if (s->d_y)
+				cudaFree(s->d_y);
+			s->d_x = nullptr;
+			s->d_y = nullptr;
+		}
 	}
 	cudaFree(d_cnt);
 	cudaFree(d_base);

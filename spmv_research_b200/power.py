@@ -14,6 +14,11 @@ which also orders the iterations.  `exchange="mc"` stores each finished row ONCE
 multicast address (NVLS) that the switch replicates into every GPU's next-x buffer, so a rank's
 NVLink egress is 8 bytes per row instead of 8 * (P - 1).
 torch.distributed is plumbing here; the arithmetic is in libb200spmv.so.
+
+Since round 2 the loop itself lives under the C-ABI (csrc/power.cu: b200spmv_power_*, NCCL bound inside the library, CUDA
+graph captured in C, scalar arithmetic in a one-thread kernel); `CPowerIteration` below is the thin caller and the default
+of bench.py.  `ShardedPowerIteration` (the round-1 Python loop over torch.distributed) is kept as a second, independent
+implementation of the same exchange for cross-checks and for the multicast experiment.
 """
 import numpy as np
 import torch
@@ -200,3 +205,50 @@ class ShardedPowerIteration:
     def vector(self):
         """The current normalised iterate (host copy)."""
         return (self.cur * self.scale).cpu().numpy()
+
+
+class CPowerIteration:
+    """Thin caller of b200spmv_power_* (include/b200spmv.h, csrc/power.cu).  The only thing Python contributes is carrying
+    the 128-byte NCCL id from rank 0 to the other ranks (torch.distributed when initialised, else `uid`)."""
+
+    EXCHANGE = {"nccl": 0, "fused": 1, "p2p": 1}
+
+    def __init__(self, MF, bounds, n, rank, world, device_index, exchange="fused", chunks=0, use_graph=True, scalar_sync=0,
+                 full_exchange=False, uid=None):
+        from . import capi
+        self.rank, self.world = rank, world
+        self.comm = None
+        if world > 1:
+            if uid is None:
+                box = [capi.comm_unique_id() if rank == 0 else None]
+                dist.broadcast_object_list(box, src=0)
+                uid = box[0]
+            self.comm = capi.Comm(uid, rank, world, device_index)
+        self.pw = capi.Power(MF.handle, self.comm, bounds, n, exchange=self.EXCHANGE[exchange], chunks=chunks,
+                             full_exchange=full_exchange, use_graph=use_graph, scalar_sync=scalar_sync)
+        self._eig = float("nan")
+
+    def set_start(self, x0):
+        self.pw.set_start(x0)
+
+    def iterate(self, iters):
+        """Runs `iters` iterations; returns their device time in ms."""
+        self._eig, ms = self.pw.iterate(iters)
+        return ms
+
+    def step(self):
+        self.iterate(1)
+
+    def eigenvalue(self):
+        return self._eig
+
+    def get_x(self):
+        return self.pw.get_x()
+
+    def info(self):
+        return self.pw.info()
+
+    def close(self):
+        self.pw.close()
+        if self.comm is not None:
+            self.comm.close()

@@ -35,6 +35,7 @@ def test_struct_layouts_match_the_header(native, tmp_path):
     _check(tmp_path, "b200spmv_opts", capi.Opts)
     _check(tmp_path, "b200spmv_launch", capi.Launch)
     _check(tmp_path, "b200spmv_pcg_result", capi.PcgResult)
+    _check(tmp_path, "b200spmv_power_opts", capi.PowerOpts)
 
 
 def test_every_opts_field_of_the_header_is_mirrored(native):

@@ -399,6 +399,33 @@ def test_column_panels(S, oracle, golden_matrices):
     MF = S.csr_to_format(rp, col, val, p.rows, p.cols, int(rp[-1]))
     assert MF.handle.stats()["col_panels"] == 1
     MF.close()
+    # panels whose rows are compressed (rows empty IN A PANEL go through the zero-rows pass, which must keep the earlier panels'
+    # partial, apply the scale, feed the peers and the norm): forced compression, plain and fused epilogue
+    for n, rp2, col2, val2 in cases[:3] + cases[-4:]:
+        m2, nnz2 = len(rp2) - 1, int(rp2[-1])
+        if nnz2 == 0 or m2 == 0:
+            continue
+        x2 = M.rand_x(n, 12)
+        MF, y = _spmv(S, dict(format=S.CSR_ADAPTIVE, col_panels=3, csr_compress_rows=2), rp2, col2, val2, n, x2)
+        _check(oracle, rp2, col2, val2, x2, y, "compressed panels")
+        dx2 = torch.from_numpy(x2).to(dev)
+        dy = torch.full((m2,), 7.0, dtype=torch.float64, device=dev)
+        peer = torch.zeros(m2, dtype=torch.float64, device=dev)
+        scale = torch.tensor([-0.5], dtype=torch.float64, device=dev)
+        norm2 = torch.zeros(1, dtype=torch.float64, device=dev)
+        MF.spmv_device(dx2, dy, st, scale=scale, norm2=norm2, peers=[peer])
+        torch.cuda.synchronize()
+        y = dy.cpu().numpy()
+        yr2 = oracle.csr_spmv(rp2, col2, val2, x2)
+        assert np.all(np.abs(y + 0.5 * yr2) <= REL * oracle.row_abs_bound(rp2, col2, val2, x2))
+        assert np.array_equal(peer.cpu().numpy(), y)
+        assert abs(norm2.item() - float(np.sum(y * y))) <= 1e-12 * max(float(np.sum(y * y)), 1e-300)
+        MF.close()
+    # a malformed row_ptr is refused at create time (it would send the kernels out of bounds)
+    bad = rp.copy()
+    bad[5] = bad[6] + 3
+    with pytest.raises(S.B200Error, match="malformed"):
+        S.csr_to_format(bad, col, val, p.rows, p.cols, int(rp[-1]))
     # PCG over a panel shell
     rps, cols, vals = M.spd_matrix(20000, 6, 8)
     b = np.random.default_rng(9).uniform(-1, 1, 20000)
@@ -493,7 +520,8 @@ def test_reference_harness_drives_the_plugin(S, oracle, tmp_path):
     """Drop-in proof: the reference's unmodified harness (bench.cpp + bench_spmv.cpp, built by oracle/Makefile) linked with
     host/b200_plugin.cpp loads a Matrix Market file, calls csr_to_format + spmv(x, y) in its own timing loop and validates
     y against its _Float128 Kahan gold (bench_spmv.cpp:108-235): no "Test failed", tiny mae, our format name in its CSV row."""
-    from spmv_research_b200 import amg, refharness as RH
+    from spmv_research_b200 import amg
+    import refharness as RH
     if not RH.available("spmv_b200_csr_d.exe"):
         pytest.skip("oracle/_ref harness executables not built (needs /root/reference at build time)")
     p = amg.MatrixParams.parse("30000 30000 12 6 normal random 0.3 50 0.5 0.5 14")

@@ -141,7 +141,7 @@ def test_pcg_vs_reference_cg_harness(oracle, tmp_path):
     into oracle/_ref/cg_csr_d.exe): same eps, same iteration count, the same ||r_k|| at every iteration (the harness prints
     4 significant digits; its dot products are OpenMP-reduced, so later iterates agree to rounding noise only) and the same
     explicit residual at exit.  b = ones as in bench_cg.cpp:512-516 when no _b.mtx file exists."""
-    from spmv_research_b200 import refharness as RH
+    import refharness as RH
     if not RH.available("cg_csr_d.exe"):
         pytest.skip("oracle/_ref/cg_csr_d.exe not built (needs /root/reference at build time)")
     for n, per_row, seed, cap in ((3000, 6, 1, 500), (800, 10, 2, 500), (3000, 6, 1, 7)):
@@ -169,7 +169,7 @@ def test_bicgstab_vs_reference_bicg_harness(oracle, tmp_path):
     """oracle_bicgstab pinned against the reference's OWN BiCGSTAB harness (bench.cpp + bench_bicg.cpp + K/csr.cpp, compiled
     unmodified into oracle/_ref/bicg_csr_d.exe): it runs exactly CG_MAX_NUM_ITERS iterations (no stop test), prints ||r_k|| at
     the top of every iteration (4 significant digits) and the explicit residual of the returned x_best at exit."""
-    from spmv_research_b200 import refharness as RH
+    import refharness as RH
     if not RH.available("bicg_csr_d.exe"):
         pytest.skip("oracle/_ref/bicg_csr_d.exe not built (needs /root/reference at build time)")
     cases = (("dd", M.dd_matrix(3000, 6, 1), 3000, 40), ("lap", M.convdiff_matrix(60, 0.0), 3600, 230),
@@ -295,7 +295,8 @@ def test_reference_f_harness_error_level(oracle, tmp_path):
     CSR plugin: runs, reports float-level errors against the _Float128 gold -- and trips its own 1e-7 relative criterion
     (bench_spmv.cpp:116,198).  The fp32 oracle agrees with what it computes (same mae to the printed digits), which is the
     level tests/test_zz_f32_device.py holds the GPU plugin to."""
-    from spmv_research_b200 import amg, refharness as RH
+    from spmv_research_b200 import amg
+    import refharness as RH
     if not RH.available("spmv_csr_f.exe"):
         pytest.skip("oracle/_ref/spmv_csr_f.exe not built (needs /root/reference at build time)")
     p = amg.MatrixParams.parse("30000 30000 12 6 normal random 0.3 50 0.5 0.5 14")

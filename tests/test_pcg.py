@@ -73,7 +73,7 @@ def test_reference_cg_harness_drives_the_plugin(native, oracle, tmp_path):
     """The reference's unmodified CG harness (bench.cpp + bench_cg.cpp) linked with host/b200_plugin.cpp: its
     preconditioned_cg() calls MF->spmv with a different x every iteration, so the plugin runs with B200SPMV_TRANSFER=always
     (the reference's own GPU plugins cache x and fail here).  Same iteration count as the oracle (+- 2), converged."""
-    from spmv_research_b200 import refharness as RH
+    import refharness as RH
     if not RH.available("cg_b200_d.exe"):
         pytest.skip("oracle/_ref/cg_b200_d.exe not built (needs /root/reference at build time)")
     n = 3000

@@ -108,7 +108,7 @@ def test_device_bicgstab_error_paths(native):
 def test_reference_bicg_harness_drives_the_plugin(native, oracle, tmp_path):
     """The reference's unmodified BiCGSTAB harness (bench.cpp + bench_bicg.cpp) linked with host/b200_plugin.cpp
     (B200SPMV_TRANSFER=always: x changes every call): the ||r_k|| trace of the oracle and a converged x_best."""
-    from spmv_research_b200 import refharness as RH
+    import refharness as RH
     if not RH.available("bicg_b200_d.exe"):
         pytest.skip("oracle/_ref/bicg_b200_d.exe not built (needs /root/reference at build time)")
     n = 3000

@@ -69,7 +69,8 @@ def test_reference_f_harness_drives_the_f32_plugin(native, oracle, tmp_path):
     (oracle/Makefile: obj_f/) linked with host/b200_plugin.cpp in its fp32 mode.  The reference's own CPU CSR plugin FAILS the
     harness's float criterion (relative max diff > 1e-7, bench_spmv.cpp:116,198: 5.8e-7 on this matrix), so the bar is the
     reference `_f` run's own error level, not the absence of "Test failed"."""
-    from spmv_research_b200 import amg, refharness as RH
+    from spmv_research_b200 import amg
+    import refharness as RH
     if not (RH.available("spmv_b200_csr_f.exe") and RH.available("spmv_csr_f.exe")):
         pytest.skip("oracle/_ref `_f` harness executables not built (needs /root/reference at build time)")
     p = amg.MatrixParams.parse("30000 30000 12 6 normal random 0.3 50 0.5 0.5 14")
