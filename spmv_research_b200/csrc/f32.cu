@@ -39,6 +39,14 @@ __device__ __forceinline__ float ld_stream_f32(const float * p, uint64_t pol)
 	return r;
 }
 
+// x gathers like the fp64 kernel's: L1-allocating, L2 evict_last (x is the only data with reuse)
+__device__ __forceinline__ float ld_x_f32(const float * p, uint64_t pol)
+{
+	float r;
+	asm volatile("ld.global.nc.L1::evict_last.L2::cache_hint.f32 %0, [%1], %2;" : "=f"(r) : "l"(p), "l"(pol));
+	return r;
+}
+
 __global__ void __launch_bounds__(256) f32_narrow_kernel(const double * __restrict__ in, float * __restrict__ out, int64_t n)
 {
 	for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x)
@@ -62,6 +70,7 @@ f32_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 	const int tid = threadIdx.x;
 	const int64_t tile = blockIdx.x;
 	const uint64_t pol_stream = make_policy_evict_first();
+	const uint64_t pol_x = make_policy_evict_last();
 	const int64_t base0 = tile * (int64_t) F32_T;
 
 	int c[F32_NPT];
@@ -76,7 +85,7 @@ f32_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 	f32_geometry(row_ptr, tile_row, tile, ntiles, m, nnz, F32_T, &g);
 	#pragma unroll
 	for (int k = 0; k < F32_NPT; k++)
-		v[k] = __fmul_rn(v[k], __ldg(x + c[k]));
+		v[k] = __fmul_rn(v[k], ld_x_f32(x + c[k], pol_x));
 	#pragma unroll
 	for (int k = 0; k < F32_NPT; k++)
 		s_prod[k * F32_THREADS + tid] = v[k];
@@ -103,18 +112,21 @@ f32_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 				tail[tile] = acc;
 		}
 	} else {
-		// warp per row: lanes stride the piece, butterfly reduction
-		const int lane = tid & 31, warp = tid >> 5;
-		for (int64_t r = g.r_first + warp; r <= g.r_last; r += F32_THREADS / 32) {
-			int a, b;
-			const int kind = f32_row_piece(row_ptr, &g, r, &a, &b);
+		// LPR lanes per row (f32_tile.h): lanes stride the piece, butterfly reduction inside the group
+		const int lpr = f32_lanes_per_row(nrows);
+		const int groups = F32_THREADS / lpr, grp = tid / lpr, lane = tid % lpr;
+		for (int64_t rb = g.r_first; rb <= g.r_last; rb += groups) {
+			const int64_t r = rb + grp;
+			const bool active = (r <= g.r_last);
+			int a = 0, b = 0, kind = 0;
+			if (active)
+				kind = f32_row_piece(row_ptr, &g, r, &a, &b);
 			float acc = 0.0f;
-			for (int j = a + lane; j < b; j += 32)
+			for (int j = a + lane; j < b; j += lpr)
 				acc = __fadd_rn(acc, s_prod[j]);
-			#pragma unroll
-			for (int o = 16; o > 0; o >>= 1)
+			for (int o = lpr >> 1; o > 0; o >>= 1)
 				acc = __fadd_rn(acc, __shfl_xor_sync(0xffffffffu, acc, o));
-			if (lane == 0) {
+			if (active && lane == 0) {
 				if (kind == 1)
 					y[r] = acc;
 				else if (kind == 2)

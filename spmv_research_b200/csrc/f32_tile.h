@@ -89,5 +89,15 @@ F32_FN int f32_fixup(const int32_t * row_ptr, const int32_t * tile_row, const fl
 	return 1;
 }
 
-/* butterfly partner order of the warp reduction (what __shfl_xor_sync with 16, 8, 4, 2, 1 computes in lane 0) */
-#define F32_WARP_ROWS_BELOW 64      /* fewer rows than this in a window: one warp per row; otherwise one thread per row */
+/* Row reduction bins.  >= F32_WARP_ROWS_BELOW rows in a window: one thread per row (sequential ascending-j sum).  Fewer: LPR
+ * adjacent lanes per row, LPR = the largest power of two in [4, 32] with rows * LPR <= 256 (every row of the window is then
+ * reduced in one pass of the CTA); lane l of a group sums the elements a + l, a + l + LPR, ... of its row, then the group
+ * combines with the butterfly of __shfl_xor_sync (offsets LPR / 2, ..., 1): group lane 0 holds the sum. */
+#define F32_WARP_ROWS_BELOW 64
+F32_FN int f32_lanes_per_row(int64_t nrows)
+{
+	int lpr = 4;
+	while (lpr < 32 && nrows * (lpr * 2) <= 256)
+		lpr *= 2;
+	return lpr;
+}

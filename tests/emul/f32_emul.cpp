@@ -3,7 +3,7 @@
  *
  * The fp32 CSR product of spmv_research_b200/csrc/f32.cu replayed on the CPU with the kernel's own bookkeeping
  * (csrc/f32_tile.h compiled as plain C++): narrowing, tile_row search, one "CTA" per window with the 256 threads / 8 warps
- * executed in turn (products to the window buffer; thread-per-row or warp-per-row reduction with the butterfly order of
+ * executed in turn (products to the window buffer; thread-per-row or lanes-per-row reduction with the butterfly order of
  * __shfl_xor_sync; y / carry / tail stores), then the fix-up.  Every float operation happens in the device's order, so
  * the result is what the GPU must produce bit for bit.  writes[r] counts the stores to y[r] (must be exactly 1).
  * Build with -ffp-contract=off (the device code uses __fmul_rn / __fadd_rn: no FMA).
@@ -70,20 +70,25 @@ extern "C" int f32_emul_spmv(const int32_t * row_ptr, const int32_t * col_ind, c
 						tail[tile] = acc;
 				}
 		} else {
-			for (int warp = 0; warp < THREADS / 32; warp++)
-				for (int64_t r = g.r_first + warp; r <= g.r_last; r += THREADS / 32) {
+			const int lpr = f32_lanes_per_row(nrows);
+			const int groups = THREADS / lpr;
+			for (int64_t rb = g.r_first; rb <= g.r_last; rb += groups)
+				for (int grp = 0; grp < groups; grp++) {
+					const int64_t r = rb + grp;
+					if (r > g.r_last)
+						continue;
 					int a, b;
 					const int kind = f32_row_piece(row_ptr, &g, r, &a, &b);
 					float acc[32], nxt[32];
-					for (int lane = 0; lane < 32; lane++) {
+					for (int lane = 0; lane < lpr; lane++) {
 						acc[lane] = 0.0f;
-						for (int j = a + lane; j < b; j += 32)
+						for (int j = a + lane; j < b; j += lpr)
 							acc[lane] = acc[lane] + s_prod[j];
 					}
-					for (int o = 16; o > 0; o >>= 1) {
-						for (int lane = 0; lane < 32; lane++)
+					for (int o = lpr >> 1; o > 0; o >>= 1) {
+						for (int lane = 0; lane < lpr; lane++)
 							nxt[lane] = acc[lane] + acc[lane ^ o];
-						for (int lane = 0; lane < 32; lane++)
+						for (int lane = 0; lane < lpr; lane++)
 							acc[lane] = nxt[lane];
 					}
 					if (kind == 1) {
