@@ -45,7 +45,9 @@ EXPERIMENTS = {
     "perm": ["-DCSR_EXP_PERM=1"],                                  # conflict-free row -> thread table (csr_perm.h); y bit-identical
     "perm_nolds128": ["-DCSR_EXP_PERM=1", "-DCSR_EXP_LDS128=0"],
     "rot_perm": ["-DCSR_EXP_ROT=1", "-DCSR_EXP_PERM=1"],           # rotation in the thread-per-row bin + table in the lanes-per-row bins
-    "rot": ["-DCSR_EXP_ROT=1"],                                    # per-row start rotation (csr_perm.h, csr_rot_build): no holes, y coalesced
+    "rot": ["-DCSR_EXP_ROT=1"],
+    "t128": ["-DCSR_EXP_THREADS=128"],                             # 128-thread CTAs, 1 024-nnz tiles, 12 resident per SM
+    "xna": ["-DCSR_EXP_XNA=1"],                                    # x gathers without L1 allocation                                    # per-row start rotation (csr_perm.h, csr_rot_build): no holes, y coalesced
 }
 
 

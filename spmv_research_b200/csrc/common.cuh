@@ -30,7 +30,10 @@ extern thread_local char g_b200_err[512];
 // ---------------------------------------------------------------------------------------------
 // Tunables of the nnz-tiled CSR kernel
 // ---------------------------------------------------------------------------------------------
-constexpr int CSR_THREADS = 256;          // threads per tile CTA
+#ifndef CSR_EXP_THREADS
+#define CSR_EXP_THREADS 256               // experiment switch (tools/sweep_exp.py): 128 = half-size CTAs, twice as many resident
+#endif
+constexpr int CSR_THREADS = CSR_EXP_THREADS;      // threads per tile CTA
 constexpr int CSR_ZERO_CTAS = 148 * 8;    // most CTAs csr_zero_rows_kernel is launched with (compressed rows); one norm slot each
 constexpr int SELL_THREADS = 128;         // threads per SELL CTA: four warps, one work item each
 constexpr int SELL_KCH = 128;             // slice columns per work item
@@ -74,11 +77,16 @@ __device__ __forceinline__ uint64_t make_policy_evict_last()
 // (A fractional evict_last policy -- createpolicy.fractional with budget / band -- was measured for x bands larger than
 // L2: <= 2 % at any budget, profiles/r01l_sweep_x_l2_budget.txt, and the run-time policy cost the long-row matrices 2-3 %;
 // removed.  Column panels, panels.cu, are what fixes those bands.)
+#ifndef CSR_EXP_XNA
+#define CSR_EXP_XNA 0                     // experiment switch: 1 = x gathers do not allocate in L1 (L2 evict_last kept)
+#endif
 template <bool HINT>
 __device__ __forceinline__ double ld_x(const double * p, uint64_t pol)
 {
 	double r;
-	if (HINT)
+	if (HINT && CSR_EXP_XNA)
+		asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(r) : "l"(p), "l"(pol));
+	else if (HINT)
 		asm volatile("ld.global.nc.L1::evict_last.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(r) : "l"(p), "l"(pol));
 	else
 		asm volatile("ld.global.nc.f64 %0, [%1];" : "=d"(r) : "l"(p));

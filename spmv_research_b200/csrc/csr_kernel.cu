@@ -92,7 +92,7 @@ __device__ __forceinline__ double block_sum_range(const double * s_prod, int a, 
 // MODE 0 = PLAIN; 1 = EPILOGUE (scale, norm partials, peer destinations: the power-iteration product);
 // 2 = FULL (adds the compressed-row map, the column-panel accumulate / partial modes and unit-range launches).
 template <int NPT, bool HINT, int MODE>
-__global__ void __launch_bounds__(CSR_THREADS, (NPT <= 4) ? 8 : ((NPT <= 8) ? 6 : ((NPT <= 16) ? 3 : 2)))
+__global__ void __launch_bounds__(CSR_THREADS, ((NPT <= 4) ? 8 : ((NPT <= 8) ? 6 : ((NPT <= 16) ? 3 : 2))) * (256 / CSR_THREADS))
 csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict__ col, const double * __restrict__ val,
                 const int2 * __restrict__ tile_info, const double * __restrict__ x,
                 double * __restrict__ tile_head, double * __restrict__ tile_tail,
