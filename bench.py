@@ -676,7 +676,8 @@ def run_power_python(args):
 POWER_VARIANTS = {
     "fused_allreduce":   dict(exchange="fused", scalar_sync=0, panels=1, chunks=0),     # round 1's default, now in C
     "fused_mailbox":     dict(exchange="fused", scalar_sync=1, panels=1, chunks=0),     # no NCCL call inside the iteration
-    "fused_mailbox_p2c4": dict(exchange="fused", scalar_sync=1, panels=2, chunks=4),    # 2 column panels interleaved over 4 row chunks
+    "fused_mailbox_p2c2": dict(exchange="fused", scalar_sync=1, panels=2, chunks=2),    # 2 column panels interleaved over 2 row chunks
+    "fused_mailbox_p2c4": dict(exchange="fused", scalar_sync=1, panels=2, chunks=4),    # ... over 4 (each chunk re-reads the panel's x)
     "fused_mailbox_p2c8": dict(exchange="fused", scalar_sync=1, panels=2, chunks=8),
     "nccl_c4":           dict(exchange="nccl", scalar_sync=0, panels=1, chunks=4),      # NCCL all-gather, chunk c under kernel c + 1
     "nccl_p2c4":         dict(exchange="nccl", scalar_sync=0, panels=2, chunks=4),
