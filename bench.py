@@ -677,10 +677,10 @@ POWER_VARIANTS = {
     "fused_allreduce":   dict(exchange="fused", scalar_sync=0, panels=1, chunks=0),     # round 1's default, now in C
     "fused_mailbox":     dict(exchange="fused", scalar_sync=1, panels=1, chunks=0),     # no NCCL call inside the iteration
     "fused_mailbox_p2c2": dict(exchange="fused", scalar_sync=1, panels=2, chunks=2),    # 2 column panels interleaved over 2 row chunks
+    "fused_mailbox_p2c3": dict(exchange="fused", scalar_sync=1, panels=2, chunks=3),
     "fused_mailbox_p2c4": dict(exchange="fused", scalar_sync=1, panels=2, chunks=4),    # ... over 4 (each chunk re-reads the panel's x)
-    "fused_mailbox_p2c8": dict(exchange="fused", scalar_sync=1, panels=2, chunks=8),
     "nccl_c4":           dict(exchange="nccl", scalar_sync=0, panels=1, chunks=4),      # NCCL all-gather, chunk c under kernel c + 1
-    "nccl_p2c4":         dict(exchange="nccl", scalar_sync=0, panels=2, chunks=4),
+    "nccl_p2c2":         dict(exchange="nccl", scalar_sync=0, panels=2, chunks=2),
 }
 
 
@@ -929,7 +929,7 @@ def run_power(args):
         bc_loc = H.compulsory_bytes(i_e - i_s, n, nnz_loc)
         gflops = 2.0 * nnz / (ms_step * 1e-3) * 1e-9
         xdesc = {"fused": "fused: the SpMV epilogue stores each finished y row of the band into every peer's next-x buffer over NVLink (CUDA IPC)",
-                 "nccl": "NCCL: y slots all-gathered in place (grouped ncclBroadcast per owner, band rows only) per row chunk on a second stream"}[vbest["exchange"]]
+                 "nccl": "NCCL: y slots all-gathered in place (grouped ncclSend / ncclRecv between every pair, band rows only) per row chunk on a second stream"}[vbest["exchange"]]
         sdesc = "mailbox barrier over peer memory (one-warp kernel, no NCCL call in the iteration)" if vbest["scalar_sync"] else "ncclAllReduce of the norm"
         out = {
             "metric": METRIC, "value": round(gflops, 2), "unit": "GFLOP/s", "n_gpus": world, "steps": K, "warmup": W,

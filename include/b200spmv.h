@@ -245,7 +245,7 @@ void b200spmv_f32_destroy(b200spmv_f32_t * h);
  * loop_partitioner_balance_prefix_sums(), lib/parallel_util.h:156-184, gives worker p of P, see b200spmv_partition*).
  * The iteration loop, the exchange of y (the next x) and the scalar arithmetic all run under this C-ABI; a caller
  * needs nothing but a way to hand a 128-byte id from rank 0 to the other ranks (a file, MPI, a torch store).
- *   exchange B200SPMV_X_NCCL : y slots all-gathered over NVLink with NCCL (grouped ncclBroadcast, unequal counts, in place in
+ *   exchange B200SPMV_X_NCCL : y slots all-gathered over NVLink with NCCL (grouped ncclSend / ncclRecv, unequal counts, in place in
  *                              the next-x buffer), band-limited (only rows some rank's columns reference), in `chunks` row
  *                              chunks so that chunk c travels under the kernel of chunk c + 1; ncclAllReduce of the norm.
  *   exchange B200SPMV_X_FUSED: the SpMV epilogue stores every finished row of the band straight into all peers' next-x

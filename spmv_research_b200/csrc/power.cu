@@ -6,8 +6,8 @@
 //     u' = s * (A_p u)  written into the rank's slot of the next-x buffer,  s' = 1 / ||u'||
 // with the scale folded into the SpMV epilogue (A (s u) = s A u) and the sum of squares coming out of the same kernel.
 // Two exchanges of u':
-//   NCCL  : grouped ncclBroadcast per owner (an all-gather with unequal counts, in place), band-limited, issued per row chunk on
-//           a second stream so that chunk c travels while chunk c + 1 is computed; ncclAllReduce of the norm;
+//   NCCL  : grouped ncclSend / ncclRecv between every pair (an all-gather with unequal counts, in place), band-limited, issued per
+//           row chunk on a second stream so that chunk c travels while chunk c + 1 is computed; ncclAllReduce of the norm;
 //   FUSED : the epilogue stores each finished row of the band into every peer's next-x buffer (NVLink P2P stores through CUDA
 //           IPC mappings); what is left per iteration is one scalar synchronisation -- ncclAllReduce, or a mailbox barrier
 //           written by a one-warp kernel (each rank posts its sum of squares + a sequence number into every peer's mailbox,
@@ -37,6 +37,8 @@ struct NcclApi {
 	decltype(&ncclAllReduce) AllReduce;
 	decltype(&ncclBroadcast) Broadcast;
 	decltype(&ncclAllGather) AllGather;
+	decltype(&ncclSend) Send;
+	decltype(&ncclRecv) Recv;
 	decltype(&ncclGroupStart) GroupStart;
 	decltype(&ncclGroupEnd) GroupEnd;
 	decltype(&ncclGetErrorString) GetErrorString;
@@ -67,6 +69,8 @@ static int nccl_load()
 	NCCL_SYM(AllReduce, "ncclAllReduce")
 	NCCL_SYM(Broadcast, "ncclBroadcast")
 	NCCL_SYM(AllGather, "ncclAllGather")
+	NCCL_SYM(Send, "ncclSend")
+	NCCL_SYM(Recv, "ncclRecv")
 	NCCL_SYM(GroupStart, "ncclGroupStart")
 	NCCL_SYM(GroupEnd, "ncclGroupEnd")
 	NCCL_SYM(GetErrorString, "ncclGetErrorString")
@@ -402,15 +406,26 @@ static int one_iteration(b200spmv_power * pw)
 			}
 			CU(cudaEventRecord(pw->ev_chunk[c], pw->st));
 			CU(cudaStreamWaitEvent(pw->cst, pw->ev_chunk[c], 0));
+			// all-gather with unequal counts, in place: every rank sends the band rows of its chunk c to every peer and receives
+			// theirs, one grouped ncclSend / ncclRecv exchange (direct peer-to-peer over NVSwitch; measured at N = 8: 8 grouped ring
+			// broadcasts per chunk cost 2.2 ms per iteration, profiles/r02n8_bench_n8.json)
+			int64_t lo[PW_MAXW], hi[PW_MAXW];
+			for (int q = 0; q < pw->world; q++) {
+				lo[q] = pw->all_final[q][c];
+				hi[q] = pw->all_final[q][c + 1];
+				if (!pw->full_exchange) {
+					lo[q] = lo[q] > pw->band_lo ? lo[q] : pw->band_lo;
+					hi[q] = hi[q] < pw->band_hi ? hi[q] : pw->band_hi;
+				}
+			}
 			NC(g_nccl.GroupStart());
 			for (int q = 0; q < pw->world; q++) {
-				int64_t lo = pw->all_final[q][c], hi = pw->all_final[q][c + 1];
-				if (!pw->full_exchange) {
-					lo = lo > pw->band_lo ? lo : pw->band_lo;
-					hi = hi < pw->band_hi ? hi : pw->band_hi;
-				}
-				if (hi > lo)
-					NC(g_nccl.Broadcast(nxt + lo, nxt + lo, (size_t) (hi - lo), ncclDouble, q, pw->comm->comm, pw->cst));
+				if (q == pw->rank)
+					continue;
+				if (hi[pw->rank] > lo[pw->rank])
+					NC(g_nccl.Send(nxt + lo[pw->rank], (size_t) (hi[pw->rank] - lo[pw->rank]), ncclDouble, q, pw->comm->comm, pw->cst));
+				if (hi[q] > lo[q])
+					NC(g_nccl.Recv(nxt + lo[q], (size_t) (hi[q] - lo[q]), ncclDouble, q, pw->comm->comm, pw->cst));
 			}
 			NC(g_nccl.GroupEnd());
 		}
