@@ -516,7 +516,10 @@ int launch_csr_spmv(b200spmv * h, const double * dx, double * dy, cudaStream_t s
 	if (csr_make_out(h, dy, l, out))
 		return 1;
 	int64_t zero_ctas = 0;
-	if (h->compressed && h->n_empty > 0) {
+	// rows that are empty in THIS handle: a plain handle writes them 0; a column panel that accumulates already has the earlier
+	// panels' partial in y, so a middle panel has nothing to do for them, nor has the last panel of a product without epilogue
+	const bool rows_keep_y = out.accum && (out.partial || (!out.scale && out.n_peer == 0 && !out.norm_partial));
+	if (h->compressed && h->n_empty > 0 && !rows_keep_y) {
 		const int64_t want = (h->n_empty + 255) / 256;
 		zero_ctas = want < CSR_ZERO_CTAS ? want : CSR_ZERO_CTAS;
 		csr_zero_rows_kernel<<<(unsigned) zero_ctas, 256, 0, st>>>(h->d_empty_rows, h->n_empty, out, h->ntiles + h->nsplit);
