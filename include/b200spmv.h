@@ -133,7 +133,7 @@ int32_t b200spmv_format(const b200spmv_t * h);
  * outside that range, so b200spmv_spmv_host uploads only x[lo..hi) and a multi-GPU exchange only needs those rows. */
 int b200spmv_col_range(const b200spmv_t * h, int64_t * lo, int64_t * hi);
 
-/* Number of kernel launches one b200spmv_spmv_device call issues for this handle (1 to 3). */
+/* Number of kernel launches one b200spmv_spmv_device call issues for this handle (CSR: 1, + 1 with compressed rows; SELL: 1, + 1 with cut slices; panels: the sum). */
 int32_t b200spmv_launches_per_spmv(const b200spmv_t * h);
 
 /* Format statistics: out[0]=mem_footprint bytes, [1]=ntiles or nslices, [2]=nsplit rows,

@@ -228,7 +228,7 @@ static void free_sell(b200spmv * h)
 static void free_csr_plan(b200spmv * h, bool arrays)
 {
 	void ** ptrs[] = { (void **) &h->d_tile_row, (void **) &h->d_split_row, (void **) &h->d_split_tile, (void **) &h->d_tile_head,
-	                   (void **) &h->d_tile_tail };
+	                   (void **) &h->d_tile_tail, (void **) &h->d_tile_split, (void **) &h->d_split_info, (void **) &h->d_split_cnt };
 	for (void ** p : ptrs) {
 		if (*p)
 			cudaFree(*p);
@@ -445,7 +445,7 @@ static void free_handle(b200spmv * h)
 	for (cudaEvent_t e : h->up_ev)
 		if (e)
 			cudaEventDestroy(e);
-	void * ptrs[] = { h->d_row_ptr, h->d_col, h->d_val, h->d_tile_row, h->d_split_row, h->d_split_tile, h->d_tile_head, h->d_tile_tail, h->d_perm, h->d_perm_off, h->d_rot,
+	void * ptrs[] = { h->d_row_ptr, h->d_col, h->d_val, h->d_tile_row, h->d_split_row, h->d_split_tile, h->d_tile_head, h->d_tile_tail, h->d_perm, h->d_perm_off, h->d_rot, h->d_tile_split, h->d_split_info, h->d_split_cnt,
 	                  h->d_row_order, h->d_slice_width, h->d_slice_ptr, h->d_scol, h->d_sval, h->d_x, h->d_y, h->d_norm_partial,
 	                  h->d_sell_items, h->d_sell_cuts, h->d_sell_partial, h->d_rp_nz, h->d_rows_nz, h->d_empty_rows, h->d_diag };
 	for (void * p : ptrs)
@@ -626,7 +626,7 @@ extern "C" int32_t b200spmv_launches_per_spmv(const b200spmv_t * h)
 		return n;
 	}
 	if (h->format == B200SPMV_CSR_ADAPTIVE)
-		return (h->nsplit > 0 ? 2 : 1) + ((h->compressed && h->n_empty > 0) ? 1 : 0);
+		return 1 + ((h->compressed && h->n_empty > 0) ? 1 : 0);      // split rows are finished inside the tile kernel
 	return h->sell_ncuts > 0 ? 2 : 1;
 }
 

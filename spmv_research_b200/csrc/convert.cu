@@ -155,6 +155,26 @@ __global__ void split_compact_kernel(const int2 * __restrict__ tile_info, const 
 	}
 }
 
+// What csr_fold_split_rows needs: per tile the split row it owns / is entered by, per split row its owner tile and the number
+// of tiles that contribute a partial (owner + every tile up to the one holding the row's last entry).
+__global__ void split_fold_kernel(const int2 * __restrict__ tile_info, const int64_t * __restrict__ split_pos, int64_t ntiles, int64_t nsplit,
+                                  const int32_t * __restrict__ row_ptr, int T, int2 * __restrict__ tile_split, int4 * __restrict__ split_info)
+{
+	const int64_t t = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= ntiles)
+		return;
+	const int64_t pos = split_pos[t];
+	const int64_t nxt = (t + 1 < ntiles) ? split_pos[t + 1] : nsplit;
+	const int own = (nxt > pos) ? (int) pos : -1;
+	const int head = (tile_info[t].x < 0) ? (int) pos - 1 : -1;      // entered by the split row of the latest owner before t
+	tile_split[t] = make_int2(own, head);
+	if (own >= 0) {
+		const int row = (tile_info[t + 1].x & 0x7fffffff) - 1;
+		const int64_t last = ((int64_t) row_ptr[row + 1] - 1) / T;
+		split_info[own] = make_int4(row, (int) t, (int) (last - t + 1), 0);
+	}
+}
+
 // ---- row compression ---------------------------------------------------------------------------
 __global__ void nonempty_flag_kernel(const int32_t * __restrict__ row_ptr, int64_t m, int64_t * __restrict__ flag)
 {
@@ -195,7 +215,8 @@ __global__ void max_owned_rows_kernel(const int2 * __restrict__ tile_info, int64
 static void free_tile_plan(b200spmv * h)
 {
 	void ** ptrs[] = { (void **) &h->d_tile_row, (void **) &h->d_split_row, (void **) &h->d_split_tile, (void **) &h->d_tile_head,
-	                   (void **) &h->d_tile_tail, (void **) &h->d_perm, (void **) &h->d_perm_off, (void **) &h->d_rot };
+	                   (void **) &h->d_tile_tail, (void **) &h->d_perm, (void **) &h->d_perm_off, (void **) &h->d_rot,
+	                   (void **) &h->d_tile_split, (void **) &h->d_split_info, (void **) &h->d_split_cnt };
 	for (void ** q : ptrs) {
 		if (*q)
 			cudaFree(*q);
@@ -300,6 +321,14 @@ static int plan_tiles_on(b200spmv * h)
 		CU(cudaMalloc(&h->d_split_tile, h->nsplit * sizeof(int32_t)));
 		split_compact_kernel<<<(unsigned) ((h->ntiles + 255) / 256), 256, 0, h->stream>>>(
 			reinterpret_cast<const int2 *>(h->d_tile_row), d_flag, h->ntiles, h->nsplit, h->d_split_row, h->d_split_tile);
+		CU_LAUNCH();
+		CU(cudaMalloc(&h->d_tile_split, h->ntiles * sizeof(int2)));
+		CU(cudaMalloc(&h->d_split_info, h->nsplit * sizeof(int4)));
+		CU(cudaMalloc(&h->d_split_cnt, h->nsplit * sizeof(unsigned int)));
+		CU(cudaMemsetAsync(h->d_split_cnt, 0, h->nsplit * sizeof(unsigned int), h->stream));
+		split_fold_kernel<<<(unsigned) ((h->ntiles + 255) / 256), 256, 0, h->stream>>>(
+			reinterpret_cast<const int2 *>(h->d_tile_row), d_flag, h->ntiles, h->nsplit, h->d_rp_plan, T,
+			reinterpret_cast<int2 *>(h->d_tile_split), reinterpret_cast<int4 *>(h->d_split_info));
 		CU_LAUNCH();
 	}
 	CU(cudaStreamSynchronize(h->stream));

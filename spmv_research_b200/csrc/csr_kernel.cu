@@ -17,8 +17,8 @@
 //  * a row belongs to the tile in which it STARTS.  The owner finishes the row even when it
 //    leaves the window, by loading up to EXT further non-zeros ("tail extension"), so ordinary
 //    matrices need one launch and no carry fix-up.  Only rows sticking out by more than EXT
-//    ("split" rows: the generator's giant skew rows) are completed by csr_fixup_kernel from
-//    per-tile head/tail partials in a fixed order -- deterministic, no atomics
+//    ("split" rows: the generator's giant skew rows) are completed from per-tile head/tail partials in a fixed
+//    order by whichever of their tiles finishes last (csr_fold_split_rows) -- deterministic, no atomics on y
 //    (cf. cuda_csr_const_nnz_per_thread.cu:578-659,864 which uses atomicAdd + memset);
 //  * per tile the row reduction is binned by the number of rows it owns: thread per row (short
 //    rows, sequential ascending-j sum = the oracle's order), 2..32 lanes per row with shuffle
@@ -86,6 +86,65 @@ __device__ __forceinline__ double block_sum_range(const double * s_prod, int a, 
 	return tot;
 }
 
+// Split rows are finished inside the tile kernel (round 2; round 1 used a second launch, csr_fixup_kernel: 4.5 us + a launch gap
+// on a ~115 us product).  Every tile a split row touches -- its owner (tail partial) and the tiles it enters (head partials) --
+// bumps the row's counter after publishing its partial; the CTA that arrives last sums tail[owner], head[owner + 1], ...,
+// head[last] in a FIXED order (thread j takes entries j, j + 256, ...; butterfly; warps in order), so y does not depend on
+// which CTA happened to be last: deterministic, still no atomics on y.  The counter is reset by the finisher.
+struct SplitFold {
+	const int2 * tile_split;      // per tile: {split row owned (tail) or -1, split row entering (head) or -1}
+	const int4 * info;            // per split row: {row (plan space), owner tile, number of contributing tiles, 0}
+	unsigned int * cnt;           // per split row: contributions so far
+	int64_t ntiles;
+};
+
+template <int MODE>
+__device__ __noinline__ void csr_fold_split_rows(int64_t tile, bool tail_split, bool head_split, SplitFold sf, const double * tile_head,
+                                                 const double * tile_tail, const int32_t * rowmap, YOut out, double scale, double * s_red)
+{
+	__shared__ int s_last;
+	const int tid = threadIdx.x;
+	const int2 ts = sf.tile_split[tile];
+	#pragma unroll 1
+	for (int which = 0; which < 2; which++) {
+		const int s = (which == 0) ? (head_split ? ts.y : -1) : (tail_split ? ts.x : -1);
+		if (s < 0)
+			continue;                               // uniform over the CTA
+		const int4 info = sf.info[s];
+		if (tid == 0) {
+			__threadfence();                        // this tile's partial (written by this thread) before the count
+			const unsigned int old = atomicAdd(&sf.cnt[s], 1u);
+			s_last = (old + 1u == (unsigned int) info.z) ? 1 : 0;
+		}
+		__syncthreads();
+		if (s_last) {
+			__threadfence();
+			double acc = 0.0;
+			for (int j = tid; j < info.z; j += CSR_THREADS)
+				acc += (j == 0) ? __ldcg(tile_tail + info.y) : __ldcg(tile_head + info.y + j);
+			acc = warp_sum(acc);
+			if ((tid & 31) == 0)
+				s_red[tid >> 5] = acc;
+			__syncthreads();
+			if (tid == 0) {
+				double tot = 0.0;
+				#pragma unroll
+				for (int w = 0; w < CSR_THREADS / 32; w++)
+					tot += s_red[w];
+				if constexpr (MODE == 0) {
+					out.y[info.x] = tot;
+				} else {
+					tot = y_finish(out, (MODE == 2 && rowmap) ? rowmap[info.x] : info.x, tot, scale);
+					if (out.norm_partial)
+						out.norm_partial[sf.ntiles + s] = tot * tot;
+				}
+				sf.cnt[s] = 0u;                         // ready for the next product of this handle
+			}
+		}
+		__syncthreads();
+	}
+}
+
 // PLAIN: the product as the harness calls it (y = A x, nothing else): no row map, scale, norm, peer destinations or
 // panel accumulation.  The kernel sits at its 40-register cap (6 CTAs per SM); each of those features measurably slowed
 // the plain product when it was a run-time branch (+5 % in total), so they are compiled out of this instantiation.
@@ -96,7 +155,7 @@ __global__ void __launch_bounds__(CSR_THREADS, ((NPT <= 4) ? 8 : ((NPT <= 8) ? 6
 csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict__ col, const double * __restrict__ val,
                 const int2 * __restrict__ tile_info, const double * __restrict__ x,
                 double * __restrict__ tile_head, double * __restrict__ tile_tail,
-                int64_t nnz, int ext_cap, const int32_t * __restrict__ rowmap, int64_t tile_base, YOut out CSR_PERM_PARAMS)
+                int64_t nnz, int ext_cap, const int32_t * __restrict__ rowmap, int64_t tile_base, YOut out, SplitFold sf CSR_PERM_PARAMS)
 {
 	constexpr bool PLAIN = (MODE == 0);
 	constexpr int T = CSR_THREADS * NPT;
@@ -344,6 +403,8 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 		if (tid == 0)
 			tile_head[tile] = part;
 	}
+	if (tail_split || head_split)
+		csr_fold_split_rows<MODE>(tile, tail_split, head_split, sf, tile_head, tile_tail, rowmap, out, scale, s_red);
 
 	// 7. optional sum of squares of the rows written here (power iteration norm, no atomics)
 	if constexpr (!PLAIN)
@@ -360,32 +421,6 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 				tot += s_red[w];
 			out.norm_partial[tile] = tot;
 		}
-	}
-}
-
-// One warp per split row: y[row] = tail[owner] + head[owner+1] + ... + head[last], fixed order.
-__global__ void csr_fixup_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict__ split_row,
-                                 const int32_t * __restrict__ split_tile, const double * __restrict__ tile_head,
-                                 const double * __restrict__ tile_tail, int64_t nsplit, int tile_nnz, int64_t ntiles,
-                                 const int32_t * __restrict__ rowmap, YOut out)
-{
-	const int64_t s = blockIdx.x;
-	if (s >= nsplit)
-		return;
-	const int lane = threadIdx.x;
-	const int row = split_row[s];
-	const int64_t k = split_tile[s];
-	const int64_t e = row_ptr[row + 1];
-	const int64_t last = (e - 1) / tile_nnz;
-	double acc = (lane == 0) ? tile_tail[k] : 0.0;
-	for (int64_t t = k + 1 + lane; t <= last; t += 32)
-		acc += tile_head[t];
-	acc = warp_sum(acc);
-	if (lane == 0) {
-		const double scale = out.scale ? *out.scale : 1.0;
-		acc = y_finish(out, rowmap ? rowmap[row] : row, acc, scale);
-		if (out.norm_partial)
-			out.norm_partial[ntiles + s] = acc * acc;
 	}
 }
 
@@ -456,9 +491,14 @@ static int launch_tiles_impl(b200spmv * h, const double * dx, cudaStream_t st, c
 	const int64_t count = h->range_count >= 0 ? h->range_count : h->ntiles;
 	if (count <= 0)
 		return 0;
+	SplitFold sf;
+	sf.tile_split = reinterpret_cast<const int2 *>(h->d_tile_split);
+	sf.info = reinterpret_cast<const int4 *>(h->d_split_info);
+	sf.cnt = h->d_split_cnt;
+	sf.ntiles = h->ntiles;
 	csr_tile_kernel<NPT, HINT, MODE><<<(unsigned) count, CSR_THREADS, smem, st>>>(
 		h->d_rp_plan, h->d_col, h->d_val, reinterpret_cast<const int2 *>(h->d_tile_row), dx,
-		h->d_tile_head, h->d_tile_tail, h->nnz, h->ext, h->compressed ? h->d_rows_nz : nullptr, first, out CSR_PERM_ARGS);
+		h->d_tile_head, h->d_tile_tail, h->nnz, h->ext, h->compressed ? h->d_rows_nz : nullptr, first, out, sf CSR_PERM_ARGS);
 	CU_LAUNCH();
 	return 0;
 }
@@ -527,12 +567,6 @@ int launch_csr_spmv(b200spmv * h, const double * dx, double * dy, cudaStream_t s
 	}
 	if (csr_launch_tiles(h, dx, st, out))
 		return 1;
-	if (h->nsplit > 0) {
-		csr_fixup_kernel<<<(unsigned) h->nsplit, 32, 0, st>>>(h->d_rp_plan, h->d_split_row, h->d_split_tile, h->d_tile_head,
-		                                                     h->d_tile_tail, h->nsplit, h->tile_nnz, h->ntiles,
-		                                                     h->compressed ? h->d_rows_nz : nullptr, out);
-		CU_LAUNCH();
-	}
 	if (l && l->norm2)
 		return launch_norm_reduce(h, h->ntiles + h->nsplit + zero_ctas, l->norm2, st);
 	return 0;

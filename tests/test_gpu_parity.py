@@ -71,7 +71,7 @@ def test_csr_edge_cases(S, oracle):
 
 def test_csr_split_rows_and_tile_plan(S, oracle):
     """The tile plan against a numpy model: first owned row per tile, split rows = rows leaving their
-    owner window by more than ext; giant rows take the fix-up launch."""
+    owner window by more than ext; giant rows are completed by the last of their tiles to finish."""
     for name, rp, col, val, n in M.edge_cases():
         m, nnz = len(rp) - 1, int(rp[-1])
         for npt, ext in ((8, 64), (8, 1024), (16, 2048)):
@@ -91,7 +91,7 @@ def test_csr_split_rows_and_tile_plan(S, oracle):
                     split_tiles.append(t)
             assert np.array_equal(MF.handle.export(S.capi.X_SPLIT_ROW), np.array(split_rows, np.int32)), (name, npt, ext)
             assert np.array_equal(MF.handle.export(S.capi.X_SPLIT_TILE), np.array(split_tiles, np.int32))
-            assert MF.gpu_launches_per_spmv == (2 if split_rows else 1)
+            assert MF.gpu_launches_per_spmv == 1          # split rows are finished inside the tile kernel (last-arriving CTA)
             MF.close()
 
 
@@ -119,7 +119,7 @@ def test_csr_compressed_rows(S, oracle):
         assert np.array_equal(MF.handle.export(S.capi.X_TILE_ROW), rows_nz[k].astype(np.int32)), name
         split = [rows_nz[k[t + 1] - 1] for t in range(ntiles) if k[t + 1] > k[t] and int(rp_nz[k[t + 1]]) - (t + 1) * T > ext]
         assert np.array_equal(MF.handle.export(S.capi.X_SPLIT_ROW), np.array(split, np.int32)), name
-        assert MF.gpu_launches_per_spmv == (2 if split else 1) + (1 if st["n_empty"] else 0)
+        assert MF.gpu_launches_per_spmv == 1 + (1 if st["n_empty"] else 0)
         MF.close()
     # auto: 60 000 empty rows in one run -> one tile would own them all
     rng = np.random.default_rng(3)
@@ -138,10 +138,10 @@ def test_csr_compressed_rows(S, oracle):
 
 
 def test_csr_deterministic_and_repeatable(S, golden_matrices):
-    p, rp, col, val = golden_matrices[3]                       # giant-row head: exercises the fix-up path
+    p, rp, col, val = golden_matrices[3]                       # giant-row head: exercises the split-row fold
     x = M.rand_x(p.cols)
     MF = S.csr_to_format(rp, col, val, p.rows, p.cols, int(rp[-1]), csr_ext=64)
-    assert MF.gpu_launches_per_spmv == 2
+    assert MF.gpu_launches_per_spmv == 1 and MF.handle.stats()["nsplit"] >= 1
     ys = []
     for _ in range(3):
         y = np.full(p.rows, 1.0)
@@ -511,7 +511,7 @@ def test_giant_row_full_size(S, oracle):
         MF, y = _spmv(S, kw, rp, col, val, p.cols, x)
         _check(oracle, rp, col, val, x, y, "giant %r" % kw)
         if kw["format"] == S.CSR_ADAPTIVE:
-            assert MF.gpu_launches_per_spmv == 2
+            assert MF.gpu_launches_per_spmv == 1 and MF.handle.stats()["nsplit"] >= 1
         MF.close()
 
 

@@ -8,7 +8,7 @@ the two on random and edge-case row-length profiles, with BLOCK_SIZE = T:
  * a multi-row adaptive block (<= T non-zeros by construction) lies inside at most two consecutive windows: the work one
    CSR-Adaptive CTA reduces in shared memory is what at most two tile CTAs see;
  * a row CSR-Adaptive gives a block of its own because it is longer than T (its 'CSR-vector / long row' bin) always leaves its
-   owner window: it is among the rows the tile plan finishes by tail extension or by the fix-up launch;
+   owner window: it is among the rows the tile plan finishes by tail extension or by the split-row fold;
  * the tile plan is the balanced one: ceil(nnz / T) units of exactly T non-zeros, never more units than the row blocking.
 """
 import numpy as np
@@ -71,7 +71,7 @@ def test_tile_plan_against_csr_adaptive_rowblocks(oracle, T, ext):
                 n_units_blocks += 1
             else:
                 if w > T:
-                    # CSR-Adaptive's long-row bin: in the tile plan the row leaves its owner window (extension or fix-up)
+                    # CSR-Adaptive's long-row bin: in the tile plan the row leaves its owner window (extension or split-row fold)
                     assert a in leaving, (name, a, w)
                 n_units_blocks += max(1, -(-w // T))                # a long row costs its owner ceil(w / T) windows of work
         assert max(1, -(-nnz // T)) <= max(1, n_units_blocks), name
