@@ -215,7 +215,8 @@ __global__ void rebase_row_ptr_kernel(const int32_t * __restrict__ in, int32_t *
 static void free_sell(b200spmv * h)
 {
 	void ** ptrs[] = { (void **) &h->d_row_order, (void **) &h->d_slice_width, (void **) &h->d_slice_ptr, (void **) &h->d_scol,
-	                   (void **) &h->d_sval, (void **) &h->d_sell_items, (void **) &h->d_sell_cuts, (void **) &h->d_sell_partial };
+	                   (void **) &h->d_sval, (void **) &h->d_sell_items, (void **) &h->d_sell_cuts, (void **) &h->d_sell_partial,
+	                   (void **) &h->d_sell_slot_cut, (void **) &h->d_sell_cut_cnt };
 	for (void ** p : ptrs) {
 		if (*p)
 			cudaFree(*p);
@@ -447,7 +448,7 @@ static void free_handle(b200spmv * h)
 			cudaEventDestroy(e);
 	void * ptrs[] = { h->d_row_ptr, h->d_col, h->d_val, h->d_tile_row, h->d_split_row, h->d_split_tile, h->d_tile_head, h->d_tile_tail, h->d_perm, h->d_perm_off, h->d_rot, h->d_tile_split, h->d_split_info, h->d_split_cnt,
 	                  h->d_row_order, h->d_slice_width, h->d_slice_ptr, h->d_scol, h->d_sval, h->d_x, h->d_y, h->d_norm_partial,
-	                  h->d_sell_items, h->d_sell_cuts, h->d_sell_partial, h->d_rp_nz, h->d_rows_nz, h->d_empty_rows, h->d_diag };
+	                  h->d_sell_items, h->d_sell_cuts, h->d_sell_partial, h->d_sell_slot_cut, h->d_sell_cut_cnt, h->d_rp_nz, h->d_rows_nz, h->d_empty_rows, h->d_diag };
 	for (void * p : ptrs)
 		if (p)
 			cudaFree(p);
@@ -549,7 +550,7 @@ static int create_common(b200spmv ** out, const int32_t * row_ptr, const int32_t
 		} else if (h->format == B200SPMV_AUTO) {
 			if (auto_select(h, o)) goto fail;           // convert_ms of an AUTO handle includes the trials
 			norm_slots = (h->format == B200SPMV_CSR_ADAPTIVE) ? h->ntiles + h->nsplit + CSR_ZERO_CTAS
-			                                                   : (h->sell_nitems + 3) / 4 + (h->sell_ncuts + 3) / 4;
+			                                                   : (h->sell_nitems + 3) / 4 + h->sell_ncuts;
 		} else if (h->format == B200SPMV_CSR_ADAPTIVE) {
 			if (csr_plan_tiles(h)) goto fail;
 			norm_slots = h->ntiles + h->nsplit + CSR_ZERO_CTAS;
@@ -560,7 +561,7 @@ static int create_common(b200spmv ** out, const int32_t * row_ptr, const int32_t
 			cudaFree(h->d_val);
 			h->d_col = nullptr;
 			h->d_val = nullptr;
-			norm_slots = (h->sell_nitems + 3) / 4 + (h->sell_ncuts + 3) / 4;
+			norm_slots = (h->sell_nitems + 3) / 4 + h->sell_ncuts;
 		}
 		if (plan_chunks(h)) goto fail;
 		h->norm_slots = norm_slots > 0 ? norm_slots : 1;
@@ -627,7 +628,7 @@ extern "C" int32_t b200spmv_launches_per_spmv(const b200spmv_t * h)
 	}
 	if (h->format == B200SPMV_CSR_ADAPTIVE)
 		return 1 + ((h->compressed && h->n_empty > 0) ? 1 : 0);      // split rows are finished inside the tile kernel
-	return h->sell_ncuts > 0 ? 2 : 1;
+	return 1;                                   // cut slices are finished inside the kernel (last-arriving warp)
 }
 
 // One product: a plain handle launches its kernel(s); a panel shell launches its sub-handles in ascending column order, the

@@ -200,6 +200,8 @@ struct b200spmv {
 	int32_t * d_sell_items;   // int4[sell_nitems]  {slice, first column, partial slot or -1, lane group}
 	int32_t * d_sell_cuts;    // int4[sell_ncuts]   {slice, first partial slot, items, lane group}
 	double * d_sell_partial;  // [sell_nslots * 32]
+	int32_t * d_sell_slot_cut;        // [sell_nslots] cut record of each partial slot
+	unsigned int * d_sell_cut_cnt;    // [sell_ncuts] arrival counters, zero between products
 	int64_t sell_nitems, sell_ncuts, sell_nslots;
 
 	// diag(A) for the Jacobi-preconditioned CG (keep_diag), number of rows without a non-zero diagonal entry

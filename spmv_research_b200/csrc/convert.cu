@@ -496,7 +496,7 @@ __global__ void sell_scatter_kernel(const int32_t * __restrict__ row_ptr, const 
 
 // Work items of the SpMV kernel: every slice is cut along k into chunks of SELL_KCH columns and
 // across lanes into groups of 32; a slice cut into n > 1 chunks also gets one "cut" record per lane
-// group that tells sell_fixup_kernel where its n partials lie.
+// group that tells the finishing warp where its n partials lie.
 __global__ void sell_item_count_kernel(const int32_t * __restrict__ slice_width, int64_t nslices, int G,
                                        int64_t * __restrict__ item_off, int64_t * __restrict__ slot_off, int64_t * __restrict__ cut_off)
 {
@@ -522,7 +522,7 @@ __global__ void sell_item_count_kernel(const int32_t * __restrict__ slice_width,
 __global__ void sell_item_fill_kernel(const int32_t * __restrict__ slice_width, const int64_t * __restrict__ slice_ptr, int C,
                                       int64_t nslices, int G, const int64_t * __restrict__ item_off,
                                       const int64_t * __restrict__ slot_off, const int64_t * __restrict__ cut_off,
-                                      int4 * __restrict__ items, int4 * __restrict__ cuts)
+                                      int4 * __restrict__ items, int4 * __restrict__ cuts, int32_t * __restrict__ slot_cut)
 {
 	const int64_t s = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
 	if (s >= nslices)
@@ -539,6 +539,8 @@ __global__ void sell_item_fill_kernel(const int32_t * __restrict__ slice_width, 
 			kc = kc < 0 ? 0 : (kc > SELL_KCH ? SELL_KCH : kc);
 			items[io++] = make_int4((int) (uint32_t) (off & 0xffffffffLL), (int) ((off >> 32) & 0xffff) | (kc << 16),
 			                        (n > 1) ? (int) (so + (int64_t) g * n + j) : -1, (int) (s * C + 32 * g));
+			if (n > 1)
+				slot_cut[so + (int64_t) g * n + j] = (int32_t) (co + g);
 		}
 		if (n > 1)
 			cuts[co + g] = make_int4((int) s, (int) (so + (int64_t) g * n), n, g);
@@ -577,12 +579,15 @@ static int sell_plan_items(b200spmv * h)
 	CU(cudaMalloc(&h->d_sell_items, (size_t) tot[0] * sizeof(int4)));
 	CU(cudaMalloc(&h->d_sell_cuts, (size_t) (tot[2] > 0 ? tot[2] : 1) * sizeof(int4)));
 	CU(cudaMalloc(&h->d_sell_partial, (size_t) (tot[1] > 0 ? tot[1] : 1) * 32 * sizeof(double)));
+	CU(cudaMalloc(&h->d_sell_slot_cut, (size_t) (tot[1] > 0 ? tot[1] : 1) * sizeof(int32_t)));
+	CU(cudaMalloc(&h->d_sell_cut_cnt, (size_t) (tot[2] > 0 ? tot[2] : 1) * sizeof(unsigned int)));
+	CU(cudaMemsetAsync(h->d_sell_cut_cnt, 0, (size_t) (tot[2] > 0 ? tot[2] : 1) * sizeof(unsigned int), st));
 	if (h->padded >= (1LL << 47)) {
 		cudaFree(d_off);
 		B200_FAIL("SELL-C-sigma padded size does not fit the item record");
 	}
 	sell_item_fill_kernel<<<(unsigned) ((ns + 255) / 256), 256, 0, st>>>(h->d_slice_width, h->d_slice_ptr, h->C, ns, G, d_item, d_slot, d_cut,
-	                                                                    reinterpret_cast<int4 *>(h->d_sell_items), reinterpret_cast<int4 *>(h->d_sell_cuts));
+	                                                                    reinterpret_cast<int4 *>(h->d_sell_items), reinterpret_cast<int4 *>(h->d_sell_cuts), h->d_sell_slot_cut);
 	CU_LAUNCH();
 	CU(cudaStreamSynchronize(st));
 	CU(cudaFree(d_off));

@@ -10,8 +10,8 @@
 // steps in flight per lane before the first x gather; no reduction is needed because a lane is a
 // row.  Cutting slices along k bounds the sequential depth of a lane: a slice holding one of the
 // generator's giant skew rows (width 500 100 at config 4) becomes thousands of items instead of
-// one 500 100-step loop.  Slices cut into several items write per-item partials that
-// sell_fixup_kernel adds in chunk order (deterministic, no atomics).  Padding entries are
+// one 500 100-step loop.  Slices cut into several items write per-item partials that the last-arriving
+// warp of the cut adds in chunk order (deterministic, no atomics on y; no second launch).  Padding entries are
 // (col 0, val 0.0) exactly as the reference writes them and are multiplied like real ones.
 #include "common.cuh"
 
@@ -19,7 +19,8 @@ template <bool HINT, int U, int MINB>
 __global__ void __launch_bounds__(SELL_THREADS, MINB)
 sell_kernel(const int4 * __restrict__ items, int64_t nitems, const int32_t * __restrict__ row_order,
             const int32_t * __restrict__ scol, const double * __restrict__ sval, const double * __restrict__ x,
-            double * __restrict__ partial, int64_t m, int C, YOut out)
+            double * __restrict__ partial, int64_t m, int C, YOut out, const int32_t * __restrict__ slot_cut,
+            const int4 * __restrict__ cuts, unsigned int * __restrict__ cut_cnt, int64_t norm_cut_base)
 {
 	__shared__ double s_red[SELL_THREADS / 32];
 	const uint64_t pol = make_policy_evict_last();
@@ -68,7 +69,37 @@ sell_kernel(const int4 * __restrict__ items, int64_t nitems, const int32_t * __r
 					acc = fma(v[u], ld_x<HINT>(x + c[u], pol), acc);
 		}
 		if (item.z >= 0) {
+			// a cut slice: publish this item's partial; the warp that arrives LAST at the cut adds all of them in chunk order
+			// (a fixed order: y does not depend on which warp that was -- deterministic, no atomics on y) and finishes the rows.
+			// Round 1 did this in a second launch (sell_fixup_kernel, ~5 us + a launch gap per product).
 			partial[(int64_t) item.z * 32 + lane] = acc;
+			const int q = slot_cut[item.z];
+			const int4 cut = cuts[q];                    // x: slice, y: first partial slot, z: number of items, w: lane group
+			__threadfence();
+			unsigned int old = 0;
+			if (lane == 0)
+				old = atomicAdd(&cut_cnt[q], 1u);
+			old = __shfl_sync(0xffffffffu, old, 0);
+			if (old + 1u == (unsigned int) cut.z) {
+				__threadfence();
+				double a = 0.0;
+				for (int j = 0; j < cut.z; j++)
+					a += __ldcg(partial + ((int64_t) cut.y + j) * 32 + lane);
+				const int64_t rr = (int64_t) cut.x * C + cut.w * 32 + lane;
+				double sq = 0.0;
+				if (rr < m && lane < C) {
+					const double scale = out.scale ? *out.scale : 1.0;
+					a = y_finish(out, row_order[rr], a, scale);
+					sq = a * a;
+				}
+				if (out.norm_partial) {
+					sq = warp_sum(sq);
+					if (lane == 0)
+						out.norm_partial[norm_cut_base + q] = sq;      // one slot per cut: the norm's grouping is fixed too
+				}
+				if (lane == 0)
+					cut_cnt[q] = 0u;
+			}
 		} else if (r < m && lane < C) {
 			const double scale = out.scale ? *out.scale : 1.0;
 			acc = y_finish(out, dst_row, acc, scale);
@@ -86,42 +117,6 @@ sell_kernel(const int4 * __restrict__ items, int64_t nitems, const int32_t * __r
 			for (int wv = 0; wv < SELL_THREADS / 32; wv++)
 				tot += s_red[wv];
 			out.norm_partial[blockIdx.x] = tot;
-		}
-	}
-}
-
-// One warp per cut (slice, lane group): y = sum of its items' partials in chunk order.
-__global__ void __launch_bounds__(SELL_THREADS)
-sell_fixup_kernel(const int4 * __restrict__ cuts, int64_t ncuts, const int32_t * __restrict__ row_order,
-                  const double * __restrict__ partial, int64_t m, int C, int64_t norm_base, YOut out)
-{
-	__shared__ double s_red[SELL_THREADS / 32];
-	const int lane = threadIdx.x & 31;
-	const int64_t q = (int64_t) blockIdx.x * (SELL_THREADS / 32) + (threadIdx.x >> 5);
-	double nrm = 0.0;
-	if (q < ncuts) {
-		const int4 cut = cuts[q];                    // x: slice, y: first partial slot, z: number of items, w: lane group
-		double acc = 0.0;
-		for (int j = 0; j < cut.z; j++)
-			acc += partial[((int64_t) cut.y + j) * 32 + lane];
-		const int64_t r = (int64_t) cut.x * C + cut.w * 32 + lane;
-		if (r < m && lane < C) {
-			const double scale = out.scale ? *out.scale : 1.0;
-			acc = y_finish(out, row_order[r], acc, scale);
-			nrm = acc * acc;
-		}
-	}
-	if (out.norm_partial) {
-		nrm = warp_sum(nrm);
-		if (lane == 0)
-			s_red[threadIdx.x >> 5] = nrm;
-		__syncthreads();
-		if (threadIdx.x == 0) {
-			double tot = 0.0;
-			#pragma unroll
-			for (int wv = 0; wv < SELL_THREADS / 32; wv++)
-				tot += s_red[wv];
-			out.norm_partial[norm_base + blockIdx.x] = tot;
 		}
 	}
 }
@@ -152,12 +147,13 @@ int launch_sell_spmv(b200spmv * h, const double * dx, double * dy, cudaStream_t 
 	const int64_t first = h->range_count >= 0 ? h->range_first : 0;
 	const int64_t nit = h->range_count >= 0 ? h->range_count : h->sell_nitems;
 	const int64_t ctas = (nit + WPC - 1) / WPC;
-	const int64_t fix_ctas = (h->sell_ncuts + WPC - 1) / WPC;
+	const int64_t ncuts = h->sell_ncuts;
 	if (ctas > 0) {
 		const int4 * items = reinterpret_cast<const int4 *>(h->d_sell_items) + first;
 		#define SELL_LAUNCH(HINT, U, MINB)                                                                                          \
 			sell_kernel<HINT, U, MINB><<<(unsigned) ctas, SELL_THREADS, 0, st>>>(items, nit, h->d_row_order, h->d_scol, \
-			                                                                     h->d_sval, dx, h->d_sell_partial, h->m, h->C, out)
+			                                                                     h->d_sval, dx, h->d_sell_partial, h->m, h->C, out, h->d_sell_slot_cut, \
+			                                                                     reinterpret_cast<const int4 *>(h->d_sell_cuts), h->d_sell_cut_cnt, ctas)
 		const bool hint = (h->x_hint == 0);
 		// shape 0: short slices are latency-bound (more resident warps win), wide ones want registers for loads in flight
 		// (measured, profiles/r01f_sweep.txt: 8 x 48 wins below ~32 columns per slice, 8 x 32 above)
@@ -173,12 +169,7 @@ int launch_sell_spmv(b200spmv * h, const double * dx, double * dy, cudaStream_t 
 		#undef SELL_LAUNCH
 		CU_LAUNCH();
 	}
-	if (fix_ctas > 0) {
-		sell_fixup_kernel<<<(unsigned) fix_ctas, SELL_THREADS, 0, st>>>(reinterpret_cast<const int4 *>(h->d_sell_cuts), h->sell_ncuts, h->d_row_order,
-		                                                               h->d_sell_partial, h->m, h->C, ctas, out);
-		CU_LAUNCH();
-	}
 	if (l && l->norm2)
-		return launch_norm_reduce(h, ctas + fix_ctas, l->norm2, st);
+		return launch_norm_reduce(h, ctas + ncuts, l->norm2, st);
 	return 0;
 }
