@@ -377,8 +377,9 @@ static int plan_chunks(b200spmv * h)
 	const int NCH = 4;
 	if (h->m < 262144 || h->npanels > 1)
 		return 0;
+	h->n_chunk_fix = 0;
 	if (h->format == B200SPMV_CSR_ADAPTIVE) {
-		if (h->nsplit > 0 || h->compressed || h->ntiles < 64 * NCH)
+		if (h->compressed || h->ntiles < 64 * NCH || h->nsplit > 65536)
 			return 0;
 		for (int c = 0; c <= NCH; c++) {
 			h->chunk_unit[c] = h->ntiles * c / NCH;
@@ -388,14 +389,33 @@ static int plan_chunks(b200spmv * h)
 		}
 		h->chunk_row[0] = 0;
 		h->chunk_row[NCH] = h->m;
+		if (h->nsplit > 0) {
+			// a split row is finished by the LAST of its tiles (csr_fold_split_rows); when those tiles straddle a range boundary
+			// the row is final only after a later range's launch: at most one such row per boundary, copied again at the end
+			int4 * info = (int4 *) malloc((size_t) h->nsplit * sizeof(int4));
+			if (!info)
+				B200_FAIL("out of host memory");
+			if (cudaMemcpy(info, h->d_split_info, (size_t) h->nsplit * sizeof(int4), cudaMemcpyDeviceToHost) != cudaSuccess) {
+				free(info);
+				B200_FAIL("plan_chunks: copy of the split-row table failed");
+			}
+			for (int64_t s = 0; s < h->nsplit; s++) {
+				const int64_t k = info[s].y, last = k + info[s].z - 1;
+				for (int c = 1; c < NCH; c++)
+					if (k < h->chunk_unit[c] && last >= h->chunk_unit[c] && h->n_chunk_fix < 4) {
+						h->chunk_fix_row[h->n_chunk_fix++] = info[s].x;
+						break;
+					}
+			}
+			free(info);
+		}
 	} else {
 		const int64_t spw = h->sigma / h->C, nwin = (h->m + h->sigma - 1) / h->sigma;
-		const int G = h->C >= 32 ? h->C / 32 : 1;
-		if (h->sell_ncuts > 0 || nwin < 2 * NCH || h->sell_nitems != h->nslices * G)
+		if (nwin < 2 * NCH)
 			return 0;
 		for (int c = 0; c <= NCH; c++) {
 			const int64_t s = (nwin * c / NCH) * spw;
-			h->chunk_unit[c] = s * G;
+			h->chunk_unit[c] = h->sell_chunk_item[c];
 			h->chunk_row[c] = s * h->C < h->m ? s * h->C : h->m;
 		}
 		h->chunk_unit[NCH] = h->sell_nitems;

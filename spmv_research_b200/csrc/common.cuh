@@ -212,6 +212,9 @@ struct b200spmv {
 	// when the range's kernel ends, so the D2H copy of a range overlaps the kernel of the next one.
 	int nchunks;                  // 0 / 1 = one launch
 	int64_t chunk_unit[5], chunk_row[5];
+	int64_t sell_chunk_item[5];   // SELL: first item of the slice at each chunk boundary (set by sell_plan_items; slices with cuts have several items)
+	int n_chunk_fix;              // CSR: split rows whose tiles straddle a chunk boundary (<= 3): final only after a LATER range,
+	int64_t chunk_fix_row[4];     //      so their y entry is copied once more after the last range
 	int64_t range_first, range_count;      // range_count < 0: whole matrix (set only around the chunked launches)
 	cudaStream_t copy_stream;
 	cudaEvent_t chunk_ev[4];

@@ -572,6 +572,19 @@ static int sell_plan_items(b200spmv * h)
 	h->sell_nitems = tot[0];
 	h->sell_nslots = tot[1];
 	h->sell_ncuts = tot[2];
+	{
+		// chunk boundaries of the host-vector path (capi.cu plan_chunks): 4 ranges on sort-window boundaries; a slice's items are
+		// contiguous, so a range holds whole slices and every cut is finished inside its own range's launch
+		const int64_t spw = h->sigma / h->C, nwin = (h->m + h->sigma - 1) / h->sigma;
+		for (int c = 0; c <= 4; c++) {
+			int64_t s = (nwin * c / 4) * spw;
+			s = s > ns ? ns : s;
+			if (c == 4)
+				s = ns;
+			CU(cudaMemcpyAsync(&h->sell_chunk_item[c], d_item + s, 8, cudaMemcpyDeviceToHost, st));
+		}
+		CU(cudaStreamSynchronize(st));
+	}
 	if (tot[1] >= 0x7fffffffLL / 32 || tot[0] >= 0x7fffffffLL) {
 		cudaFree(d_off);
 		B200_FAIL("SELL-C-sigma plan too large (%lld items)", (long long) tot[0]);

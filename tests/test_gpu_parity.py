@@ -436,6 +436,36 @@ def test_column_panels(S, oracle, golden_matrices):
     MF.close()
 
 
+def test_host_path_ranges_with_split_rows_and_cut_slices(S, oracle):
+    """The host-vector path launches matrices of >= 262 144 rows as 4 unit ranges so that the D2H copy of a range overlaps the
+    next range's kernel.  Since round 2 that also holds with split rows (finished by the last of their tiles -- possibly in a
+    LATER range: their y entry is copied once more at the end) and with cut SELL slices (a range holds whole slices).  Giant
+    rows are planted exactly where the range boundaries fall in nnz space; rows of 300 make every SELL slice a cut one."""
+    m, n = 300000, 300000
+    rng = np.random.default_rng(21)
+    for base_len, giants in ((10, {74000: 60000, 150100: 9000, 226000: 2500}), (300, {75000: 200000, 149990: 5000})):
+        lens = np.full(m, base_len, np.int64)
+        for r, l in giants.items():
+            lens[r] = l
+        rp = np.zeros(m + 1, np.int32)
+        np.cumsum(lens, out=rp[1:])
+        nnz = int(rp[-1])
+        col = ((np.arange(nnz, dtype=np.int64) * 2654435761) % n).astype(np.int32)
+        val = rng.uniform(0.0, 1.0, nnz)
+        x = M.rand_x(n, 6)
+        for fmt in (S.CSR_ADAPTIVE, S.SELL_C_SIGMA):
+            if fmt == S.SELL_C_SIGMA and base_len == 10:
+                continue                              # a 60 000-wide slice pads 32 x: nothing to learn
+            MF, y = _spmv(S, dict(format=fmt), rp, col, val, n, x)
+            _check(oracle, rp, col, val, x, y, "ranges fmt %d base %d" % (fmt, base_len))
+            if fmt == S.CSR_ADAPTIVE:
+                assert MF.handle.stats()["nsplit"] >= len(giants)
+            y2 = np.full(m + 64, 1.0)
+            MF.spmv(x, y2)                            # counters reset by the finisher: a second product gives the same bits
+            assert np.array_equal(y2[:m], y)
+            MF.close()
+
+
 def test_host_flags_reference_convention(S, oracle, golden_matrices):
     """cache_x=True follows the reference GPU plugins: x is uploaded on the first call only
     (GPU_clean/cuda_csr.cu:353-382), so a changed x at the same address is NOT seen."""
