@@ -379,7 +379,7 @@ static int plan_chunks(b200spmv * h)
 		return 0;
 	h->n_chunk_fix = 0;
 	if (h->format == B200SPMV_CSR_ADAPTIVE) {
-		if (h->compressed || h->ntiles < 64 * NCH || h->nsplit > 65536)
+		if (h->compressed || h->ntiles < 64 * NCH || (h->nsplit > 0 && !h->fold_splits))
 			return 0;
 		for (int c = 0; c <= NCH; c++) {
 			h->chunk_unit[c] = h->ntiles * c / NCH;
@@ -647,7 +647,7 @@ extern "C" int32_t b200spmv_launches_per_spmv(const b200spmv_t * h)
 		return n;
 	}
 	if (h->format == B200SPMV_CSR_ADAPTIVE)
-		return 1 + ((h->compressed && h->n_empty > 0) ? 1 : 0);      // split rows are finished inside the tile kernel
+		return 1 + ((h->nsplit > 0 && !h->fold_splits) ? 1 : 0) + ((h->compressed && h->n_empty > 0) ? 1 : 0);
 	return 1;                                   // cut slices are finished inside the kernel (last-arriving warp)
 }
 
@@ -787,6 +787,9 @@ extern "C" int b200spmv_spmv_host_ex(b200spmv_t * h, const double * x, double * 
 		h->range_count = -1;
 		if (rc)
 			return rc;
+		// split rows finished by a later range than the one that owns them (plan_chunks): the copy stream is past the last range
+		for (int f = 0; f < h->n_chunk_fix; f++)
+			CU(cudaMemcpyAsync(y + h->chunk_fix_row[f], h->d_y + h->chunk_fix_row[f], sizeof(double), cudaMemcpyDeviceToHost, h->copy_stream));
 		CU(cudaStreamSynchronize(h->stream));
 		CU(cudaStreamSynchronize(h->copy_stream));
 		return 0;

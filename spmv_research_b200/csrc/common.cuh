@@ -180,6 +180,7 @@ struct b200spmv {
 	int32_t * d_tile_split;   // int2[ntiles]: {split row owned, split row entering} or -1 (csr_fold_split_rows); null when nsplit = 0
 	int32_t * d_split_info;   // int4[nsplit]: {row, owner tile, contributing tiles, 0}
 	unsigned int * d_split_cnt;   // [nsplit] arrival counters, zero between products
+	int fold_splits;              // 1: split rows are finished inside the tile kernel (few of them); 0: by csr_fixup_kernel
 	double * d_tile_head;     // [ntiles] partial of a split row entering the tile
 	double * d_tile_tail;     // [ntiles] partial of a split row leaving the tile
 	uint16_t * d_perm;        // CSR_EXP_PERM builds only (csr_perm.h): thread slot -> tile-local row; null otherwise

@@ -316,12 +316,18 @@ static int plan_tiles_on(b200spmv * h)
 	CU(cudaMemcpyAsync(&last_pos, d_flag + h->ntiles - 1, sizeof(int64_t), cudaMemcpyDeviceToHost, h->stream));
 	CU(cudaStreamSynchronize(h->stream));
 	h->nsplit = last_flag + last_pos;
+	h->fold_splits = 0;
 	if (h->nsplit > 0) {
 		CU(cudaMalloc(&h->d_split_row, h->nsplit * sizeof(int32_t)));
 		CU(cudaMalloc(&h->d_split_tile, h->nsplit * sizeof(int32_t)));
 		split_compact_kernel<<<(unsigned) ((h->ntiles + 255) / 256), 256, 0, h->stream>>>(
 			reinterpret_cast<const int2 *>(h->d_tile_row), d_flag, h->ntiles, h->nsplit, h->d_split_row, h->d_split_tile);
 		CU_LAUNCH();
+		// Few split rows (the generator's skew rows): finished inside the tile kernel by the last-arriving CTA.  Many (long-row
+		// matrices: at 500 per row almost every tile is entered and left by one) keep the separate fix-up launch -- measured:
+		// the fences, the counter and the dependent look-ups on EVERY tile cost the 500-per-row sample matrix 19 % (0.165 ->
+		// 0.197 ms, profiles/r02f_bench_n1.json), a 4.5 us launch costs it 3 %.
+		h->fold_splits = (h->nsplit * 16 <= h->ntiles) ? 1 : 0;
 		CU(cudaMalloc(&h->d_tile_split, h->ntiles * sizeof(int2)));
 		CU(cudaMalloc(&h->d_split_info, h->nsplit * sizeof(int4)));
 		CU(cudaMalloc(&h->d_split_cnt, h->nsplit * sizeof(unsigned int)));

@@ -403,7 +403,7 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 		if (tid == 0)
 			tile_head[tile] = part;
 	}
-	if (tail_split || head_split)
+	if ((tail_split || head_split) && sf.tile_split)
 		csr_fold_split_rows<MODE>(tile, tail_split, head_split, sf, tile_head, tile_tail, rowmap, out, scale, s_red);
 
 	// 7. optional sum of squares of the rows written here (power iteration norm, no atomics)
@@ -421,6 +421,33 @@ csr_tile_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict
 				tot += s_red[w];
 			out.norm_partial[tile] = tot;
 		}
+	}
+}
+
+// Handles with MANY split rows (fold_splits = 0): one warp per split row after the tile kernel,
+// y[row] = tail[owner] + head[owner+1] + ... + head[last], fixed order.
+__global__ void csr_fixup_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict__ split_row,
+                                 const int32_t * __restrict__ split_tile, const double * __restrict__ tile_head,
+                                 const double * __restrict__ tile_tail, int64_t nsplit, int tile_nnz, int64_t ntiles,
+                                 const int32_t * __restrict__ rowmap, YOut out)
+{
+	const int64_t s = blockIdx.x;
+	if (s >= nsplit)
+		return;
+	const int lane = threadIdx.x;
+	const int row = split_row[s];
+	const int64_t k = split_tile[s];
+	const int64_t e = row_ptr[row + 1];
+	const int64_t last = (e - 1) / tile_nnz;
+	double acc = (lane == 0) ? tile_tail[k] : 0.0;
+	for (int64_t t = k + 1 + lane; t <= last; t += 32)
+		acc += tile_head[t];
+	acc = warp_sum(acc);
+	if (lane == 0) {
+		const double scale = out.scale ? *out.scale : 1.0;
+		acc = y_finish(out, rowmap ? rowmap[row] : row, acc, scale);
+		if (out.norm_partial)
+			out.norm_partial[ntiles + s] = acc * acc;
 	}
 }
 
@@ -492,7 +519,7 @@ static int launch_tiles_impl(b200spmv * h, const double * dx, cudaStream_t st, c
 	if (count <= 0)
 		return 0;
 	SplitFold sf;
-	sf.tile_split = reinterpret_cast<const int2 *>(h->d_tile_split);
+	sf.tile_split = h->fold_splits ? reinterpret_cast<const int2 *>(h->d_tile_split) : nullptr;
 	sf.info = reinterpret_cast<const int4 *>(h->d_split_info);
 	sf.cnt = h->d_split_cnt;
 	sf.ntiles = h->ntiles;
@@ -567,6 +594,12 @@ int launch_csr_spmv(b200spmv * h, const double * dx, double * dy, cudaStream_t s
 	}
 	if (csr_launch_tiles(h, dx, st, out))
 		return 1;
+	if (h->nsplit > 0 && !h->fold_splits) {
+		csr_fixup_kernel<<<(unsigned) h->nsplit, 32, 0, st>>>(h->d_rp_plan, h->d_split_row, h->d_split_tile, h->d_tile_head,
+		                                                     h->d_tile_tail, h->nsplit, h->tile_nnz, h->ntiles,
+		                                                     h->compressed ? h->d_rows_nz : nullptr, out);
+		CU_LAUNCH();
+	}
 	if (l && l->norm2)
 		return launch_norm_reduce(h, h->ntiles + h->nsplit + zero_ctas, l->norm2, st);
 	return 0;
