@@ -76,6 +76,7 @@ sell_kernel(const int4 * __restrict__ items, int64_t nitems, const int32_t * __r
 			const int q = slot_cut[item.z];
 			const int4 cut = cuts[q];                    // x: slice, y: first partial slot, z: number of items, w: lane group
 			__threadfence();
+			__syncwarp();                                // every lane's partial is fenced before lane 0 counts the item in
 			unsigned int old = 0;
 			if (lane == 0)
 				old = atomicAdd(&cut_cnt[q], 1u);
