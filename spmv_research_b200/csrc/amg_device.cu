@@ -77,6 +77,7 @@ struct scratch {
 extern "C" int b200spmv_amg_fill_device(const b200amg_params * p, const int32_t * d_row_ptr, double bw_corrected, int64_t i_s, int64_t i_e,
                                         int32_t * d_col_ind, double * d_values, void * stream)
 {
+	B200Range nvtx_range_("b200spmv_amg_fill_device");
 	if (!p || !d_row_ptr)
 		B200_FAIL("amg_fill_device: null argument");
 	const int64_t m = p->nr_rows;

@@ -303,6 +303,7 @@ static int auto_select(b200spmv * h, const b200spmv_opts & o)
 
 static int auto_select_impl(b200spmv * h, const b200spmv_opts & o, cudaEvent_t e0, cudaEvent_t e1)
 {
+	B200Range nvtx_range_("b200spmv AUTO trial");
 	CU(cudaMalloc(&h->d_x, (h->n > 0 ? h->n : 1) * sizeof(double)));
 	CU(cudaMalloc(&h->d_y, (h->m > 0 ? h->m : 1) * sizeof(double)));
 	CU(cudaMemsetAsync(h->d_x, 0, (h->n > 0 ? h->n : 1) * sizeof(double), h->stream));
@@ -481,6 +482,7 @@ static void free_handle(b200spmv * h)
 static int create_common(b200spmv ** out, const int32_t * row_ptr, const int32_t * col_ind, const double * values,
                          int64_t m, int64_t n, int64_t nnz, const b200spmv_opts * opts_in, cudaMemcpyKind kind)
 {
+	B200Range nvtx_range_("b200spmv_create");
 	if (!out)
 		B200_FAIL("out is NULL");
 	*out = nullptr;
@@ -719,6 +721,7 @@ static void pin_once(b200spmv * h, const void * p, size_t bytes)
 
 extern "C" int b200spmv_spmv_host_ex(b200spmv_t * h, const double * x, double * y, int32_t flags)
 {
+	B200Range nvtx_range_("b200spmv_spmv_host");
 	if (!h || !x || !y)
 		B200_FAIL("NULL argument");
 	CU(cudaSetDevice(h->device));

@@ -4,6 +4,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <string.h>
+#include <nvtx3/nvToolsExt.h>      // header-only; a no-op unless a profiler (nsys / ncu --nvtx) is attached
 #include "../../include/b200spmv.h"
 
 #if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
@@ -26,6 +27,13 @@ extern thread_local char g_b200_err[512];
 	} while (0)
 
 #define CU_LAUNCH() CU(cudaPeekAtLastError())
+
+// NVTX range over a C-ABI entry point / a create-time phase (the reference's SDV / TIME_IT region markers,
+// bench_spmv.cpp:321-324, cuda_csr.cu:138-204, become profiler ranges).  Not placed on the device-resident product path.
+struct B200Range {
+	explicit B200Range(const char * name) { nvtxRangePushA(name); }
+	~B200Range() { nvtxRangePop(); }
+};
 
 // ---------------------------------------------------------------------------------------------
 // Tunables of the nnz-tiled CSR kernel

@@ -260,6 +260,7 @@ static int plan_tiles_on(b200spmv * h);
 // measured 0.70 ms -> see profiles/, the mawi twin of config 3).
 int csr_plan_tiles(b200spmv * h)
 {
+	B200Range nvtx_range_("b200spmv csr_plan_tiles");
 	h->d_rp_plan = h->d_row_ptr;
 	h->m_plan = h->m;
 	h->compressed = 0;
@@ -615,6 +616,7 @@ static int sell_plan_items(b200spmv * h)
 
 int sell_convert(b200spmv * h)
 {
+	B200Range nvtx_range_("b200spmv sell_convert");
 	const int64_t m = h->m;
 	const int C = h->C;
 	const int64_t sigma = h->sigma;

@@ -167,6 +167,7 @@ int panels_auto_count(const b200spmv * h, int requested)
 // Splits h's CSR arrays (device) into P column panels and creates one sub-handle per panel.
 int panels_split(b200spmv * h, int P, const b200spmv_opts * sub_opts)
 {
+	B200Range nvtx_range_("b200spmv panels_split");
 	const int64_t m = h->m;
 	PanelBounds b;
 	const int64_t lo = h->col_lo, span = h->col_hi - h->col_lo;

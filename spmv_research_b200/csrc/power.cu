@@ -656,6 +656,7 @@ static int power_setup(b200spmv_power * pw, const b200spmv_power_opts * o)
 extern "C" int b200spmv_power_create(b200spmv_power_t ** out, b200spmv_t * shard, b200spmv_comm_t * comm, const int64_t * bounds, int64_t n,
                                      const b200spmv_power_opts * opts)
 {
+	B200Range nvtx_range_("b200spmv_power_create");
 	if (!out || !shard || !bounds)
 		B200_FAIL("NULL argument");
 	*out = nullptr;
@@ -754,6 +755,7 @@ static int capture_pair(b200spmv_power * pw)
 
 extern "C" int b200spmv_power_iterate(b200spmv_power_t * pw, int32_t iters, double * eigenvalue_out, float * ms_out)
 {
+	B200Range nvtx_range_("b200spmv_power_iterate");
 	if (!pw || iters < 0)
 		B200_FAIL("bad arguments");
 	CU(cudaSetDevice(pw->device));
