@@ -150,6 +150,17 @@ int b200spmv_export(const b200spmv_t * h, int32_t what, void * dst_host, int64_t
 int b200spmv_partition_device(const int32_t * d_sums, int64_t N, int64_t total, int32_t W, int64_t * bounds_out_host);
 int b200spmv_partition(const int32_t * sums_host, int64_t N, int64_t total, int32_t W, int64_t * bounds_out_host);
 
+/* The same partition as b200spmv_partition_device for callers that cannot call cudaMalloc (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid it).  No counterpart in the reference.
+ * Allocates nothing (no cudaMalloc / cudaFree / allocating library routine): the 2 W bounds are staged in a
+ * file-scope static device array of B200SPMV_NOALLOC_MAX_WORKERS workers (64 KB, held by every GPU that loads the library
+ * until exit); W beyond that is refused with an error.  d_sums: DEVICE pointer; bounds_out_host: HOST, 2 W entries; the
+ * kernel and the copy run on `stream` (NULL = legacy default stream), which is synchronised before returning.  Every call
+ * on a device shares the one array (it keeps the last call's contents; every entry that is read back is overwritten first):
+ * calls that overlap on the GPU -- other streams, other threads -- race; calls on one stream are safe. */
+#define B200SPMV_NOALLOC_MAX_WORKERS 4096
+int b200spmv_partition_device_noalloc(const int32_t * d_sums, int64_t N, int64_t total, int32_t W, int64_t * bounds_out_host, void * stream);
+
 /* Merge-path coordinates on the GPU for W workers: coords_out[2t], [2t+1] = (row, nz) where worker t
  * starts, t = 0..W (W+1 pairs), items per worker = ceil((m+nnz)/W) as K/merge.cpp:277-283. */
 int b200spmv_merge_coords(const b200spmv_t * h, int32_t W, int64_t * coords_out_host);

@@ -79,6 +79,7 @@ def lib():
         "b200spmv_export": (C.c_int, [vp, i32, vp, i64, C.POINTER(i64)]),
         "b200spmv_partition_device": (C.c_int, [vp, i64, i64, i32, vp]),
         "b200spmv_partition": (C.c_int, [vp, i64, i64, i32, vp]),
+        "b200spmv_partition_device_noalloc": (C.c_int, [vp, i64, i64, i32, vp, vp]),
         "b200spmv_merge_coords": (C.c_int, [vp, i32, vp]),
         "b200spmv_device_count": (C.c_int, [C.POINTER(i32)]),
         "b200spmv_set_device": (C.c_int, [i32]),
@@ -258,6 +259,17 @@ def partition(sums, N, total, W, device=False):
     out = np.zeros((W, 2), np.int64)
     fn = lib().b200spmv_partition_device if device else lib().b200spmv_partition
     check(fn(_ptr(sums), int(N), int(total), int(W), out.ctypes.data))
+    return out
+
+
+NOALLOC_MAX_WORKERS = 4096
+
+
+def partition_noalloc(d_sums, N, total, W, stream=None):
+    """b200spmv_partition_device_noalloc: the reference partitioner on DEVICE prefix sums with its scratch in a static device
+    array (no cudaMalloc inside the call; W <= NOALLOC_MAX_WORKERS): int64[W, 2] of [i_s, i_e)."""
+    out = np.zeros((max(int(W), 1), 2), np.int64)
+    check(lib().b200spmv_partition_device_noalloc(_ptr(d_sums), int(N), int(total), int(W), out.ctypes.data, stream))
     return out
 
 

@@ -106,3 +106,61 @@ int b200spmv_merge_coords(const b200spmv_t * h, int32_t W, int64_t * coords_out_
 	CU(cudaFree(d_c));
 	return 0;
 }
+
+// ---------------------------------------------------------------------------------------------
+// b200spmv_partition_device_noalloc -- the same partition for callers that cannot call cudaMalloc (code under CUDA graph
+// capture, tight serving loops, harnesses that forbid it).  No counterpart in the reference.
+// The 2 W row bounds that b200spmv_partition_device puts into a cudaMalloc'd scratch buffer go into a
+// file-scope device array instead: B200SPMV_NOALLOC_MAX_WORKERS (4096) workers -> 64 KB that every GPU which loads the library
+// holds until exit.  Nothing here allocates: no cudaMalloc / cudaFree / cudaMallocHost, no allocating library routine.
+//
+// The array is ONE per device and shared by every call: it keeps the last call's contents (nothing has to start at zero -- the
+// kernel overwrites all 2 W entries the copy reads, and only those are copied), and two calls that overlap on the GPU
+// (different streams, or threads racing on one stream's tail) race on it.  Calls on one stream are ordered and safe.
+//
+// g_partition_scratch is a HOST-SIDE STAND-IN in host code, not a device address: handing it to a kernel faults (or silently
+// uses the wrong memory where the GPU can reach host memory).  The device address comes from cudaGetSymbolAddress, once per
+// device, with that device current.
+// ---------------------------------------------------------------------------------------------
+static __device__ __align__(256) int64_t g_partition_scratch[2 * B200SPMV_NOALLOC_MAX_WORKERS];
+
+static int64_t * g_partition_scratch_addr[64] = { nullptr };      // per device ordinal; filled at first use on that device
+
+static int partition_scratch_address(int64_t ** out)
+{
+	int dev = -1;
+	CU(cudaGetDevice(&dev));
+	if (dev < 0 || dev >= 64)
+		B200_FAIL("device ordinal %d outside [0, 64)", dev);
+	if (!g_partition_scratch_addr[dev]) {
+		void * p = nullptr;
+		const cudaError_t e = cudaGetSymbolAddress(&p, g_partition_scratch);      // the current device's copy of the array
+		if (e != cudaSuccess || !p)
+			B200_FAIL("cudaGetSymbolAddress(g_partition_scratch) on device %d -> %s", dev, cudaGetErrorString(e));
+		g_partition_scratch_addr[dev] = (int64_t *) p;
+	}
+	*out = g_partition_scratch_addr[dev];
+	return 0;
+}
+
+int b200spmv_partition_device_noalloc(const int32_t * d_sums, int64_t N, int64_t total, int32_t W, int64_t * bounds_out_host, void * stream)
+{
+	if (!d_sums || !bounds_out_host)
+		B200_FAIL("NULL argument");
+	if (N < 1)
+		B200_FAIL("Empty Sums array.");          // the reference's own error text (parallel_util.h:166)
+	if (W < 1)
+		B200_FAIL("num_workers must be >= 1");
+	if (W > B200SPMV_NOALLOC_MAX_WORKERS)
+		B200_FAIL("b200spmv_partition_device_noalloc: %d workers exceed the static scratch (B200SPMV_NOALLOC_MAX_WORKERS = %d); "
+		          "use b200spmv_partition_device", W, B200SPMV_NOALLOC_MAX_WORKERS);
+	int64_t * d_b = nullptr;
+	if (partition_scratch_address(&d_b))
+		return 1;
+	cudaStream_t st = (cudaStream_t) stream;
+	partition_kernel<<<(W + 127) / 128, 128, 0, st>>>(d_sums, N, total, W, d_b);
+	CU_LAUNCH();
+	CU(cudaMemcpyAsync(bounds_out_host, d_b, 2 * (size_t) W * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+	CU(cudaStreamSynchronize(st));
+	return 0;
+}
