@@ -463,44 +463,6 @@ __global__ void sell_order_kernel(const uint64_t * __restrict__ keys, int64_t m,
 	}
 }
 
-// sorted row r, k-th entry -> slice_ptr[r / C] + r % C + k * C   (sellcs_format.c:173-186)
-__global__ void sell_scatter_kernel(const int32_t * __restrict__ row_ptr, const int32_t * __restrict__ col, const double * __restrict__ val,
-                                    const int32_t * __restrict__ row_order, const int64_t * __restrict__ slice_ptr, int64_t m, int C,
-                                    int32_t * __restrict__ scol, double * __restrict__ sval)
-{
-	const int64_t pos = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
-	const bool valid = pos < m;
-	int64_t src = 0, dst = 0;
-	int len = 0;
-	if (valid) {
-		const int orig = row_order[pos];
-		src = row_ptr[orig];
-		len = row_ptr[orig + 1] - row_ptr[orig];
-		dst = slice_ptr[pos / C] + (pos % C);
-	}
-	const bool longrow = len >= 64;
-	if (!longrow) {
-		for (int k = 0; k < len; k++) {
-			scol[dst + (int64_t) k * C] = col[src + k];
-			sval[dst + (int64_t) k * C] = val[src + k];
-		}
-	}
-	// long rows: the whole warp copies them together (coalesced reads of the CSR row)
-	unsigned mask = __ballot_sync(0xffffffffu, longrow);
-	const int lane = threadIdx.x & 31;
-	while (mask) {
-		const int l = __ffs(mask) - 1;
-		mask &= mask - 1;
-		const int64_t s2 = __shfl_sync(0xffffffffu, src, l);
-		const int64_t d2 = __shfl_sync(0xffffffffu, dst, l);
-		const int n2 = __shfl_sync(0xffffffffu, len, l);
-		for (int k = lane; k < n2; k += 32) {
-			scol[d2 + (int64_t) k * C] = col[s2 + k];
-			sval[d2 + (int64_t) k * C] = val[s2 + k];
-		}
-	}
-}
-
 // Work items of the SpMV kernel: every slice is cut along k into chunks of SELL_KCH columns and
 // across lanes into groups of 32; a slice cut into n > 1 chunks also gets one "cut" record per lane
 // group that tells the finishing warp where its n partials lie.
@@ -614,6 +576,87 @@ static int sell_plan_items(b200spmv * h)
 	return 0;
 }
 
+// sorted row r, k-th entry -> slice_ptr[r / C] + r % C + k * C   (sellcs_format.c:173-186)
+//
+// One warp per WORK ITEM of the product plan (slice, group of 32 lanes, chunk of SELL_KCH slice columns; sell_plan_items):
+// the CSR -> column-major move is a transpose, done through a 32 x 32 shared-memory tile so that BOTH sides are coalesced --
+// each row's entries are read as one contiguous run (lane = column), each slice column is written as one contiguous run
+// (lane = row).  Items, not slices, are the unit so that a slice holding one of the generator's giant skew rows (500 100
+// entries) is spread over thousands of warps.  Narrow items (<= 16 columns, the short-row matrices) skip the tile: thread
+// per row, strided reads served by L1, coalesced writes.
+// Round 1's kernel (thread per row; rows >= 64 copied by the warp with stride-C writes, i.e. 32 different lines per store)
+// took 2.4 - 8.6 ms on the 44 M-nnz matrices of the bench sample with rows >= 100 long or a giant row, 14 - 50 x the HBM time
+// of the move (profiles/r02f_launches_bench_summary.txt).  Padding entries stay as the memset left them: (0, 0.0).
+constexpr int SCAT_WARPS = 2;
+
+__global__ void __launch_bounds__(32 * SCAT_WARPS)
+sell_scatter_items_kernel(const int4 * __restrict__ items, int64_t nitems, const int32_t * __restrict__ row_ptr, const int32_t * __restrict__ col,
+                          const double * __restrict__ val, const int32_t * __restrict__ row_order, const int64_t * __restrict__ slice_ptr,
+                          int64_t m, int C, int32_t * __restrict__ scol, double * __restrict__ sval)
+{
+	__shared__ double s_v[SCAT_WARPS][32][33];
+	__shared__ int s_c[SCAT_WARPS][32][33];
+	const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
+	const int64_t it = (int64_t) blockIdx.x * SCAT_WARPS + wp;
+	if (it >= nitems)
+		return;                                      // warp-uniform; only warp-level synchronisation below
+	const int4 item = items[it];
+	const int kc = (int) ((uint32_t) item.y >> 16);
+	const int64_t off = ((int64_t) (item.y & 0xffff) << 32) + (int64_t) (uint32_t) item.x;
+	const int64_t w = item.w;
+	const int64_t s = w / C;
+	const int k0 = (int) ((off - slice_ptr[s] - (w - s * C)) / C);          // first slice column of this item
+	const int64_t r = w + lane;
+	int64_t src = 0;
+	int cnt = 0;                                         // this lane's (= row's) entries inside the item's columns
+	if (lane < C && r < m) {
+		const int orig = row_order[r];
+		src = row_ptr[orig];
+		cnt = row_ptr[orig + 1] - (int) src - k0;
+		cnt = cnt < 0 ? 0 : (cnt > kc ? kc : cnt);
+		src += k0;
+	}
+	const int64_t dst = off + lane;
+	int wmax = cnt;
+	#pragma unroll
+	for (int o = 16; o > 0; o >>= 1) {
+		const int t = __shfl_xor_sync(0xffffffffu, wmax, o);
+		wmax = t > wmax ? t : wmax;
+	}
+	if (wmax == 0)
+		return;
+	if (wmax <= 16) {
+		for (int k = 0; k < cnt; k++) {
+			scol[dst + (int64_t) k * C] = col[src + k];
+			sval[dst + (int64_t) k * C] = val[src + k];
+		}
+		return;
+	}
+	for (int kb = 0; kb < wmax; kb += 32) {
+		unsigned mask = __ballot_sync(0xffffffffu, cnt > kb);
+		while (mask) {
+			const int l = __ffs(mask) - 1;
+			mask &= mask - 1;
+			const int64_t s2 = __shfl_sync(0xffffffffu, src, l);
+			const int n2 = __shfl_sync(0xffffffffu, cnt, l);
+			const int k = kb + lane;
+			if (k < n2) {
+				s_c[wp][l][lane] = col[s2 + k];
+				s_v[wp][l][lane] = val[s2 + k];
+			}
+		}
+		__syncwarp();
+		int lim = wmax - kb;
+		lim = lim > 32 ? 32 : lim;
+		for (int kk = 0; kk < lim; kk++)
+			if (kb + kk < cnt) {
+				scol[dst + (int64_t) (kb + kk) * C] = s_c[wp][lane][kk];
+				sval[dst + (int64_t) (kb + kk) * C] = s_v[wp][lane][kk];
+			}
+		__syncwarp();
+	}
+}
+
 int sell_convert(b200spmv * h)
 {
 	B200Range nvtx_range_("b200spmv sell_convert");
@@ -671,11 +714,15 @@ int sell_convert(b200spmv * h)
 	CU(cudaMalloc(&h->d_sval, alloc * sizeof(double)));
 	CU(cudaMemsetAsync(h->d_scol, 0, alloc * sizeof(int32_t), st));
 	CU(cudaMemsetAsync(h->d_sval, 0, alloc * sizeof(double), st));
-	if (m > 0) {
-		sell_scatter_kernel<<<(unsigned) ((m + 255) / 256), 256, 0, st>>>(h->d_row_ptr, h->d_col, h->d_val, h->d_row_order, h->d_slice_ptr,
-		                                                                  m, C, h->d_scol, h->d_sval);
+	// the product's work items first: they are also the units of the scatter
+	if (sell_plan_items(h))
+		return 1;
+	if (h->sell_nitems > 0) {
+		sell_scatter_items_kernel<<<(unsigned) ((h->sell_nitems + SCAT_WARPS - 1) / SCAT_WARPS), 32 * SCAT_WARPS, 0, st>>>(
+			reinterpret_cast<const int4 *>(h->d_sell_items), h->sell_nitems, h->d_row_ptr, h->d_col, h->d_val, h->d_row_order, h->d_slice_ptr, m, C,
+			h->d_scol, h->d_sval);
 		CU_LAUNCH();
 	}
 	CU(cudaStreamSynchronize(st));
-	return sell_plan_items(h);
+	return 0;
 }
