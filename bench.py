@@ -33,14 +33,17 @@ METRIC = "SpMV GFLOP/s (2*nnz/t), fp64; effective HBM GB/s over compulsory bytes
 NOMINAL_HBM_GBS = 8000.0
 
 
-def ncu_traffic(kernel):
-    """DRAM bytes of one launch of `kernel` from the committed ncu --set full capture (profiles/ncu_traffic.json)."""
+def ncu_traffic(kernel, sub=None):
+    """DRAM bytes of one launch of `kernel` from the committed ncu --set full captures (profiles/ncu_traffic.json); `sub` selects
+    a variant of an entry (the config-5 shard with 1 / 2 column panels)."""
     try:
         t = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
         k = t[kernel]
+        matrix, bc = k.get("matrix", t["matrix"]), k.get("compulsory_bytes", t["compulsory_bytes"])
+        if sub is not None:
+            k = k[sub]
         tot = int(k["dram_bytes_read"]) + int(k["dram_bytes_write"])
-        return tot, "one launch on '%s' (compulsory bytes of that matrix: %d, ratio %.3f); %s" % (
-            t["matrix"], t["compulsory_bytes"], tot / t["compulsory_bytes"], t["source"])
+        return tot, "one product on '%s' (compulsory bytes: %d, ratio %.3f); %s" % (matrix, bc, tot / bc, t["source"])
     except Exception:
         return None, None
 
@@ -928,6 +931,10 @@ def run_power(args):
         bc = H.compulsory_bytes(m, n, nnz)
         bc_loc = H.compulsory_bytes(i_e - i_s, n, nnz_loc)
         gflops = 2.0 * nnz / (ms_step * 1e-3) * 1e-9
+        # DRAM traffic of the shard kernel: captured for the rank-0 shard of config 5 at N = 8 (the default series member)
+        shard_traffic = shard_traffic_note = None
+        if world == 8 and args.rows_per_gpu == 4194304 and MF.format == S.CSR_ADAPTIVE and MF.col_panels in (1, 2):
+            shard_traffic, shard_traffic_note = ncu_traffic("c5shard_n8", "panels_%d" % MF.col_panels)
         xdesc = {"fused": "fused: the SpMV epilogue stores each finished y row of the band into every peer's next-x buffer over NVLink (CUDA IPC)",
                  "nccl": "NCCL: y slots all-gathered in place (grouped ncclSend / ncclRecv between every pair, band rows only) per row chunk on a second stream"}[vbest["exchange"]]
         sdesc = "mailbox barrier over peer memory (one-warp kernel, no NCCL call in the iteration)" if vbest["scalar_sync"] else "ncclAllReduce of the norm"
@@ -947,8 +954,8 @@ def run_power(args):
             "roofline_frac_nominal_8TBs": round(bc / (ms_step * 1e-3) * 1e-9 / (NOMINAL_HBM_GBS * world), 4),
             "roofline": {"bound": "hbm", "kernel": "csr_tile_kernel" if MF.format == S.CSR_ADAPTIVE else "sell_kernel",
                          "achieved": round(bc_loc / kern_ms * 1e-6, 1), "peak": peak, "unit": "GB/s",
-                         "frac": round(bc_loc / kern_ms * 1e-6 / peak, 4), "traffic": None, "peak_source": peak_src,
-                         "kernel_only_ms": round(kern_ms, 5),
+                         "frac": round(bc_loc / kern_ms * 1e-6 / peak, 4), "traffic": shard_traffic, "traffic_note": shard_traffic_note,
+                         "peak_source": peak_src, "kernel_only_ms": round(kern_ms, 5),
                          "achieved_def": "rank-0 shard compulsory bytes / slowest rank's kernel-only SpMV time (CUDA events, 5 launches, plain product)"},
             "limiter": {"kernel_only_ms": round(kern_ms, 5), "iteration_ms": round(ms_step, 5),
                         "exchange_and_sync_ms": round(ms_step - kern_ms, 5)},
