@@ -41,6 +41,11 @@ def main():
                     help="medium: synthetic_matrices_medium_dataset.txt (config 2); twins_range: the 3 637 lines of "
                          "validation_matrices_10_samples_30_range_twins.txt (config 3), harness.validation_twins_range()")
     ap.add_argument("--max-nnz", type=float, default=1.6e9, help="skip lines whose nominal rows x avg exceeds this (int32 index space / HBM)")
+    ap.add_argument("--max-skew", type=float, default=0.0,
+                    help="skip lines whose skew parameter exceeds this (0 = no limit): one row of skew x avg entries is ONE sequential random "
+                         "stream for the device generator (the mawi twin's 8e6-skew variants: 100 s each); the summary counts what was skipped")
+    ap.add_argument("--min-skew", type=float, default=0.0, help="only lines whose skew parameter is at least this (re-measuring the giant-row lines)")
+    ap.add_argument("--limit", type=int, default=0, help="run at most this many lines (0 = all selected)")
     ap.add_argument("--resume", action="append", default=[],
                     help="JSONL of an earlier (interrupted) run of the same sweep: lines already measured there are not run again and "
                          "count in the summary (the reference's sweep script retries / skips finished work too, benchmark_code/BENCH/run.sh:672-745); repeatable")
@@ -55,6 +60,11 @@ def main():
         peak = 6650.0
     dataset = H.medium_dataset() if args.dataset == "medium" else [p for p, _ in H.validation_twins_range()]
     lines = [p for i, p in enumerate(dataset) if i % args.stride == args.offset % args.stride and p.rows * p.avg <= args.max_nnz]
+    if args.min_skew > 0:
+        lines = [p for p in lines if p.skew >= args.min_skew]
+    n_skew_skipped = sum(1 for p in lines if args.max_skew > 0 and p.skew > args.max_skew)
+    if args.max_skew > 0:
+        lines = [p for p in lines if p.skew <= args.max_skew]
     # resume: records of earlier runs (kept for the summary), their lines skipped
     prior = {}
     for path in args.resume:
@@ -66,6 +76,8 @@ def main():
                     continue                     # a line cut off when the earlier run was killed
                 if "matrix" in r and "best_ms" in r:
                     prior[r["matrix"]] = r
+    if args.limit > 0:
+        lines = lines[:args.limit]
     wanted = {p.line() for p in lines}
     resumed = [r for k, r in prior.items() if k in wanted]
     lines = [p for p in lines if p.line() not in prior]
@@ -148,7 +160,7 @@ def main():
         torch.cuda.empty_cache()
     # summary per footprint class
     summ = {"summary": True, "lines_run": done, "lines_resumed": len(resumed), "lines_selected": len(lines) + len(resumed), "dataset": args.dataset, "dataset_lines": len(dataset), "stride": args.stride,
-            "generator": args.generator, "wall_s": round(time.time() - t_start, 1), "pass1_host_s": round(t_pass1, 1),
+            "generator": args.generator, "skipped_for_skew": n_skew_skipped, "wall_s": round(time.time() - t_start, 1), "pass1_host_s": round(t_pass1, 1),
             "fill_s": round(t_fill, 1), "hbm_peak_GBs": peak, "stopped_early": stopped, "classes": {}}
     for cls in ("<32MB", "32-128MB", "128-512MB", ">=512MB", "all"):
         rs = [r for r in recs if "best_ms" in r and (cls == "all" or r["class"] == cls)]
